@@ -1,0 +1,83 @@
+// api.cu -- library-level entry points of libfetode.so: version, error strings, device query
+// and the FP32 peak probe bench.py uses as the CUDA-core roofline denominator.
+#include "common.cuh"
+#include <cstdio>
+
+extern "C" int fetode_version(void) { return FETODE_VERSION; }
+
+extern "C" const char* fetode_strerror(int rc) {
+    switch (rc) {
+        case FETODE_OK: return "ok";
+        case FETODE_EINVAL: return "fetode: invalid argument";
+        case FETODE_EUNSUPPORTED: return "fetode: shape or option not supported by the sm_100a kernels";
+        case FETODE_ENOGPU: return "fetode: no CUDA device of compute capability 10.x";
+        case FETODE_ESHAPE: return "fetode: shape mismatch";
+        default: break;
+    }
+    if (rc > 0) return cudaGetErrorString((cudaError_t)rc);
+    return "fetode: unknown error";
+}
+
+extern "C" int fetode_device_info(int* sm_count, int* cc_major, int* cc_minor, int* clock_khz) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return FETODE_ENOGPU;
+    int v = 0;
+    if (sm_count) { e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev); if (e) return (int)e; *sm_count = v; }
+    if (cc_major) { e = cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMajor, dev); if (e) return (int)e; *cc_major = v; }
+    if (cc_minor) { e = cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMinor, dev); if (e) return (int)e; *cc_minor = v; }
+    if (clock_khz) { e = cudaDeviceGetAttribute(&v, cudaDevAttrClockRate, dev); if (e) return (int)e; *clock_khz = v; }
+    return FETODE_OK;
+}
+
+namespace {
+// 8 independent FFMA chains per thread, 4096 iterations: pure FMA-pipe work.
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, float a, float b, int iters) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (float)(threadIdx.x + i);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = fmaf(v[i], a, b);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += v[i];
+    if (s == 123.456f) out[0] = s;      // never true; keeps the chains alive
+}
+}  // namespace
+
+extern "C" int fetode_probe_fp32_peak(double* tflops, void* stream) {
+    FETODE_CHECK_ARG(tflops != nullptr);
+    cudaStream_t st = (cudaStream_t)stream;
+    int sms = 0;
+    int rc = fetode_device_info(&sms, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    float* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, 4);      // probe only: the one allocation in the library
+    if (e) return (int)e;
+    const int iters = 4096, blocks = sms * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0, st);
+        fp32_peak_kernel<<<blocks, threads, 0, st>>>(d, 0.999f, 0.001f, iters);
+        cudaEventRecord(e1, st);
+        e = cudaEventSynchronize(e1);
+        if (e) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flop = 2.0 * 64.0 * iters * (double)blocks * threads;
+        const double tf = flop / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d);
+    if (e) return (int)e;
+    *tflops = best;
+    return FETODE_OK;
+}

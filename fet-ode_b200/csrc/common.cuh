@@ -1,0 +1,120 @@
+// common.cuh -- device helpers shared by the fetode kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/fetode.h"
+
+#define FETODE_LOG2E 1.4426950408889634f
+
+#define FETODE_CHECK_ARG(cond)            do { if (!(cond)) return FETODE_EINVAL; } while (0)
+#define FETODE_CHECK_SHAPE(cond)          do { if (!(cond)) return FETODE_ESHAPE; } while (0)
+#define FETODE_CHECK_SUPPORTED(cond)      do { if (!(cond)) return FETODE_EUNSUPPORTED; } while (0)
+#define FETODE_LAUNCH_RC()                ((int)cudaGetLastError())
+
+namespace fetode {
+
+__host__ __device__ constexpr int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// MUFU wrappers.  ex2/rcp approximations are within 2 ulp / 1 ulp, well inside the 1e-5
+// max-norm tolerance of the per-RHS parity gate; the bit-exact hard gate does NOT use them.
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// Exponent clamp for values that enter a batched reciprocal: 2^30 per factor keeps a product
+// of four below 2^127, and 1/(1+2^30) = 9.3e-10 is indistinguishable from 0 at fp32 output scale.
+#define FETODE_EXP_CLAMP 30.0f
+
+// r[i] = 1 / a[i] for N values with ceil(N/4) MUFU.RCP instead of N (a[i] in [1, 2^30+1]).
+template <int N>
+__device__ __forceinline__ void rcp_batch(const float (&a)[N], float (&r)[N]) {
+    constexpr int Q = N / 4;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+        const float a0 = a[4 * q], a1 = a[4 * q + 1], a2 = a[4 * q + 2], a3 = a[4 * q + 3];
+        const float p01 = a0 * a1, p23 = a2 * a3;
+        const float inv = rcp_approx(p01 * p23);
+        const float q01 = inv * p23, q23 = inv * p01;
+        r[4 * q] = q01 * a1;
+        r[4 * q + 1] = q01 * a0;
+        r[4 * q + 2] = q23 * a3;
+        r[4 * q + 3] = q23 * a2;
+    }
+    constexpr int R = N - 4 * Q;
+    if constexpr (R == 1) {
+        r[4 * Q] = rcp_approx(a[4 * Q]);
+    } else if constexpr (R == 2) {
+        const float inv = rcp_approx(a[4 * Q] * a[4 * Q + 1]);
+        r[4 * Q] = inv * a[4 * Q + 1];
+        r[4 * Q + 1] = inv * a[4 * Q];
+    } else if constexpr (R == 3) {
+        const float p01 = a[4 * Q] * a[4 * Q + 1];
+        const float inv = rcp_approx(p01 * a[4 * Q + 2]);
+        const float q01 = inv * a[4 * Q + 2];
+        r[4 * Q] = q01 * a[4 * Q + 1];
+        r[4 * Q + 1] = q01 * a[4 * Q];
+        r[4 * Q + 2] = inv * p01;
+    }
+}
+
+// sigmoid(z) with z already multiplied by log2(e):  1 / (1 + 2^-zl)
+__device__ __forceinline__ float sigmoid_l2(float zl) { return rcp_approx(1.0f + ex2_approx(-zl)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Local cubic B-spline evaluation on a padded knot table (3 extrapolated knots either side,
+// so kp[m+3] is the reference's t_m).  Given t_m <= x < t_{m+1} it returns the four values
+// N^3_{m-3..m}(x) that the Cox-de Boor recursion of efficientkan.py:122-128 leaves non-zero;
+// every other entry of the reference's [.., G+k] basis row is exactly 0.  rdp[j] holds
+// 1 / (kp[j+p] - kp[j]).
+__device__ __forceinline__ void bspline3_local(float x, const float* kp, const float* rd1,
+                                               const float* rd2, const float* rd3, int mp,
+                                               float (&v)[4]) {
+    const float left1 = x - kp[mp], right1 = kp[mp + 1] - x;
+    const float left2 = x - kp[mp - 1], right2 = kp[mp + 2] - x;
+    const float left3 = x - kp[mp - 2], right3 = kp[mp + 3] - x;
+    float t = rd1[mp];
+    const float a0 = right1 * t, a1 = left1 * t;
+    t = a0 * rd2[mp - 1];
+    const float b0 = right1 * t;
+    float saved = left2 * t;
+    t = a1 * rd2[mp];
+    const float b1 = saved + right2 * t;
+    const float b2 = left1 * t;
+    t = b0 * rd3[mp - 2];
+    v[0] = right1 * t;
+    saved = left3 * t;
+    t = b1 * rd3[mp - 1];
+    v[1] = saved + right2 * t;
+    saved = left2 * t;
+    t = b2 * rd3[mp];
+    v[2] = saved + right3 * t;
+    v[3] = left1 * t;
+}
+
+// Interval search: largest m in [0, NK-2] with t_m <= x, for x known to lie in [t_0, t_{NK-1}).
+// gi = {t_0, (NK-1)/(t_last - t_0), t_last, -}; the guess is exact for the default uniform
+// grid and the two loops repair it for the non-uniform grids update_grid() produces
+// (efficientkan.py:184-221).  Comparisons are against the stored fp32 knots, so membership is
+// bit-identical to the reference's (x >= t_j) & (x < t_{j+1}) test (:122).
+__device__ __forceinline__ int bspline_interval(float x, const float* kp, float t0, float inv_h,
+                                                int NK) {
+    int g = (int)((x - t0) * inv_h);
+    g = min(max(g, 0), NK - 2);
+    while (g > 0 && x < kp[g + 3]) --g;
+    while (g < NK - 2 && x >= kp[g + 4]) ++g;
+    return g;
+}
+
+}  // namespace fetode

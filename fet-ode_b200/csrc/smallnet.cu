@@ -1,0 +1,606 @@
+// smallnet.cu -- fused small-width KAN / KANFET network + Runge-Kutta loop (sm_100a).
+//
+// One thread integrates one trajectory; all n_steps RK steps (each 1/2/4 right-hand-side
+// evaluations of the two-layer KAN) run inside one launch with the state in registers.  The
+// network's parameters are folded once per parameter update (fetode_smallnet_pack) into a
+// ~9 KB image that every CTA stages in shared memory; all weight reads are warp-uniform
+// (broadcast) 128-bit LDS except the four spline coefficients selected by the knot interval.
+//
+// Reference arithmetic being replaced (file:line relative to the reference checkout):
+//   KAN.forward / KANLinear.forward           efficient_kan/efficientkan.py:160-182, 274-279
+//   b_splines (Cox-de Boor)                   efficient_kan/efficientkan.py:117-131
+//   LogisticBasis.forward                     efficient_kan/efficientkan.py:20-24
+//   TwoDimensionFerroelectricBasis.forward    ferro_class.py:547-592      (KANFET branch)
+//   integrate_euler / rk2 / rk4               train_ecg_kan_fet_nn_ode.py:670-705
+//   odeint_rk4                                train_kan_fet_ett.py:51-83
+//   torchdiffeq fixed-grid euler/midpoint/rk4 (call sites train_kanfet_node_predprey.py:252)
+//
+// Folding (all exact in real arithmetic; fp32 rounding differs from the reference by O(1e-7)):
+//   sigmoid(z) = 1/(1+2^(-z*log2e)),  tanh(z) = 1 - 2/(1+2^(2z*log2e)),  branch_sign == 1
+//   (never written by TwoDimensionFerroelectricBasis) => momentum = 1 - 2(1-alpha)*to_lower.
+//   With r = 1/(1+2^t3):  coef*(Ps*tanh+bias)*W = W*coef*(Ps+bias) + (-2*W*coef*Ps)*r ; the first
+//   term is input independent and summed into a per-output bias at pack time.
+#include "common.cuh"
+
+namespace fetode {
+
+constexpr int SN_THREADS = 128;
+
+// Shared-memory image.  Everything whose size depends only on (D, NB, G) sits at a compile-time
+// offset; everything per hidden unit h is gathered into one record of REC floats so the fused
+// hidden-unit loop walks a single pointer with immediate offsets.
+//   hdr[4]      {gate_slope*log2e layer 1, layer 2, -, -}
+//   layer-1 input tables, per input d < D: padded knots kp[NKP], 1/(kp[j+p]-kp[j]) p=1..3,
+//               gi[4] = {t_0, (NK-1)/(t_last-t_0), t_last, -}, branch params bp[NB][4]
+//   b2[4]       layer-2 output bias (folded branch constants)
+//   rec[H]:     b1[4] (layer-1 bias of output h) | wu1[D][FU] ([base | branch j] weights of
+//               output h) | ws1[D][SPP] (spline coefficients, s stored at s+3) |
+//               layer-2 tables of input h: kp, rd1, rd2, rd3, gi, bp | wu2[FU][DV] | ws2[SPP][DV]
+struct SNLayout {
+    int D, H, NB, NK, NKP, S, SPP, FU, DV;
+    int hdr, l1_kn, l1_rd1, l1_rd2, l1_rd3, l1_gi, l1_bp, b2, rec0, REC;
+    int r_b1, r_wu1, r_ws1, r_kn, r_rd1, r_rd2, r_rd3, r_gi, r_bp, r_wu2, r_ws2;
+    int total;
+};
+
+__host__ __device__ constexpr SNLayout sn_layout(int D, int H, int NB, int G) {
+    SNLayout L{};
+    L.D = D; L.H = H; L.NB = NB;
+    L.NK = G + 7;                       // knots per input (spline_order 3)
+    L.NKP = round_up(L.NK + 6, 4);      // + 3 extrapolated knots either side
+    L.S = G + 3;                        // spline coefficients per input
+    L.SPP = round_up(L.S + 6, 4);       // + 3 zero coefficients either side
+    L.FU = round_up(1 + NB, 4);         // [silu | branch j] weights, padded
+    L.DV = D <= 1 ? 1 : (D == 2 ? 2 : 4);
+    int o = 0;
+    L.hdr = o; o += 4;
+    L.l1_kn = o; o += D * L.NKP;
+    L.l1_rd1 = o; o += D * L.NKP;
+    L.l1_rd2 = o; o += D * L.NKP;
+    L.l1_rd3 = o; o += D * L.NKP;
+    L.l1_gi = o; o += D * 4;
+    L.l1_bp = o; o += D * NB * 4;
+    L.b2 = o; o += 4;
+    L.rec0 = o;
+    int r = 0;
+    L.r_b1 = r; r += 4;
+    L.r_wu1 = r; r += D * L.FU;
+    L.r_ws1 = r; r += D * L.SPP;
+    L.r_kn = r; r += L.NKP;
+    L.r_rd1 = r; r += L.NKP;
+    L.r_rd2 = r; r += L.NKP;
+    L.r_rd3 = r; r += L.NKP;
+    L.r_gi = r; r += 4;
+    L.r_bp = r; r += NB * 4;
+    L.r_wu2 = r; r += L.FU * L.DV;
+    L.r_ws2 = r; r += L.SPP * L.DV;
+    L.REC = r;
+    L.total = o + H * r;
+    return L;
+}
+
+// ------------------------------------------------------------------------------------------
+// pack: fold the two layers' parameters into the image
+// ------------------------------------------------------------------------------------------
+// padded knots: kp[j+3] = t_j ; 3 knots extrapolated either side with the end spacings so that every
+// read of the local evaluation is finite (those basis values meet zero coefficients)
+__device__ inline void pack_knots_row(const float* t, int NK, int NKP, float* kp, float* rd1,
+                                      float* rd2, float* rd3, float* gi) {
+    for (int j = 0; j < NKP; ++j) {
+        const int jj = j - 3;
+        float v;
+        if (jj < 0) v = t[0] + (float)jj * (t[1] - t[0]);
+        else if (jj >= NK) v = t[NK - 1] + (float)(jj - NK + 1) * (t[NK - 1] - t[NK - 2]);
+        else v = t[jj];
+        kp[j] = v;
+    }
+    for (int j = 0; j < NKP; ++j) {
+        rd1[j] = (j + 1 < NKP) ? 1.0f / (kp[j + 1] - kp[j]) : 0.f;
+        rd2[j] = (j + 2 < NKP) ? 1.0f / (kp[j + 2] - kp[j]) : 0.f;
+        rd3[j] = (j + 3 < NKP) ? 1.0f / (kp[j + 3] - kp[j]) : 0.f;
+    }
+    gi[0] = t[0];
+    gi[1] = (float)(NK - 1) / (t[NK - 1] - t[0]);
+    gi[2] = t[NK - 1];
+    gi[3] = 0.f;
+}
+
+__device__ inline double branch_w(const fetode_kanlayer_t& P, int o, int i, int j) {
+    double w = (double)P.branch_weight[(size_t)o * P.in_features * P.num_basis + i * P.num_basis + j] *
+               (double)P.scale_logistic;
+    if (P.branch_scaler) w *= (double)P.branch_scaler[o];
+    return w;
+}
+
+// bp[j] = the four folded constants of branch basis (i, j)
+__device__ inline float4 branch_params(const fetode_kanlayer_t& P, int idx) {
+    const double l2e = 1.4426950408889634;
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (P.branch == FETODE_BRANCH_FERRO2D) {
+        const double k = P.bp[0][idx], Ec = P.bp[1][idx];
+        q.x = (float)((double)P.gate_slope * Ec * l2e);      // c1: cneg = 1/(1+2^(x*gl+c1))
+        q.y = (float)(2.0 * l2e * k);                          // k'
+        q.z = (float)(2.0 * l2e * k * Ec);                     // c2'
+        q.w = (float)(-2.0 * (1.0 - (double)P.alpha) * 2.0 * l2e * k * Ec);   // c3
+    } else if (P.branch == FETODE_BRANCH_LOGISTIC) {
+        const double a = P.bp[0][idx], b = P.bp[1][idx];
+        q.x = (float)(-a * l2e);
+        q.y = (float)(a * b * l2e);
+    }
+    return q;
+}
+
+// multiplier of r = 1/(1+2^t) in the folded branch contraction, and its constant companion
+__device__ inline void branch_fold(const fetode_kanlayer_t& P, int o, int i, int j, double& wr, double& wc) {
+    const double w = branch_w(P, o, i, j);
+    const int idx = i * P.num_basis + j;
+    if (P.branch == FETODE_BRANCH_FERRO2D) {
+        const double Ps = P.bp[2][idx], bias = P.bp[3][idx], coef = P.bp[4][idx];
+        wr = -2.0 * w * coef * Ps;
+        wc = w * coef * (Ps + bias);
+    } else {
+        wr = 2.0 * w;
+        wc = 0.0;
+    }
+}
+
+__global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2, SNLayout L, float* img) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int D = L.D, H = L.H, NB = L.NB, S = L.S;
+    for (int i = tid; i < L.total; i += nt) img[i] = 0.f;
+    __syncthreads();
+    if (tid == 0) {
+        img[L.hdr + 0] = P1.gate_slope * FETODE_LOG2E;
+        img[L.hdr + 1] = P2.gate_slope * FETODE_LOG2E;
+    }
+    for (int d = tid; d < D; d += nt)
+        pack_knots_row(P1.grid + (size_t)d * L.NK, L.NK, L.NKP, img + L.l1_kn + d * L.NKP,
+                       img + L.l1_rd1 + d * L.NKP, img + L.l1_rd2 + d * L.NKP, img + L.l1_rd3 + d * L.NKP,
+                       img + L.l1_gi + d * 4);
+    for (int idx = tid; idx < D * NB; idx += nt)
+        reinterpret_cast<float4*>(img + L.l1_bp)[idx] = branch_params(P1, idx);
+    for (int o = tid; o < D; o += nt) {
+        double b = P2.branch_bias ? (double)P2.branch_bias[o] : 0.0;
+        for (int h = 0; h < H; ++h)
+            for (int j = 0; j < NB; ++j) { double wr, wc; branch_fold(P2, o, h, j, wr, wc); b += wc; }
+        img[L.b2 + o] = (float)b;
+    }
+    for (int h = tid; h < H; h += nt) {
+        float* rec = img + L.rec0 + h * L.REC;
+        double b = P1.branch_bias ? (double)P1.branch_bias[h] : 0.0;
+        for (int d = 0; d < D; ++d) {
+            float* wu = rec + L.r_wu1 + d * L.FU;
+            wu[0] = P1.base_weight[h * D + d];
+            for (int j = 0; j < NB; ++j) {
+                double wr, wc;
+                branch_fold(P1, h, d, j, wr, wc);
+                wu[1 + j] = (float)wr;
+                b += wc;
+            }
+            float* ws = rec + L.r_ws1 + d * L.SPP;
+            const float sc = P1.spline_scaler ? P1.spline_scaler[h * D + d] : 1.0f;
+            for (int s = 0; s < S; ++s) ws[s + 3] = P1.spline_weight[(h * D + d) * S + s] * sc;
+        }
+        rec[L.r_b1] = (float)b;
+        pack_knots_row(P2.grid + (size_t)h * L.NK, L.NK, L.NKP, rec + L.r_kn, rec + L.r_rd1, rec + L.r_rd2,
+                       rec + L.r_rd3, rec + L.r_gi);
+        for (int j = 0; j < NB; ++j) reinterpret_cast<float4*>(rec + L.r_bp)[j] = branch_params(P2, h * NB + j);
+        for (int o = 0; o < D; ++o) {
+            float* wu = rec + L.r_wu2 + o;
+            wu[0] = P2.base_weight[o * H + h];
+            for (int j = 0; j < NB; ++j) { double wr, wc; branch_fold(P2, o, h, j, wr, wc); wu[(1 + j) * L.DV] = (float)wr; }
+            float* ws = rec + L.r_ws2 + o;
+            const float sc = P2.spline_scaler ? P2.spline_scaler[o * H + h] : 1.0f;
+            for (int s = 0; s < S; ++s) ws[(s + 3) * L.DV] = P2.spline_weight[(o * H + h) * S + s] * sc;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// device: per-input features
+// ------------------------------------------------------------------------------------------
+// r[j] = 1/(1+2^t_j): the only input-dependent factor of branch basis j (see header comment)
+template <int NB, int BR>
+__device__ __forceinline__ void branch_eval(float x, float omu, float gl, const float4* __restrict__ bp,
+                                            float (&r)[NB > 0 ? NB : 1]) {
+    if constexpr (NB > 0 && BR == FETODE_BRANCH_FERRO2D) {
+        float a[NB], cn[NB];
+        const float xg = x * gl;
+#pragma unroll
+        for (int j = 0; j < NB; ++j)
+            a[j] = 1.0f + ex2_approx(fminf(xg + bp[j].x, FETODE_EXP_CLAMP));
+        rcp_batch<NB>(a, cn);                                   // crossed_neg_Ec  ferro_class.py:563
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+            const float4 p = bp[j];
+            const float sl = omu * cn[j];                       // switch_to_lower :567
+            const float t = fmaf(p.w, sl, fmaf(p.y, x, p.z));   // 2*log2e*k*(x + Ec*momentum) :572-575
+            a[j] = 1.0f + ex2_approx(fminf(t, FETODE_EXP_CLAMP));
+        }
+        rcp_batch<NB>(a, r);                                    // tanh = 1 - 2 r           :578
+    } else if constexpr (NB > 0 && BR == FETODE_BRANCH_LOGISTIC) {
+        float a[NB];
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+            const float4 p = bp[j];
+            a[j] = 1.0f + ex2_approx(fminf(fmaf(x, p.x, p.y), FETODE_EXP_CLAMP));
+        }
+        rcp_batch<NB>(a, r);                                    // phi = 2 r  efficientkan.py:24
+    }
+}
+
+struct SNArgs {
+    const float* packed;
+    const float* y0;
+    float* y_out;
+    float* state;        // [B, D+H] in/out or null
+    float* traj;         // [n_dump, B, D] or null
+    float* ckpt;         // [n_steps, D+D+H, B] or null
+    long long B;
+    float dt, hdt, dt6;
+    int H, tab, n_steps, dump_every, state_is_zero;
+};
+
+constexpr int TAB_RHS_ONLY = -1;
+
+// One right-hand-side evaluation out = KAN(y).  prev1 (registers) / prev2 (shared-memory column,
+// stride SN_THREADS) hold the previous input of each layer and are advanced to the current one,
+// exactly like the reference's prev_x buffer is by every forward call (ferro_class.py:584-590).
+template <int D, int NB, int G, int BR>
+__device__ __forceinline__ void sn_rhs(const float* __restrict__ sm, int H, const float (&y)[D],
+                                       float (&prev1)[D], float* prev2, float (&out)[D]) {
+    constexpr SNLayout L = sn_layout(D, 1, NB, G);
+    constexpr int NBR = NB > 0 ? NB : 1;
+    constexpr int DV = L.DV, FU = L.FU, NKP = L.NKP, SPP = L.SPP, NK = L.NK;
+    const float gl1 = sm[L.hdr], gl2 = sm[L.hdr + 1];
+    float silu1[D], v1[D][4], r1[D][NBR];
+    int m1[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const float x = y[d];
+        silu1[d] = x * rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));       // efficientkan.py:166
+        float omu = 0.f;
+        if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+            omu = rcp_approx(1.0f + ex2_approx(gl1 * (x - prev1[d])));           // 1 - is_moving_up :560
+            prev1[d] = x;
+        }
+        const float4 gi = reinterpret_cast<const float4*>(sm + L.l1_gi)[d];
+        m1[d] = -1;
+        v1[d][0] = v1[d][1] = v1[d][2] = v1[d][3] = 0.f;
+        if (x >= gi.x && x < gi.z) {
+            const float* kp = sm + L.l1_kn + d * NKP;
+            const int m = bspline_interval(x, kp, gi.x, gi.y, NK);
+            bspline3_local(x, kp, sm + L.l1_rd1 + d * NKP, sm + L.l1_rd2 + d * NKP,
+                           sm + L.l1_rd3 + d * NKP, m + 3, v1[d]);
+            m1[d] = m;
+        }
+        branch_eval<NB, BR>(x, omu, gl1, reinterpret_cast<const float4*>(sm + L.l1_bp) + d * NB, r1[d]);
+    }
+    {
+        const float4 b2 = *reinterpret_cast<const float4*>(sm + L.b2);
+        out[0] = b2.x;
+        if constexpr (D > 1) out[1] = b2.y;
+        if constexpr (D > 2) out[2] = b2.z;
+        if constexpr (D > 3) out[3] = b2.w;
+    }
+    const float* rec = sm + L.rec0;
+#pragma unroll 1
+    for (int h = 0; h < H; ++h, rec += L.REC) {
+        // ---- layer 1, output h
+        float acc = rec[L.r_b1];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const float4* w4 = reinterpret_cast<const float4*>(rec + L.r_wu1 + d * FU);
+            float feat[FU];
+            feat[0] = silu1[d];
+#pragma unroll
+            for (int j = 0; j < NB; ++j) feat[1 + j] = r1[d][j];
+#pragma unroll
+            for (int j = 1 + NB; j < FU; ++j) feat[j] = 0.f;
+#pragma unroll
+            for (int q = 0; q < FU / 4; ++q) {
+                const float4 w = w4[q];
+                acc = fmaf(w.x, feat[4 * q], acc);
+                acc = fmaf(w.y, feat[4 * q + 1], acc);
+                acc = fmaf(w.z, feat[4 * q + 2], acc);
+                acc = fmaf(w.w, feat[4 * q + 3], acc);
+            }
+            if (m1[d] >= 0) {
+                const float* ws = rec + L.r_ws1 + d * SPP + m1[d];
+                acc = fmaf(ws[0], v1[d][0], acc);
+                acc = fmaf(ws[1], v1[d][1], acc);
+                acc = fmaf(ws[2], v1[d][2], acc);
+                acc = fmaf(ws[3], v1[d][3], acc);
+            }
+        }
+        // ---- layer 2, input h
+        const float x = acc;
+        const float sl = x * rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));
+        float omu = 0.f;
+        if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+            omu = rcp_approx(1.0f + ex2_approx(gl2 * (x - prev2[h * SN_THREADS])));
+            prev2[h * SN_THREADS] = x;
+        }
+        float r2[NBR];
+        branch_eval<NB, BR>(x, omu, gl2, reinterpret_cast<const float4*>(rec + L.r_bp), r2);
+        {
+            const float* wu = rec + L.r_wu2;
+            float feat[1 + NB];
+            feat[0] = sl;
+#pragma unroll
+            for (int j = 0; j < NB; ++j) feat[1 + j] = r2[j];
+#pragma unroll
+            for (int f = 0; f < 1 + NB; ++f) {
+                if constexpr (DV == 1) {
+                    out[0] = fmaf(wu[f], feat[f], out[0]);
+                } else if constexpr (DV == 2) {
+                    const float2 w = reinterpret_cast<const float2*>(wu)[f];
+                    out[0] = fmaf(w.x, feat[f], out[0]);
+                    out[1] = fmaf(w.y, feat[f], out[1]);
+                } else {
+                    const float4 w = reinterpret_cast<const float4*>(wu)[f];
+                    out[0] = fmaf(w.x, feat[f], out[0]);
+                    out[1] = fmaf(w.y, feat[f], out[1]);
+                    if constexpr (D > 2) out[2] = fmaf(w.z, feat[f], out[2]);
+                    if constexpr (D > 3) out[3] = fmaf(w.w, feat[f], out[3]);
+                }
+            }
+        }
+        const float4 gi = *reinterpret_cast<const float4*>(rec + L.r_gi);
+        if (x >= gi.x && x < gi.z) {
+            const float* kp = rec + L.r_kn;
+            const int m = bspline_interval(x, kp, gi.x, gi.y, NK);
+            float v[4];
+            bspline3_local(x, kp, rec + L.r_rd1, rec + L.r_rd2, rec + L.r_rd3, m + 3, v);
+            const float* ws = rec + L.r_ws2 + m * DV;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if constexpr (DV == 1) {
+                    out[0] = fmaf(ws[c], v[c], out[0]);
+                } else if constexpr (DV == 2) {
+                    const float2 w = reinterpret_cast<const float2*>(ws)[c];
+                    out[0] = fmaf(w.x, v[c], out[0]);
+                    out[1] = fmaf(w.y, v[c], out[1]);
+                } else {
+                    const float4 w = reinterpret_cast<const float4*>(ws)[c];
+                    out[0] = fmaf(w.x, v[c], out[0]);
+                    out[1] = fmaf(w.y, v[c], out[1]);
+                    if constexpr (D > 2) out[2] = fmaf(w.z, v[c], out[2]);
+                    if constexpr (D > 3) out[3] = fmaf(w.w, v[c], out[3]);
+                }
+            }
+        }
+    }
+}
+
+template <int D, int NB, int G, int BR>
+__global__ void __launch_bounds__(SN_THREADS, 4) smallnet_rk_kernel(const SNArgs a) {
+    extern __shared__ float4 sn_smem4[];
+    float* sm = reinterpret_cast<float*>(sn_smem4);
+    constexpr SNLayout L0 = sn_layout(D, 0, NB, G);
+    const int H = a.H;
+    const int total = L0.total + H * L0.REC;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < total / 4; i += SN_THREADS)
+        sn_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    float* prev2 = sm + total + tid;          // [H][SN_THREADS] column of this thread
+    __syncthreads();
+
+    const long long b = (long long)blockIdx.x * SN_THREADS + tid;
+    if (b >= a.B) return;
+    const int SF = (BR == FETODE_BRANCH_FERRO2D) ? D + H : 0;
+
+    float y[D], prev1[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) { y[d] = a.y0[b * D + d]; prev1[d] = 0.f; }
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+        if (!a.state_is_zero) {
+#pragma unroll
+            for (int d = 0; d < D; ++d) prev1[d] = a.state[b * SF + d];
+#pragma unroll 1
+            for (int h = 0; h < H; ++h) prev2[h * SN_THREADS] = a.state[b * SF + D + h];
+        } else {
+#pragma unroll 1
+            for (int h = 0; h < H; ++h) prev2[h * SN_THREADS] = 0.f;
+        }
+    }
+
+    const int tab = a.tab;
+    if (tab == TAB_RHS_ONLY) {
+        float out[D];
+        sn_rhs<D, NB, G, BR>(sm, H, y, prev1, prev2, out);
+#pragma unroll
+        for (int d = 0; d < D; ++d) y[d] = out[d];
+    } else {
+        const int nst = tab == FETODE_TABLEAU_EULER ? 1 : (tab == FETODE_TABLEAU_MIDPOINT ? 2 : 4);
+        const int NC = D + SF;
+#pragma unroll 1
+        for (int step = 0; step < a.n_steps; ++step) {
+            if (a.ckpt) {
+                float* c = a.ckpt + ((size_t)step * NC) * a.B + b;
+#pragma unroll
+                for (int d = 0; d < D; ++d) c[(size_t)d * a.B] = y[d];
+                if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) c[(size_t)(D + d) * a.B] = prev1[d];
+#pragma unroll 1
+                    for (int h = 0; h < H; ++h) c[(size_t)(2 * D + h) * a.B] = prev2[h * SN_THREADS];
+                }
+            }
+            float k1[D], k2[D], acc[D], ys[D], kn[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) { k1[d] = k2[d] = acc[d] = 0.f; ys[d] = y[d]; }
+#pragma unroll 1
+            for (int s = 0; s < nst; ++s) {
+                sn_rhs<D, NB, G, BR>(sm, H, ys, prev1, prev2, kn);
+                if (tab == FETODE_TABLEAU_RK4) {
+                    // (k1 + 2*k2 + 2*k3 + k4), stage inputs h + c*k_prev   train_ecg_kan_fet_nn_ode.py:698-703
+                    const float c = (s == 2) ? a.dt : a.hdt;
+                    const float w = (s == 0 || s == 3) ? 1.0f : 2.0f;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        acc[d] = (s == 0) ? kn[d] : fmaf(w, kn[d], acc[d]);
+                        ys[d] = fmaf(c, kn[d], y[d]);
+                    }
+                } else if (tab == FETODE_TABLEAU_RK4_38) {
+                    // torchdiffeq rk4_alt_step_func (3/8 rule); acc carries k3 after stage 2
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        if (s == 0) { k1[d] = kn[d]; ys[d] = y[d] + a.dt * kn[d] * (1.0f / 3.0f); }
+                        else if (s == 1) { k2[d] = kn[d]; ys[d] = y[d] + a.dt * (kn[d] - k1[d] * (1.0f / 3.0f)); }
+                        else if (s == 2) { acc[d] = kn[d]; ys[d] = y[d] + a.dt * (k1[d] - k2[d] + kn[d]); }
+                        else acc[d] = (k1[d] + 3.0f * (k2[d] + acc[d]) + kn[d]) * a.dt * 0.125f;
+                    }
+                } else {
+                    // euler: h + dt*f(h) :676 ; midpoint: k2 = f(h + 0.5*dt*k1), h + dt*k2 :686-689
+#pragma unroll
+                    for (int d = 0; d < D; ++d) { ys[d] = fmaf(a.hdt, kn[d], y[d]); acc[d] = kn[d]; }
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                if (tab == FETODE_TABLEAU_RK4) y[d] = fmaf(a.dt6, acc[d], y[d]);
+                else if (tab == FETODE_TABLEAU_RK4_38) y[d] = y[d] + acc[d];
+                else y[d] = fmaf(a.dt, acc[d], y[d]);
+            }
+            if (a.traj && (step + 1) % a.dump_every == 0) {
+                float* t = a.traj + ((size_t)((step + 1) / a.dump_every - 1) * a.B + b) * D;
+#pragma unroll
+                for (int d = 0; d < D; ++d) t[d] = y[d];
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) a.y_out[b * D + d] = y[d];
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+        if (a.state) {
+#pragma unroll
+            for (int d = 0; d < D; ++d) a.state[b * SF + d] = prev1[d];
+#pragma unroll 1
+            for (int h = 0; h < H; ++h) a.state[b * SF + D + h] = prev2[h * SN_THREADS];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host dispatch
+// ------------------------------------------------------------------------------------------
+static int sn_check(const fetode_smallnet_t* net) {
+    if (!net) return FETODE_EINVAL;
+    if (net->n_layers != 2) return FETODE_EUNSUPPORTED;
+    const int D = net->widths[0], H = net->widths[1];
+    if (net->widths[2] != D) return FETODE_EUNSUPPORTED;
+    if (D < 1 || D > 4 || H < 1 || H > 64) return FETODE_EUNSUPPORTED;
+    if (net->spline_order != 3 || net->grid_size != 5) return FETODE_EUNSUPPORTED;
+    switch (net->branch) {
+        case FETODE_BRANCH_NONE: if (net->num_basis != 0) return FETODE_EINVAL; break;
+        case FETODE_BRANCH_LOGISTIC:
+        case FETODE_BRANCH_FERRO2D:
+            if (net->num_basis != 10) return FETODE_EUNSUPPORTED;
+            break;
+        default: return FETODE_EINVAL;
+    }
+    return FETODE_OK;
+}
+
+template <int D, int NB, int BR>
+static int sn_launch_k(const SNArgs& a, cudaStream_t st) {
+    constexpr SNLayout L0 = sn_layout(D, 0, NB, 5);
+    const size_t smem = (size_t)(L0.total + a.H * L0.REC) * 4 + (size_t)a.H * SN_THREADS * 4;
+    const unsigned grid = (unsigned)((a.B + SN_THREADS - 1) / SN_THREADS);
+    auto kern = smallnet_rk_kernel<D, NB, 5, BR>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<grid, SN_THREADS, smem, st>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+template <int D>
+static int sn_launch_d(const fetode_smallnet_t* net, const SNArgs& a, cudaStream_t st) {
+    switch (net->branch) {
+        case FETODE_BRANCH_NONE: return sn_launch_k<D, 0, FETODE_BRANCH_NONE>(a, st);
+        case FETODE_BRANCH_LOGISTIC: return sn_launch_k<D, 10, FETODE_BRANCH_LOGISTIC>(a, st);
+        case FETODE_BRANCH_FERRO2D: return sn_launch_k<D, 10, FETODE_BRANCH_FERRO2D>(a, st);
+    }
+    return FETODE_EUNSUPPORTED;
+}
+
+static int sn_launch(const fetode_smallnet_t* net, const SNArgs& a, cudaStream_t st) {
+    switch (net->widths[0]) {
+        case 1: return sn_launch_d<1>(net, a, st);
+        case 2: return sn_launch_d<2>(net, a, st);
+        case 3: return sn_launch_d<3>(net, a, st);
+        case 4: return sn_launch_d<4>(net, a, st);
+    }
+    return FETODE_EUNSUPPORTED;
+}
+
+}  // namespace fetode
+
+using namespace fetode;
+
+extern "C" int fetode_smallnet_supported(const fetode_smallnet_t* net) { return sn_check(net); }
+
+extern "C" int64_t fetode_smallnet_packed_floats(const fetode_smallnet_t* net) {
+    if (sn_check(net) != FETODE_OK) return -1;
+    return sn_layout(net->widths[0], net->widths[1], net->num_basis, net->grid_size).total;
+}
+
+extern "C" int64_t fetode_smallnet_state_floats(const fetode_smallnet_t* net) {
+    if (sn_check(net) != FETODE_OK) return -1;
+    return net->branch == FETODE_BRANCH_FERRO2D ? net->widths[0] + net->widths[1] : 0;
+}
+
+extern "C" int fetode_smallnet_pack(const fetode_smallnet_t* net, const fetode_kanlayer_t* layers,
+                                    float* packed, void* stream) {
+    int rc = sn_check(net);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(layers && packed);
+    const int D = net->widths[0], H = net->widths[1];
+    for (int l = 0; l < 2; ++l) {
+        const fetode_kanlayer_t& P = layers[l];
+        FETODE_CHECK_SHAPE(P.in_features == (l ? H : D) && P.out_features == (l ? D : H));
+        FETODE_CHECK_SHAPE(P.grid_size == net->grid_size && P.spline_order == 3);
+        FETODE_CHECK_SHAPE(P.branch == net->branch && P.num_basis == net->num_basis);
+        FETODE_CHECK_ARG(P.grid && P.base_weight && P.spline_weight);
+        if (P.branch != FETODE_BRANCH_NONE) {
+            FETODE_CHECK_ARG(P.branch_weight && P.bp[0] && P.bp[1]);
+            if (P.branch == FETODE_BRANCH_FERRO2D) FETODE_CHECK_ARG(P.bp[2] && P.bp[3] && P.bp[4]);
+        }
+    }
+    const SNLayout L = sn_layout(D, H, net->num_basis, net->grid_size);
+    smallnet_pack_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(layers[0], layers[1], L, packed);
+    return FETODE_LAUNCH_RC();
+}
+
+static int sn_run(const fetode_smallnet_t* net, const float* packed, int tab, const float* y0, float* y_out,
+                  float* state, int state_is_zero, int64_t B, double dt, int32_t n_steps, float* traj,
+                  int32_t dump_every, float* ckpt, void* stream) {
+    int rc = sn_check(net);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(packed && y0 && y_out && B >= 0);
+    if (B == 0) return FETODE_OK;
+    if (net->branch == FETODE_BRANCH_FERRO2D && !state_is_zero) FETODE_CHECK_ARG(state != nullptr);
+    if (traj) FETODE_CHECK_ARG(dump_every >= 1);
+    SNArgs a;
+    a.packed = packed; a.y0 = y0; a.y_out = y_out; a.state = state; a.traj = traj; a.ckpt = ckpt;
+    a.B = B; a.dt = (float)dt; a.hdt = (float)(0.5 * dt); a.dt6 = (float)(dt / 6.0);
+    a.H = net->widths[1]; a.tab = tab;
+    a.n_steps = n_steps; a.dump_every = dump_every > 0 ? dump_every : 1; a.state_is_zero = state_is_zero;
+    return sn_launch(net, a, (cudaStream_t)stream);
+}
+
+extern "C" int fetode_smallnet_rk_fwd(const fetode_smallnet_t* net, const float* packed, int tableau,
+                                      const float* y0, float* y_out, float* state, int state_is_zero,
+                                      int64_t B, double dt, int32_t n_steps, float* traj,
+                                      int32_t dump_every, float* ckpt, void* stream) {
+    FETODE_CHECK_ARG(tableau >= FETODE_TABLEAU_EULER && tableau <= FETODE_TABLEAU_RK4_38 && n_steps >= 0);
+    return sn_run(net, packed, tableau, y0, y_out, state, state_is_zero, B, dt, n_steps, traj, dump_every,
+                  ckpt, stream);
+}
+
+extern "C" int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
+                                   float* dy, float* state, int state_is_zero, int64_t B, void* stream) {
+    return sn_run(net, packed, TAB_RHS_ONLY, y, dy, state, state_is_zero, B, 0.0, 0, nullptr, 1, nullptr,
+                  stream);
+}

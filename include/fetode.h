@@ -1,0 +1,202 @@
+/*
+ * fetode.h -- C ABI of libfetode.so: the B200 (sm_100a) implementation of the KAN-FET
+ * neural-ODE right-hand side.
+ *
+ * This is the drop-in boundary.  The reference (sallywang147/FET-ODE @ 704a0df4) has no FFI of
+ * its own: the path sits behind torch.nn.Module.forward calls and the torchdiffeq-style
+ * odeint(func, y0, t) call.  Each entry point below therefore names the reference *method*
+ * (file:line, relative to the reference checkout) whose arithmetic it replaces; INTEGRATION.md
+ * shows the ctypes stub a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to contiguous row-major fp32 unless marked "host";
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - every function returns 0 on success, a negative FETODE_E* code on a usage error, or a
+ *     positive cudaError_t; fetode_strerror() renders all three;
+ *   - nothing allocates device memory: scratch comes from the caller (sizes from the
+ *     *_floats / *_bytes queries); launches are asynchronous on `stream`;
+ *   - re-entrant, no global state.
+ */
+#ifndef FETODE_H_
+#define FETODE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FETODE_VERSION 100
+#define FETODE_API __attribute__((visibility("default")))
+
+/* ---- error codes ------------------------------------------------------------------- */
+#define FETODE_OK            0
+#define FETODE_EINVAL       (-1)   /* bad argument (null pointer, non-positive size, ...)  */
+#define FETODE_EUNSUPPORTED (-2)   /* shape / option outside what the kernels implement    */
+#define FETODE_ENOGPU       (-3)   /* no sm_100 device                                     */
+#define FETODE_ESHAPE       (-4)   /* shape mismatch (reference raises AssertionError)     */
+
+FETODE_API const char* fetode_strerror(int rc);
+FETODE_API int fetode_version(void);
+/* host out-params; any may be NULL */
+FETODE_API int fetode_device_info(int* sm_count, int* cc_major, int* cc_minor, int* clock_khz);
+
+/* ---- branch (per-input basis in the "logistic" slot of KANLinear) ------------------ */
+#define FETODE_BRANCH_NONE     0   /* enable_logistic_basis=False                           */
+#define FETODE_BRANCH_LOGISTIC 1   /* LogisticBasis              efficientkan.py:7-24       */
+#define FETODE_BRANCH_FERRO2D  2   /* TwoDimensionFerroelectricBasis  ferro_class.py:526-596 (KANFET) */
+
+/*
+ * One KANLinear layer (efficient_kan/efficientkan.py:27-182; MNIST copy
+ * mnist_kuramoto_kan.py:25-142).  Field names follow the reference's parameter names.
+ * bp[]: branch-basis parameters, each [in_features, num_basis]:
+ *   LOGISTIC: bp[0]=a, bp[1]=b                          (efficientkan.py:17-18)
+ *   FERRO2D : bp[0]=k, bp[1]=Ec, bp[2]=Ps, bp[3]=bias, bp[4]=coef   (ferro_class.py:537-541)
+ */
+typedef struct fetode_kanlayer {
+    int32_t in_features, out_features;
+    int32_t grid_size, spline_order;          /* spline_order must be 3                      */
+    int32_t num_basis;                        /* 0 when branch == NONE                       */
+    int32_t branch;                           /* FETODE_BRANCH_*                             */
+    const float* grid;                        /* [I, G+2k+1]            efficientkan.py:55-61 */
+    const float* base_weight;                 /* [O, I]                                :64   */
+    const float* spline_weight;               /* [O, I, G+k]                           :65   */
+    const float* spline_scaler;               /* [O, I] or NULL                        :67   */
+    const float* branch_weight;               /* logistic_weight [O, I*nb] or NULL     :86   */
+    const float* branch_scaler;               /* logistic_scaler [O] or NULL           :88   */
+    const float* branch_bias;                 /* logistic_bias [O] or NULL  mnist_kuramoto_kan.py:78 */
+    const float* bp[5];
+    float scale_logistic;                     /* efficientkan.py:45,153                      */
+    float gate_slope, alpha;                  /* ferro_class.py:527  (10.0, 0.8)             */
+} fetode_kanlayer_t;
+
+/* Gradient destinations, same shapes as the parameters; NULL = not wanted.  Kernels ACCUMULATE
+ * (+=) into these buffers, so the caller zeroes them first (torch's .grad convention). */
+typedef struct fetode_kanlayer_grads {
+    float* base_weight;
+    float* spline_weight;
+    float* spline_scaler;
+    float* branch_weight;
+    float* branch_scaler;
+    float* branch_bias;
+    float* bp[5];
+} fetode_kanlayer_grads_t;
+
+/* ---- KANLinear, any width (CUDA-core path; the tcgen05 path is selected inside) ------
+ * Replaces KANLinear.forward efficientkan.py:160-182 (b_splines :117-131,
+ * scaled_spline_weight :145-147, scaled_logistic_weight :149-158, LogisticBasis.forward :20-24)
+ * and its autograd backward.
+ *
+ * `wcat` is the folded weight matrix [I*F, O], F = 1 + (G+k) + nb, rows ordered
+ * (i, [silu | spline s | branch j]); it is rebuilt by fetode_kanlinear_pack whenever the
+ * parameters change.  `prev` is the hysteresis state of the FERRO2D branch: the previous input
+ * [B, I]; with prev_is_zero != 0 it is taken as all-zero and not read (first call after
+ * reset_state, ferro_class.py:544,594-596).  prev_out (may alias prev, may be NULL) receives x.
+ */
+FETODE_API int64_t fetode_kanlinear_wcat_floats(const fetode_kanlayer_t* L);
+FETODE_API int fetode_kanlinear_pack(const fetode_kanlayer_t* L, float* wcat, void* stream);
+FETODE_API int fetode_kanlinear_fwd(const fetode_kanlayer_t* L, const float* wcat, const float* x,
+                         const float* prev, int prev_is_zero, float* prev_out,
+                         float* y, int64_t B, void* stream);
+/* scratch for bwd: fetode_kanlinear_bwd_ws_floats(L) floats, need not be zeroed */
+FETODE_API int64_t fetode_kanlinear_bwd_ws_floats(const fetode_kanlayer_t* L);
+FETODE_API int fetode_kanlinear_bwd(const fetode_kanlayer_t* L, const float* wcat, const float* x,
+                         const float* prev, int prev_is_zero, const float* gy,
+                         float* gx /* [B,I] or NULL, overwritten */,
+                         const fetode_kanlayer_grads_t* grads, float* ws,
+                         int64_t B, void* stream);
+
+/* ---- fused small-width KAN / KANFET network + Runge-Kutta loop -----------------------
+ * Replaces, for a stack of KANLinear layers whose widths are all <= 32 (the Lotka-Volterra
+ * KANFET([2,10,2]) of train_kanfet_node_predprey.py:146), the whole of
+ *   KAN.forward efficientkan.py:274-279  inside  integrate_euler/rk2/rk4
+ *   train_ecg_kan_fet_nn_ode.py:670-705 (= odeint_rk4 train_kan_fet_ett.py:51-83 with
+ *   n_substeps folded into n_steps) and torchdiffeq's fixed-grid euler/midpoint/rk4(3/8).
+ * One thread integrates one trajectory; n_steps RK steps run inside one launch.
+ */
+#define FETODE_TABLEAU_EULER    0
+#define FETODE_TABLEAU_MIDPOINT 1   /* integrate_rk2 :681-691 / torchdiffeq "midpoint"       */
+#define FETODE_TABLEAU_RK4      2   /* classic, integrate_rk4 :693-705                      */
+#define FETODE_TABLEAU_RK4_38   3   /* torchdiffeq "rk4" (3/8 rule)                          */
+
+#define FETODE_SMALLNET_MAX_LAYERS 2
+typedef struct fetode_smallnet {
+    int32_t n_layers;                          /* currently exactly 2                        */
+    int32_t widths[FETODE_SMALLNET_MAX_LAYERS + 1];   /* [D, H, D]: in == out (ODE state)    */
+    int32_t grid_size, spline_order, num_basis, branch;
+} fetode_smallnet_t;
+
+/* 0 if the fused kernel has an instantiation for this net, FETODE_EUNSUPPORTED otherwise */
+FETODE_API int fetode_smallnet_supported(const fetode_smallnet_t* net);
+FETODE_API int64_t fetode_smallnet_packed_floats(const fetode_smallnet_t* net);
+/* fold the layers' parameters into the shared-memory image the kernels stage */
+FETODE_API int fetode_smallnet_pack(const fetode_smallnet_t* net, const fetode_kanlayer_t* layers,
+                         float* packed, void* stream);
+/* hysteresis state per trajectory: [B, state_floats] = previous input of every layer */
+FETODE_API int64_t fetode_smallnet_state_floats(const fetode_smallnet_t* net);
+/*
+ * y0 [B,D] -> y_out [B,D] after n_steps steps of size dt.  state (in/out, [B, state_floats]) is
+ * ignored on input when state_is_zero != 0; may be NULL when branch != FERRO2D.
+ * traj (or NULL): [n_steps/dump_every, B, D] receives y after every dump_every-th step.
+ * ckpt (or NULL): [n_steps, B, D + state_floats] receives (y, state) at the START of every step
+ * (what fetode_smallnet_rk_bwd replays from).
+ */
+FETODE_API int fetode_smallnet_rk_fwd(const fetode_smallnet_t* net, const float* packed, int tableau,
+                           const float* y0, float* y_out, float* state, int state_is_zero,
+                           int64_t B, double dt, int32_t n_steps,
+                           float* traj, int32_t dump_every, float* ckpt, void* stream);
+/* one RHS evaluation y -> f(y) (KAN.forward), same state rules */
+FETODE_API int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
+                        float* dy, float* state, int state_is_zero, int64_t B, void* stream);
+
+/* ---- stand-alone ferroelectric neurons ------------------------------------------------
+ * FULL    : FerroelectricBasis.forward ferro_class.py:368-420 (update_branch=0) and
+ *           NoisyFerroelectricBasis.forward :466-519 with noise_std=0 (update_branch=1);
+ *           params [I,O,K]; out [B,O].  prev [B,I]; br [B,I,O,K] or NULL (== all ones).
+ * TWO_D   : TwoDimensionFerroelectricBasis.forward :547-592; params [I,K] (O must be 1);
+ *           out [B,I,K] = basis*coef.
+ * HARDGATE: hysteretic LogisticBasis.forward train_ecg_kan_fet_nn_ode.py:102-134; params [I,K];
+ *           out [B,I,K]; prev is ONE row [I] shared by the whole batch; gate (or NULL) [B,I,K]
+ *           uint8 receives the branch actually taken; prev_out receives the LAST row of x.
+ */
+#define FETODE_FERRO_FULL     0
+#define FETODE_FERRO_TWO_D    1
+#define FETODE_FERRO_HARDGATE 2
+
+typedef struct fetode_ferro {
+    int32_t variant, in_dim, out_dim, num_basis;
+    const float *k, *Ec, *Ps, *bias, *coef;
+    float gate_slope, alpha;                   /* hard gate: gate_slope=5, alpha=breaking point 0.5 */
+    int32_t apply_sigmoid;                     /* HARDGATE only: KANFeatureMixer's sigmoid :419 */
+} fetode_ferro_t;
+
+typedef struct fetode_ferro_grads { float *k, *Ec, *Ps, *bias, *coef; } fetode_ferro_grads_t;
+
+FETODE_API int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
+                     const float* br, float* out, float* basis_out /* or NULL */,
+                     float* br_out /* or NULL */, uint8_t* gate_out /* or NULL */,
+                     int64_t B, void* stream);
+FETODE_API int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
+                     const float* br, const float* gout, float* gx /* [B,I] overwritten, or NULL */,
+                     const fetode_ferro_grads_t* grads /* accumulated */, int64_t B, void* stream);
+
+/* ---- Kuramoto lattice -----------------------------------------------------------------
+ * Kuramoto2D.forward mnist_kuramoto_kan.py:175-204: x [B,H*W] in [0,1] -> feat [B, 2*H*W]
+ * = [cos(theta), sin(theta)] after `steps` Euler steps.  K: device scalar, omega: [H*W].
+ * ckpt (or NULL) [steps, B, H*W] receives theta before every step (for the backward).
+ */
+FETODE_API int fetode_kuramoto_fwd(const float* x, const float* K, const float* omega, int32_t H, int32_t W,
+                        int32_t steps, float dt, float* feat, float* ckpt, int64_t B, void* stream);
+FETODE_API int fetode_kuramoto_bwd(const float* ckpt, const float* theta_final_feat, const float* K,
+                        const float* omega, int32_t H, int32_t W, int32_t steps, float dt,
+                        const float* gfeat, float* gx /* or NULL */, float* gK /* accum */,
+                        float* gomega /* accum */, int64_t B, void* stream);
+
+/* ---- probes used by bench.py for the roofline denominators --------------------------- */
+/* runs an FFMA-only kernel and returns achieved TFLOP/s in *tflops (host) */
+FETODE_API int fetode_probe_fp32_peak(double* tflops, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FETODE_H_ */
