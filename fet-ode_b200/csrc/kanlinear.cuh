@@ -1,0 +1,87 @@
+// kanlinear.cuh -- packed-parameter layout and the per-(row, input) feature evaluation shared by
+// the any-width KANLinear kernels (CUDA-core forward/backward, tcgen05 forward).
+#pragma once
+#include <algorithm>
+#include "common.cuh"
+
+namespace fetode {
+
+// Packed image of one KANLinear layer ("wcat" in the C ABI):
+//   wcat [I*F, O]   folded weights, row (i, f): f = 0 silu | 1..S spline s | S+1.. branch j
+//   bias [O]        branch_bias + the input-independent part of the folded FERRO2D branch
+//   tab  [I, TAB]   per input: padded knots kp[NKP], 1/(kp[j+p]-kp[j]) p=1..3, gi[4], bp[NB][4]
+struct KLLayout {
+    int I, O, G, NB, S, F, NK, NKP, TAB;
+    int t_kn, t_rd1, t_rd2, t_rd3, t_gi, t_bp;
+    long long wcat, bias, tab, total;
+};
+
+__host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
+    KLLayout L{};
+    L.I = I; L.O = O; L.G = G; L.NB = NB;
+    L.S = G + 3;
+    L.F = 1 + L.S + NB;
+    L.NK = G + 7;
+    L.NKP = round_up(L.NK + 6, 4);
+    int t = 0;
+    L.t_kn = t; t += L.NKP;
+    L.t_rd1 = t; t += L.NKP;
+    L.t_rd2 = t; t += L.NKP;
+    L.t_rd3 = t; t += L.NKP;
+    L.t_gi = t; t += 4;
+    L.t_bp = t; t += 4 * NB;
+    L.TAB = t;
+    long long o = 0;
+    L.wcat = o; o += ((long long)I * L.F * O + 3) / 4 * 4;
+    L.bias = o; o += (O + 3) / 4 * 4;
+    L.tab = o; o += (long long)I * L.TAB;
+    L.total = o;
+    return L;
+}
+
+// silu and the single input-dependent factor of each branch basis, see smallnet.cu header:
+//   LOGISTIC: r_j = 1/(1+2^(-a(x-b) log2e))                 (phi = 2 r)
+//   FERRO2D : r_j = 1/(1+2^(2 log2e k (x + Ec*momentum)))   (tanh = 1 - 2 r)
+template <int BR>
+__device__ __forceinline__ float kl_branch_r(float x, float omu, float gl, const float4 p) {
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+        const float cn = rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, gl, p.x), FETODE_EXP_CLAMP)));
+        const float sl = omu * cn;
+        const float t = fmaf(p.w, sl, fmaf(p.y, x, p.z));
+        return rcp_approx(1.0f + ex2_approx(fminf(t, FETODE_EXP_CLAMP)));
+    } else {
+        return rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, p.x, p.y), FETODE_EXP_CLAMP)));
+    }
+}
+
+// All F feature values of one (row, input) pair, written to col[f * stride].
+template <int BR>
+__device__ __forceinline__ void kl_features(float x, float prev, float gl, const float* __restrict__ tab,
+                                            const KLLayout& L, float* col, int stride) {
+    col[0] = x * rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));                 // efficientkan.py:166
+    const int S = L.S;
+    for (int s = 0; s < S; ++s) col[(1 + s) * stride] = 0.f;
+    const float4 gi = *reinterpret_cast<const float4*>(tab + L.t_gi);
+    if (x >= gi.x && x < gi.z) {                                                     // :122 half-open test
+        const float* kp = tab + L.t_kn;
+        const int m = bspline_interval(x, kp, gi.x, gi.y, L.NK);
+        float v[4];
+        bspline3_local(x, kp, tab + L.t_rd1, tab + L.t_rd2, tab + L.t_rd3, m + 3, v);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int s = m - 3 + c;
+            if (s >= 0 && s < S) col[(1 + s) * stride] = v[c];
+        }
+    }
+    if constexpr (BR != FETODE_BRANCH_NONE) {
+        float omu = 0.f;
+        if constexpr (BR == FETODE_BRANCH_FERRO2D)
+            omu = rcp_approx(1.0f + ex2_approx(gl * (x - prev)));                    // 1 - is_moving_up  ferro_class.py:560
+        const float4* bp = reinterpret_cast<const float4*>(tab + L.t_bp);
+        for (int j = 0; j < L.NB; ++j) col[(1 + S + j) * stride] = kl_branch_r<BR>(x, omu, gl, bp[j]);
+    }
+}
+
+int kl_check(const fetode_kanlayer_t* P);
+
+}  // namespace fetode

@@ -82,68 +82,6 @@ __host__ __device__ constexpr SNLayout sn_layout(int D, int H, int NB, int G) {
 // ------------------------------------------------------------------------------------------
 // pack: fold the two layers' parameters into the image
 // ------------------------------------------------------------------------------------------
-// padded knots: kp[j+3] = t_j ; 3 knots extrapolated either side with the end spacings so that every
-// read of the local evaluation is finite (those basis values meet zero coefficients)
-__device__ inline void pack_knots_row(const float* t, int NK, int NKP, float* kp, float* rd1,
-                                      float* rd2, float* rd3, float* gi) {
-    for (int j = 0; j < NKP; ++j) {
-        const int jj = j - 3;
-        float v;
-        if (jj < 0) v = t[0] + (float)jj * (t[1] - t[0]);
-        else if (jj >= NK) v = t[NK - 1] + (float)(jj - NK + 1) * (t[NK - 1] - t[NK - 2]);
-        else v = t[jj];
-        kp[j] = v;
-    }
-    for (int j = 0; j < NKP; ++j) {
-        rd1[j] = (j + 1 < NKP) ? 1.0f / (kp[j + 1] - kp[j]) : 0.f;
-        rd2[j] = (j + 2 < NKP) ? 1.0f / (kp[j + 2] - kp[j]) : 0.f;
-        rd3[j] = (j + 3 < NKP) ? 1.0f / (kp[j + 3] - kp[j]) : 0.f;
-    }
-    gi[0] = t[0];
-    gi[1] = (float)(NK - 1) / (t[NK - 1] - t[0]);
-    gi[2] = t[NK - 1];
-    gi[3] = 0.f;
-}
-
-__device__ inline double branch_w(const fetode_kanlayer_t& P, int o, int i, int j) {
-    double w = (double)P.branch_weight[(size_t)o * P.in_features * P.num_basis + i * P.num_basis + j] *
-               (double)P.scale_logistic;
-    if (P.branch_scaler) w *= (double)P.branch_scaler[o];
-    return w;
-}
-
-// bp[j] = the four folded constants of branch basis (i, j)
-__device__ inline float4 branch_params(const fetode_kanlayer_t& P, int idx) {
-    const double l2e = 1.4426950408889634;
-    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (P.branch == FETODE_BRANCH_FERRO2D) {
-        const double k = P.bp[0][idx], Ec = P.bp[1][idx];
-        q.x = (float)((double)P.gate_slope * Ec * l2e);      // c1: cneg = 1/(1+2^(x*gl+c1))
-        q.y = (float)(2.0 * l2e * k);                          // k'
-        q.z = (float)(2.0 * l2e * k * Ec);                     // c2'
-        q.w = (float)(-2.0 * (1.0 - (double)P.alpha) * 2.0 * l2e * k * Ec);   // c3
-    } else if (P.branch == FETODE_BRANCH_LOGISTIC) {
-        const double a = P.bp[0][idx], b = P.bp[1][idx];
-        q.x = (float)(-a * l2e);
-        q.y = (float)(a * b * l2e);
-    }
-    return q;
-}
-
-// multiplier of r = 1/(1+2^t) in the folded branch contraction, and its constant companion
-__device__ inline void branch_fold(const fetode_kanlayer_t& P, int o, int i, int j, double& wr, double& wc) {
-    const double w = branch_w(P, o, i, j);
-    const int idx = i * P.num_basis + j;
-    if (P.branch == FETODE_BRANCH_FERRO2D) {
-        const double Ps = P.bp[2][idx], bias = P.bp[3][idx], coef = P.bp[4][idx];
-        wr = -2.0 * w * coef * Ps;
-        wc = w * coef * (Ps + bias);
-    } else {
-        wr = 2.0 * w;
-        wc = 0.0;
-    }
-}
-
 __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2, SNLayout L, float* img) {
     const int tid = threadIdx.x, nt = blockDim.x;
     const int D = L.D, H = L.H, NB = L.NB, S = L.S;

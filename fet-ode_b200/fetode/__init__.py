@@ -1,0 +1,16 @@
+"""fetode -- B200 (sm_100a) implementation of the KAN-FET neural-ODE right-hand side.
+
+Host-side mirror of the reference's module surface (sallywang147/FET-ODE @ 704a0df4):
+  fetode.efficientkan   LogisticBasis, KANLinear, KAN, KANFET      (efficient_kan/efficientkan.py)
+  fetode.ferro_class    *FerroelectricBasis                         (ferro_class.py)
+  fetode.odeint         odeint, integrate_euler/rk2/rk4, odeint_rk4 (torchdiffeq call sites + in-repo loops)
+All arithmetic runs in fetode/libfetode.so (C ABI: include/fetode.h); there is no CPU fallback.
+"""
+from . import _lib  # noqa: F401
+from .efficientkan import KAN, KANFET, KANLinear, LogisticBasis  # noqa: F401
+from .ferro_class import TwoDimensionFerroelectricBasis  # noqa: F401
+from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odeint,  # noqa: F401
+                     odeint_rk4)
+
+__all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "odeint",
+           "integrate_euler", "integrate_rk2", "integrate_rk4", "odeint_rk4", "as_rhs"]

@@ -1,0 +1,97 @@
+"""Drop-in for the reference's ``ferro_class`` module: the ferroelectric hysteresis neurons.
+
+Same class names, constructor arguments, parameter / buffer names and call semantics as
+ferro_class.py (reference checkout, commit 704a0df4); the arithmetic runs in libfetode.so
+(csrc/ferro.cu, and inside the fused KAN kernels for the 2-D variant).  Class names matter:
+``reset_stateful_ferro_buffers`` (train_ecg.py:371-378) matches modules by
+``__class__.__name__`` and then zeroes ``prev_x`` / fills ``branch_sign`` in place.
+
+State representation.  The reference keeps ``prev_x`` as the previous input *expanded* over the
+basis axes ([B,I,O,K] / [B,I,K]).  Here the state is the compact previous input ``[B, I]`` and
+the ``prev_x`` buffer is a stride-0 expanded view of it, so ``prev_x.zero_()`` from user code
+still resets the real state without ever materialising B*I*O*K floats in HBM.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+
+class _FerroState:
+    """Mixin: compact previous-input rows + the reference-shaped buffer views."""
+
+    def _init_state(self, shape_tail):
+        self._tail = tuple(shape_tail)
+        self.register_buffer("prev_x", torch.zeros(1, *self._tail))
+        self.register_buffer("branch_sign", torch.ones(1, *self._tail))
+        self._rows: Optional[torch.Tensor] = None       # [B, I]; None == reference's fresh [1,...] zeros
+
+    def _set_rows(self, rows: torch.Tensor) -> None:
+        """Record x as the new previous input (ferro_class.py:409 / :584-590)."""
+        self._rows = rows
+        view = rows
+        for _ in range(len(self._tail) - 1):
+            view = view.unsqueeze(-1)
+        self.prev_x = view.expand(rows.shape[0], *self._tail)
+
+    def _prev_rows(self, B: int, device) -> Optional[torch.Tensor]:
+        """Previous input to use for a batch of B rows, or None for 'all zeros'."""
+        r = self._rows
+        if r is None:
+            # fresh / reset buffers: [1,...] zeros broadcast against any B.  A user may also have
+            # written into the registered buffer directly (load_state_dict): honour a non-zero
+            # [1,...] buffer by broadcasting its first basis column.
+            return None
+        if r.shape[0] != B:
+            if r.shape[0] == 1:
+                return r.expand(B, -1).contiguous()
+            raise RuntimeError(
+                f"ferro state holds {r.shape[0]} rows but the input has {B}: call reset_state() "
+                "when the batch size changes (the reference fails on the same broadcast)")
+        return r if r.is_contiguous() else r.contiguous()
+
+    def reset_state(self):
+        """ferro_class.py:422-424 / :594-596."""
+        dev = self.prev_x.device
+        self._rows = None
+        self.prev_x = torch.zeros(1, *self._tail, device=dev)
+        self.branch_sign = torch.ones(1, *self._tail, device=dev)
+
+    def _apply(self, fn, *a, **k):                      # keep the compact rows with the module on .to()
+        out = super()._apply(fn, *a, **k)
+        if self._rows is not None:
+            self._set_rows(fn(self._rows))
+        return out
+
+
+class TwoDimensionFerroelectricBasis(_FerroState, nn.Module):
+    """ferro_class.py:526-596.  Used in the ``logistic_basis`` slot of KANLinear to form KANFET;
+    returns ``basis * coef`` of shape [B, in_dim, num_basis]."""
+
+    def __init__(self, in_dim, num_basis, use_noise=False, gate_slope=10.0, alpha=0.8, noise_std=0.05):
+        super().__init__()
+        self.in_dim, self.num_basis = in_dim, num_basis
+        self.use_noise, self.noise_std = use_noise, noise_std
+        self.gate_slope, self.alpha = gate_slope, alpha
+        self.k = nn.Parameter(torch.rand(in_dim, num_basis) * 2 + 0.5)
+        self.Ec = nn.Parameter(torch.rand(in_dim, num_basis) * 2 + 0.5)
+        self.Ps = nn.Parameter(torch.rand(in_dim, num_basis) * 1.5 + 0.5)
+        self.bias = nn.Parameter(torch.randn(in_dim, num_basis) * 0.1)
+        self.coef = nn.Parameter(torch.randn(in_dim, num_basis))
+        self._init_state((in_dim, num_basis))
+
+    def forward(self, x, return_activations=False):
+        ops.abort_if_tracing()
+        if x.dim() > 2:
+            x = x.view(x.shape[0], -1)
+        x2 = ops.f32c(x)
+        prev = self._prev_rows(x2.shape[0], x2.device)
+        out = ops.ferro_apply(self, ops.FERRO_TWO_D, x2, prev)
+        if self.use_noise:
+            out = out + (torch.randn_like(out) * self.noise_std).detach() * self.coef
+        self._set_rows(x2.detach())
+        return out

@@ -1,0 +1,349 @@
+"""Thin callers of the C ABI (include/fetode.h): pack caches, launches, autograd glue.
+
+Everything here is plumbing -- tensors are allocated with torch, the arithmetic happens in
+libfetode.so.  Nothing in this file computes a KAN / ferro value on the host or with torch ops.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import (BRANCH_FERRO2D, BRANCH_LOGISTIC, BRANCH_NONE, KanLayer, KanLayerGrads, SmallNet,
+                   check, f32c, lib, ptr, stream)
+
+_BP_NAMES = {
+    BRANCH_LOGISTIC: ("a", "b"),
+    BRANCH_FERRO2D: ("k", "Ec", "Ps", "bias", "coef"),
+}
+
+
+def _require_cuda(t: torch.Tensor, what: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"fetode: {what} lives on {t.device}; the KAN-FET path runs on CUDA only "
+            "(there is no CPU fallback) -- move the module and its inputs with .to('cuda')")
+
+
+class LayerView:
+    """The tensors of one KANLinear-shaped module in the order the C struct wants them.
+
+    ``module`` must expose the reference's attribute names (efficientkan.py:49-90 /
+    mnist_kuramoto_kan.py:40-78): grid, base_weight, spline_weight, [spline_scaler],
+    [logistic_basis.{a,b}|{k,Ec,Ps,bias,coef}], [logistic_weight], [logistic_scaler], [logistic_bias].
+    """
+
+    def __init__(self, module):
+        self.m = module
+
+    @property
+    def branch(self) -> int:
+        m = self.m
+        if not getattr(m, "enable_logistic_basis", getattr(m, "use_logistic_basis", False)):
+            return BRANCH_NONE
+        return BRANCH_FERRO2D if hasattr(m.logistic_basis, "Ec") else BRANCH_LOGISTIC
+
+    def tensors(self) -> List[Tuple[str, Optional[torch.Tensor]]]:
+        m = self.m
+        br = self.branch
+        out = [("grid", m.grid), ("base_weight", m.base_weight), ("spline_weight", m.spline_weight),
+               ("spline_scaler", getattr(m, "spline_scaler", None) if getattr(m, "enable_standalone_scale_spline", True) else None)]
+        if br == BRANCH_NONE:
+            out += [("branch_weight", None), ("branch_scaler", None), ("branch_bias", None)]
+            out += [(f"bp{i}", None) for i in range(5)]
+        else:
+            out.append(("branch_weight", m.logistic_weight))
+            out.append(("branch_scaler", getattr(m, "logistic_scaler", None)
+                        if getattr(m, "enable_standalone_scale_logistic", False) else None))
+            out.append(("branch_bias", getattr(m, "logistic_bias", None)))
+            names = _BP_NAMES[br]
+            for i in range(5):
+                out.append((f"bp{i}", getattr(m.logistic_basis, names[i]) if i < len(names) else None))
+        return out
+
+    def struct(self, tensors=None) -> KanLayer:
+        m = self.m
+        br = self.branch
+        ts = dict(tensors if tensors is not None else self.tensors())
+        s = KanLayer()
+        s.in_features, s.out_features = int(m.in_features), int(m.out_features)
+        s.grid_size, s.spline_order = int(m.grid_size), int(m.spline_order)
+        s.num_basis = 0 if br == BRANCH_NONE else int(m.num_basis)
+        s.branch = br
+        for name in ("grid", "base_weight", "spline_weight", "spline_scaler", "branch_weight",
+                     "branch_scaler", "branch_bias"):
+            t = ts[name]
+            if t is not None:
+                _require_cuda(t, name)
+            setattr(s, name, ptr(None if t is None else _keep(s, f32c(t.detach()))).value)
+        for i in range(5):
+            t = ts[f"bp{i}"]
+            s.bp[i] = ptr(None if t is None else _keep(s, f32c(t.detach()))).value
+        s.scale_logistic = float(getattr(m, "scale_logistic", 1.0))
+        lb = getattr(m, "logistic_basis", None)
+        s.gate_slope = float(getattr(lb, "gate_slope", 10.0))
+        s.alpha = float(getattr(lb, "alpha", 0.8))
+        return s
+
+    def key(self):
+        return tuple((n, None if t is None else (t.data_ptr(), t._version, tuple(t.shape)))
+                     for n, t in self.tensors())
+
+
+def _keep(owner, t: torch.Tensor) -> torch.Tensor:
+    """Pin a (possibly temporary) tensor's lifetime to the ctypes struct that points at it."""
+    refs = getattr(owner, "_refs", None)
+    if refs is None:
+        refs = []
+        owner._refs = refs
+    refs.append(t)
+    return t
+
+
+# --------------------------------------------------------------------------------------
+# any-width KANLinear
+# --------------------------------------------------------------------------------------
+class LayerPack:
+    """Device image of one layer's folded parameters; rebuilt when any parameter's version
+    counter or storage changes (i.e. after every optimiser step)."""
+
+    def __init__(self, module):
+        self.view = LayerView(module)
+        self._key = None
+        self.blob: Optional[torch.Tensor] = None
+        self.struct: Optional[KanLayer] = None
+
+    def get(self) -> Tuple[KanLayer, torch.Tensor]:
+        k = self.view.key()
+        if k != self._key:
+            s = self.view.struct()
+            n = lib().fetode_kanlinear_wcat_floats(C.byref(s))
+            if n < 0:
+                raise RuntimeError("fetode: KANLinear configuration not supported by the sm_100a kernels "
+                                   f"(in={s.in_features}, out={s.out_features}, grid={s.grid_size}, "
+                                   f"order={s.spline_order}, nb={s.num_basis})")
+            dev = self.view.m.base_weight.device
+            if self.blob is None or self.blob.numel() != n or self.blob.device != dev:
+                self.blob = torch.empty(n, dtype=torch.float32, device=dev)
+            check(lib().fetode_kanlinear_pack(C.byref(s), ptr(self.blob), stream()), "kanlinear_pack")
+            self.struct, self._key = s, k
+        return self.struct, self.blob
+
+
+def kanlinear_fwd(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor]) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """y = KANLinear(x2d); returns (y, new_prev) where new_prev (FERRO2D only) is x2d itself."""
+    _require_cuda(x2d, "input")
+    s, blob = pack.get()
+    B = x2d.shape[0]
+    y = torch.empty(B, s.out_features, dtype=torch.float32, device=x2d.device)
+    ferro = s.branch == BRANCH_FERRO2D
+    if B == 0:
+        return y, (x2d if ferro else None)
+    check(lib().fetode_kanlinear_fwd(C.byref(s), ptr(blob), ptr(x2d), ptr(prev) if ferro else None,
+                                      C.c_int(1 if prev is None else 0), None, ptr(y),
+                                      C.c_int64(B), stream()), "kanlinear_fwd")
+    return y, (x2d if ferro else None)
+
+
+class KanLinearFn(torch.autograd.Function):
+    """autograd node of one KANLinear call.  The hysteresis state ``prev`` is a constant of the
+    graph, as in the reference (ferro_class.py:553-554 detaches the snapshots)."""
+
+    @staticmethod
+    def forward(ctx, pack: LayerPack, prev, x2d, *params):
+        y, _ = kanlinear_fwd(pack, x2d, prev)
+        ctx.pack, ctx.prev = pack, prev
+        ctx.save_for_backward(x2d)
+        ctx.names = [n for n, t in pack.view.tensors() if t is not None and n != "grid"]
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (x2d,) = ctx.saved_tensors
+        pack = ctx.pack
+        s, blob = pack.get()
+        L = lib()
+        gy = f32c(gy)
+        B = x2d.shape[0]
+        need_x = ctx.needs_input_grad[2]
+        gx = torch.empty_like(x2d) if need_x else None
+        g = KanLayerGrads()
+        outs = []
+        tens = dict(pack.view.tensors())
+        for idx, name in enumerate(ctx.names):
+            t = tens[name]
+            gt = torch.zeros_like(t, dtype=torch.float32, memory_format=torch.contiguous_format) \
+                if ctx.needs_input_grad[3 + idx] else None
+            outs.append(gt)
+            if name.startswith("bp"):
+                g.bp[int(name[2:])] = ptr(gt).value
+            else:
+                setattr(g, name, ptr(gt).value)
+        n_ws = L.fetode_kanlinear_bwd_ws_floats(C.byref(s))
+        ws = torch.empty(max(int(n_ws), 1), dtype=torch.float32, device=x2d.device)
+        ferro = s.branch == BRANCH_FERRO2D
+        check(L.fetode_kanlinear_bwd(C.byref(s), ptr(blob), ptr(x2d), ptr(ctx.prev) if ferro else None,
+                                     C.c_int(1 if ctx.prev is None else 0), ptr(gy), ptr(gx), C.byref(g),
+                                     ptr(ws), C.c_int64(B), stream()), "kanlinear_bwd")
+        return (None, None, gx, *outs)
+
+
+def kanlinear_apply(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor]) -> torch.Tensor:
+    params = [t for n, t in pack.view.tensors() if t is not None and n != "grid"]
+    if torch.is_grad_enabled() and (x2d.requires_grad or any(p.requires_grad for p in params)):
+        return KanLinearFn.apply(pack, prev, x2d, *params)
+    return kanlinear_fwd(pack, x2d, prev)[0]
+
+
+# --------------------------------------------------------------------------------------
+# fused small-width network + Runge-Kutta loop
+# --------------------------------------------------------------------------------------
+class SmallNetPlan:
+    """Packed image + launch helpers for a two-layer KAN/KANFET whose widths fit the fused
+    kernel (fetode_smallnet_supported).  ``layers`` are KANLinear-shaped modules."""
+
+    def __init__(self, layers: Sequence):
+        self.views = [LayerView(m) for m in layers]
+        self.net = SmallNet()
+        self.net.n_layers = len(layers)
+        widths = [int(layers[0].in_features)] + [int(m.out_features) for m in layers]
+        for i, w in enumerate(widths[:3]):
+            self.net.widths[i] = w
+        self.net.grid_size = int(layers[0].grid_size)
+        self.net.spline_order = int(layers[0].spline_order)
+        br = self.views[0].branch
+        self.net.branch = br
+        self.net.num_basis = 0 if br == BRANCH_NONE else int(layers[0].num_basis)
+        self.D, self.H = widths[0], widths[1] if len(widths) > 1 else 0
+        self._key = None
+        self.packed: Optional[torch.Tensor] = None
+
+    @staticmethod
+    def supported(layers: Sequence) -> bool:
+        if len(layers) != 2:
+            return False
+        v = [LayerView(m) for m in layers]
+        if v[0].branch != v[1].branch:
+            return False
+        net = SmallNet()
+        net.n_layers = 2
+        net.widths[0], net.widths[1], net.widths[2] = (int(layers[0].in_features), int(layers[0].out_features),
+                                                      int(layers[1].out_features))
+        if int(layers[1].in_features) != net.widths[1]:
+            return False
+        net.grid_size, net.spline_order = int(layers[0].grid_size), int(layers[0].spline_order)
+        if (int(layers[1].grid_size), int(layers[1].spline_order)) != (net.grid_size, net.spline_order):
+            return False
+        net.branch = v[0].branch
+        net.num_basis = 0 if net.branch == BRANCH_NONE else int(layers[0].num_basis)
+        if net.branch != BRANCH_NONE and int(layers[1].num_basis) != net.num_basis:
+            return False
+        return lib().fetode_smallnet_supported(C.byref(net)) == 0
+
+    @property
+    def state_floats(self) -> int:
+        return int(lib().fetode_smallnet_state_floats(C.byref(self.net)))
+
+    def image(self) -> torch.Tensor:
+        k = tuple(v.key() for v in self.views)
+        if k != self._key:
+            structs = (KanLayer * 2)(*[v.struct() for v in self.views])
+            n = lib().fetode_smallnet_packed_floats(C.byref(self.net))
+            if n < 0:
+                raise RuntimeError("fetode: network not supported by the fused small-width kernel")
+            dev = self.views[0].m.base_weight.device
+            if self.packed is None or self.packed.numel() != n or self.packed.device != dev:
+                self.packed = torch.empty(n, dtype=torch.float32, device=dev)
+            check(lib().fetode_smallnet_pack(C.byref(self.net), structs, ptr(self.packed), stream()),
+                  "smallnet_pack")
+            self._structs = structs                      # keeps the f32c() temporaries alive until the
+            torch.cuda.current_stream().synchronize()    # pack kernel has consumed them
+            self._key = k
+        return self.packed
+
+    def rhs(self, y: torch.Tensor, state: Optional[torch.Tensor], state_is_zero: bool) -> torch.Tensor:
+        _require_cuda(y, "state vector")
+        img = self.image()
+        dy = torch.empty_like(y)
+        if y.shape[0] == 0:
+            return dy
+        check(lib().fetode_smallnet_rhs(C.byref(self.net), ptr(img), ptr(y), ptr(dy), ptr(state),
+                                        C.c_int(1 if state_is_zero else 0), C.c_int64(y.shape[0]), stream()),
+              "smallnet_rhs")
+        return dy
+
+    def rk_fwd(self, tableau: int, y0: torch.Tensor, dt: float, n_steps: int, *, state=None,
+               state_is_zero=True, traj: Optional[torch.Tensor] = None, dump_every: int = 1,
+               ckpt: Optional[torch.Tensor] = None, y_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        _require_cuda(y0, "initial state")
+        img = self.image()
+        if y_out is None:
+            y_out = torch.empty_like(y0)
+        if y0.shape[0] == 0:
+            return y_out
+        check(lib().fetode_smallnet_rk_fwd(C.byref(self.net), ptr(img), C.c_int(tableau), ptr(y0), ptr(y_out),
+                                           ptr(state), C.c_int(1 if state_is_zero else 0),
+                                           C.c_int64(y0.shape[0]), C.c_double(dt), C.c_int32(n_steps),
+                                           ptr(traj), C.c_int32(dump_every), ptr(ckpt), stream()),
+              "smallnet_rk_fwd")
+        return y_out
+
+
+# --------------------------------------------------------------------------------------
+# dry-run tracing used by odeint to recognise  func(t, y) == model(y)
+# --------------------------------------------------------------------------------------
+class TraceAbort(Exception):
+    """Raised by any fetode module that is evaluated during a dry run but cannot be fused."""
+
+
+class _Trace:
+    def __init__(self):
+        self.calls = []          # (module, input, sentinel)
+
+
+_ACTIVE_TRACE: Optional[_Trace] = None
+
+
+class tracing:
+    def __enter__(self):
+        global _ACTIVE_TRACE
+        self._saved = _ACTIVE_TRACE
+        _ACTIVE_TRACE = _Trace()
+        return _ACTIVE_TRACE
+
+    def __exit__(self, *exc):
+        global _ACTIVE_TRACE
+        _ACTIVE_TRACE = self._saved
+        return False
+
+
+def active_trace() -> Optional[_Trace]:
+    return _ACTIVE_TRACE
+
+
+def abort_if_tracing() -> None:
+    if _ACTIVE_TRACE is not None:
+        raise TraceAbort()
+
+
+# --------------------------------------------------------------------------------------
+# Runge-Kutta stage algebra
+# --------------------------------------------------------------------------------------
+def rk_combine(y: Optional[torch.Tensor], ks: Sequence[torch.Tensor], coefs: Sequence[float]) -> torch.Tensor:
+    """out = y + sum_i coefs[i] * ks[i] in one launch (csrc/rkstage.cu)."""
+    ref = y if y is not None else ks[0]
+    _require_cuda(ref, "stage tensor")
+    ks = [f32c(k.detach()) for k in ks]
+    yc = None if y is None else f32c(y.detach())
+    out = torch.empty_like(ref, dtype=torch.float32, memory_format=torch.contiguous_format)
+    n = len(ks)
+    karr = (C.c_void_p * max(n, 1))(*[k.data_ptr() for k in ks])
+    carr = (C.c_float * max(n, 1))(*[float(c) for c in coefs])
+    check(lib().fetode_rk_combine(ptr(yc), karr, carr, C.c_int32(n), ptr(out), C.c_int64(out.numel()), stream()),
+          "rk_combine")
+    return out
+
+
+FERRO_FULL, FERRO_TWO_D, FERRO_HARDGATE = _lib.FERRO_FULL, _lib.FERRO_TWO_D, _lib.FERRO_HARDGATE

@@ -91,7 +91,8 @@ typedef struct fetode_kanlayer_grads {
  * (i, [silu | spline s | branch j]); it is rebuilt by fetode_kanlinear_pack whenever the
  * parameters change.  `prev` is the hysteresis state of the FERRO2D branch: the previous input
  * [B, I]; with prev_is_zero != 0 it is taken as all-zero and not read (first call after
- * reset_state, ferro_class.py:544,594-596).  prev_out (may alias prev, may be NULL) receives x.
+ * reset_state, ferro_class.py:544,594-596).  prev_out (NULL, or a buffer that does NOT alias prev)
+ * receives x, the next call's prev (ferro_class.py:584-590).
  */
 FETODE_API int64_t fetode_kanlinear_wcat_floats(const fetode_kanlayer_t* L);
 FETODE_API int fetode_kanlinear_pack(const fetode_kanlayer_t* L, float* wcat, void* stream);
@@ -148,6 +149,19 @@ FETODE_API int fetode_smallnet_rk_fwd(const fetode_smallnet_t* net, const float*
 /* one RHS evaluation y -> f(y) (KAN.forward), same state rules */
 FETODE_API int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
                         float* dy, float* state, int state_is_zero, int64_t B, void* stream);
+
+/* ---- Runge-Kutta stage algebra for right-hand sides that are not fused --------------------
+ * out = y + sum_{i<ns} coef[i] * ks[i]   (y may be NULL == 0; ks / coef are HOST arrays, ns <= 8).
+ * Replaces the axpy chains of integrate_euler/rk2/rk4 train_ecg_kan_fet_nn_ode.py:670-705,
+ * odeint_rk4 train_kan_fet_ett.py:51-83 and of torchdiffeq's fixed-grid / dopri5 steps.
+ */
+#define FETODE_RK_MAX_TERMS 8
+FETODE_API int fetode_rk_combine(const float* y, const float* const* ks, const float* coef, int32_t ns,
+                      float* out, int64_t n, void* stream);
+/* *sumsq (device double) = sum_i (err_i / (atol + rtol * max(|y0_i|, |y1_i|)))^2 : the numerator of
+ * torchdiffeq's dopri5 accept/reject RMS norm (one global norm over the whole state tensor). */
+FETODE_API int fetode_rk_error_sumsq(const float* err, const float* y0, const float* y1, float atol, float rtol,
+                          int64_t n, double* sumsq, void* stream);
 
 /* ---- stand-alone ferroelectric neurons ------------------------------------------------
  * FULL    : FerroelectricBasis.forward ferro_class.py:368-420 (update_branch=0) and
