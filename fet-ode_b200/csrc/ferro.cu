@@ -1,0 +1,368 @@
+// ferro.cu -- stand-alone ferroelectric hysteresis neurons (sm_100a), forward and backward.
+//
+// Reference arithmetic being replaced (file:line relative to the reference checkout):
+//   FULL     FerroelectricBasis.forward        ferro_class.py:368-420  (branch_sign never written => br == 1)
+//            NoisyFerroelectricBasis.forward   ferro_class.py:466-519  (noise_std = 0; branch_sign <- target_sign)
+//   TWO_D    TwoDimensionFerroelectricBasis    ferro_class.py:547-592
+//   HARDGATE hysteretic LogisticBasis.forward  train_ecg_kan_fet_nn_ode.py:102-134 (+ KANFeatureMixer sigmoid :419)
+//
+// The reference materialises a [B,I,O,K] tensor per elementary op (~30 launches); here one thread owns
+// one (row, output) pair and reduces over (input, basis) in registers, the previous-input state is the
+// compact [B,I] row block, and the optional branch_sign state of the Noisy variant is the only
+// [B,I,O,K] array that touches HBM (one read + one write per call).
+//
+// The hard gate  (sigmoid(5 (x - prev)) > 0.5)  is evaluated with IEEE expf / add / divide so that the
+// branch taken is bit-identical to torch's CPU result (the threshold is a rounding artefact of
+// 1/(1+exp(-z)): true from z >= ~8.94e-8, false at z == 0); everything else uses MUFU ex2 / rcp.
+#include "common.cuh"
+
+namespace fetode {
+
+__device__ __forceinline__ float sigm(float z) { return rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * z)); }
+__device__ __forceinline__ float tanh_fast(float z) {
+    // 1 - 2/(1+e^{2z}); saturates cleanly for |z| large
+    return 1.0f - 2.0f * rcp_approx(1.0f + ex2_approx(fminf(2.0f * FETODE_LOG2E * z, 80.0f)));
+}
+
+struct SoftBranch {          // forward values the backward needs
+    float up, cp, cn, su, sl, tgt, m, T;
+};
+
+// ferro_class.py:384-408.  br_one: branch_sign == 1 for every element (FerroelectricBasis, TwoDimension...)
+__device__ __forceinline__ SoftBranch soft_branch(float x, float up, float k, float Ec, float br, float g,
+                                                  float alpha) {
+    SoftBranch s;
+    s.up = up;
+    s.cp = sigm(g * (x - Ec));
+    s.cn = sigm(g * (-x - Ec));
+    s.su = up * s.cp;
+    s.sl = (1.0f - up) * s.cn;
+    s.tgt = s.su - s.sl + (1.0f - s.su - s.sl) * br;
+    s.m = alpha * br + (1.0f - alpha) * s.tgt;
+    s.T = tanh_fast(k * fmaf(Ec, s.m, x));
+    return s;
+}
+
+// d(momentum)/dx and d(momentum)/dEc   (prev and br are constants of the graph, ferro_class.py:381-382)
+__device__ __forceinline__ void soft_branch_grad(const SoftBranch& s, float br, float g, float alpha,
+                                                 float& dm_dx, float& dm_dEc) {
+    const float dup = g * s.up * (1.0f - s.up);
+    const float dcp = g * s.cp * (1.0f - s.cp);          // d cp / dx  = - d cp / dEc
+    const float dcn = g * s.cn * (1.0f - s.cn);          // d cn / dx  = -dcn ; d cn / dEc = -dcn
+    const float dsu_dx = dup * s.cp + s.up * dcp;
+    const float dsu_dEc = -s.up * dcp;
+    const float dsl_dx = -dup * s.cn - (1.0f - s.up) * dcn;
+    const float dsl_dEc = -(1.0f - s.up) * dcn;
+    const float a = (1.0f - alpha) * (1.0f - br), b = (1.0f - alpha) * (-1.0f - br);
+    dm_dx = a * dsu_dx + b * dsl_dx;
+    dm_dEc = a * dsu_dEc + b * dsl_dEc;
+}
+
+// ------------------------------------------------------------------------------------------
+// FULL: params [I,O,K], out [B,O]
+// ------------------------------------------------------------------------------------------
+constexpr int FF_THREADS = 128;     // 4 warps: lanes = 32 consecutive outputs, warps split the inputs
+
+struct FerroArgs {
+    const float *k, *Ec, *Ps, *bias, *coef;
+    const float *x, *prev, *br, *gout;
+    float *out, *basis_out, *br_out, *gx;
+    float *gk, *gEc, *gPs, *gbias, *gcoef;
+    unsigned char* gate_out;
+    long long B;
+    int I, O, K, prev_is_zero, apply_sigmoid;
+    float g, alpha;
+};
+
+template <bool HAS_BR>
+__global__ void __launch_bounds__(FF_THREADS) ferro_full_fwd_kernel(const FerroArgs a) {
+    extern __shared__ float ff_sm[];
+    float* xs = ff_sm;                 // [I] x row
+    float* ups = ff_sm + a.I;          // [I] is_moving_up
+    __shared__ float part[4][32];
+    const long long b = blockIdx.x;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int o = blockIdx.y * 32 + lane;
+    const int I = a.I, O = a.O, K = a.K;
+    for (int i = threadIdx.x; i < I; i += FF_THREADS) {
+        const float x = a.x[b * I + i];
+        const float p = a.prev_is_zero ? 0.f : a.prev[b * I + i];
+        xs[i] = x;
+        ups[i] = sigm(a.g * (x - p));
+    }
+    __syncthreads();
+    float acc = 0.f;
+    if (o < O) {
+        for (int i = w; i < I; i += 4) {
+            const float x = xs[i], up = ups[i];
+            const size_t base = ((size_t)i * O + o) * K;
+            const size_t sbase = (((size_t)b * I + i) * O + o) * K;
+            for (int j = 0; j < K; ++j) {
+                const float br = HAS_BR ? a.br[sbase + j] : 1.0f;
+                const SoftBranch s = soft_branch(x, up, a.k[base + j], a.Ec[base + j], br, a.g, a.alpha);
+                const float P = fmaf(a.Ps[base + j], s.T, a.bias[base + j]);
+                acc = fmaf(a.coef[base + j], P, acc);
+                if (a.basis_out) a.basis_out[sbase + j] = P;
+                if (HAS_BR && a.br_out) a.br_out[sbase + j] = s.tgt;          // ferro_class.py:512-514
+            }
+        }
+    }
+    part[w][lane] = acc;
+    __syncthreads();
+    if (w == 0 && o < O) a.out[b * O + o] = part[0][lane] + part[1][lane] + part[2][lane] + part[3][lane];
+}
+
+// backward: one CTA per (input i, 32 outputs, tile of FB_BT rows); warps split the basis index j.
+constexpr int FB_BT = 64;
+
+template <bool HAS_BR>
+__global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroArgs a) {
+    __shared__ float xs[FB_BT], ups[FB_BT], dxs[FB_BT];
+    const int i = blockIdx.x;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int o = blockIdx.y * 32 + lane;
+    const long long b0 = (long long)blockIdx.z * FB_BT;
+    const int nb = (int)min((long long)FB_BT, a.B - b0);
+    const int I = a.I, O = a.O, K = a.K;
+    for (int t = threadIdx.x; t < FB_BT; t += FF_THREADS) {
+        float x = 0.f, p = 0.f;
+        if (t < nb) { x = a.x[(b0 + t) * I + i]; p = a.prev_is_zero ? 0.f : a.prev[(b0 + t) * I + i]; }
+        xs[t] = x;
+        ups[t] = sigm(a.g * (x - p));
+        dxs[t] = 0.f;
+    }
+    __syncthreads();
+    for (int j = w; j < K; j += 4) {
+        float k = 0.f, Ec = 0.f, Ps = 0.f, bias = 0.f, coef = 0.f;
+        const size_t base = ((size_t)i * O + o) * K + j;
+        if (o < O) { k = a.k[base]; Ec = a.Ec[base]; Ps = a.Ps[base]; bias = a.bias[base]; coef = a.coef[base]; }
+        float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f;
+        for (int t = 0; t < nb; ++t) {
+            float dx = 0.f;
+            if (o < O) {
+                const float x = xs[t];
+                const float br = HAS_BR ? a.br[(((size_t)(b0 + t) * I + i) * O + o) * K + j] : 1.0f;
+                const SoftBranch s = soft_branch(x, ups[t], k, Ec, br, a.g, a.alpha);
+                float dm_dx, dm_dEc;
+                soft_branch_grad(s, br, a.g, a.alpha, dm_dx, dm_dEc);
+                const float go = a.gout[(b0 + t) * O + o];
+                ac = fmaf(go, fmaf(Ps, s.T, bias), ac);
+                const float gP = go * coef;
+                aPs = fmaf(gP, s.T, aPs);
+                ab += gP;
+                const float dz = gP * Ps * (1.0f - s.T * s.T);
+                ak = fmaf(dz, fmaf(Ec, s.m, x), ak);
+                aEc = fmaf(dz * k, fmaf(Ec, dm_dEc, s.m), aEc);
+                dx = dz * k * fmaf(Ec, dm_dx, 1.0f);
+            }
+            if (a.gx) {
+                dx = warp_sum(dx);
+                if (lane == 0) atomicAdd(&dxs[t], dx);
+            }
+        }
+        if (o < O) {
+            if (a.gk) atomicAdd(a.gk + base, ak);
+            if (a.gEc) atomicAdd(a.gEc + base, aEc);
+            if (a.gPs) atomicAdd(a.gPs + base, aPs);
+            if (a.gbias) atomicAdd(a.gbias + base, ab);
+            if (a.gcoef) atomicAdd(a.gcoef + base, ac);
+        }
+    }
+    __syncthreads();
+    if (a.gx)
+        for (int t = threadIdx.x; t < nb; t += FF_THREADS) atomicAdd(a.gx + (b0 + t) * I + i, dxs[t]);
+}
+
+// ------------------------------------------------------------------------------------------
+// TWO_D and HARDGATE: params [I,K], out [B,I,K] (element-wise over the basis axis)
+// ------------------------------------------------------------------------------------------
+// IEEE evaluation of torch's CPU  sigmoid(z) > 0.5  (see file header)
+__device__ __forceinline__ bool hard_gate(float z) {
+    const float e = expf(-z);
+    const float s = __fadd_rn(1.0f, e);
+    return __fdiv_rn(1.0f, s) > 0.5f;
+}
+
+template <int VARIANT>
+__global__ void __launch_bounds__(256) ferro_elem_fwd_kernel(const FerroArgs a) {
+    const long long n = a.B * a.I * a.K;
+    const int IK = a.I * a.K;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+        const long long b = e / IK;
+        const int p = (int)(e % IK), i = p / a.K;
+        const float x = a.x[b * a.I + i];
+        float out;
+        if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
+            const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
+            const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), a.k[p], a.Ec[p], 1.0f, a.g, a.alpha);
+            const float P = fmaf(a.Ps[p], s.T, a.bias[p]);
+            if (a.basis_out) a.basis_out[e] = P;
+            out = a.coef[p] * P;
+        } else {
+            const float pv = a.prev_is_zero ? 0.f : a.prev[i];                  // ONE row shared by the batch :93
+            const bool up = hard_gate(a.g * (x - pv));                          // :122-123
+            const float Ec = a.Ec[p], Ps = a.Ps[p];
+            const float s = sigm(a.k[p] * (up ? x - Ec : x + Ec));              // :116-117
+            out = fmaf(2.0f * Ps, s, -Ps) + a.bias[p];                          // :126
+            if (a.gate_out) a.gate_out[e] = up ? 1 : 0;
+            if (a.basis_out) a.basis_out[e] = out;
+            if (a.apply_sigmoid) out = sigm(out);                               // KANFeatureMixer :419
+        }
+        a.out[e] = out;
+    }
+}
+
+// one thread per parameter (i,j), loop over a tile of rows; gx via atomics (K-way contention)
+constexpr int FE_BT = 128;
+
+template <int VARIANT>
+__global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) {
+    const int IK = a.I * a.K;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= IK) return;
+    const int i = p / a.K;
+    const long long b0 = (long long)blockIdx.y * FE_BT;
+    const int nb = (int)min((long long)FE_BT, a.B - b0);
+    const float k = a.k[p], Ec = a.Ec[p], Ps = a.Ps[p], bias = a.bias[p];
+    const float coef = VARIANT == FETODE_FERRO_TWO_D ? a.coef[p] : 1.0f;
+    float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f;
+    for (int t = 0; t < nb; ++t) {
+        const long long b = b0 + t;
+        const float x = a.x[b * a.I + i];
+        float go = a.gout[b * IK + p];
+        float dx;
+        if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
+            const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
+            const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), k, Ec, 1.0f, a.g, a.alpha);
+            float dm_dx, dm_dEc;
+            soft_branch_grad(s, 1.0f, a.g, a.alpha, dm_dx, dm_dEc);
+            ac = fmaf(go, fmaf(Ps, s.T, bias), ac);
+            const float gP = go * coef;
+            aPs = fmaf(gP, s.T, aPs);
+            ab += gP;
+            const float dz = gP * Ps * (1.0f - s.T * s.T);
+            ak = fmaf(dz, fmaf(Ec, s.m, x), ak);
+            aEc = fmaf(dz * k, fmaf(Ec, dm_dEc, s.m), aEc);
+            dx = dz * k * fmaf(Ec, dm_dx, 1.0f);
+        } else {
+            const float pv = a.prev_is_zero ? 0.f : a.prev[i];
+            const bool up = hard_gate(a.g * (x - pv));
+            const float arg = up ? x - Ec : x + Ec;
+            const float s = sigm(k * arg);
+            if (a.apply_sigmoid) {
+                const float y = sigm(fmaf(2.0f * Ps, s, -Ps) + bias);
+                go *= y * (1.0f - y);
+            }
+            aPs = fmaf(go, 2.0f * s - 1.0f, aPs);
+            ab += go;
+            const float dz = go * 2.0f * Ps * s * (1.0f - s);
+            ak = fmaf(dz, arg, ak);
+            aEc += up ? -dz * k : dz * k;
+            dx = dz * k;
+        }
+        if (a.gx) atomicAdd(a.gx + b * a.I + i, dx);
+    }
+    if (a.gk) atomicAdd(a.gk + p, ak);
+    if (a.gEc) atomicAdd(a.gEc + p, aEc);
+    if (a.gPs) atomicAdd(a.gPs + p, aPs);
+    if (a.gbias) atomicAdd(a.gbias + p, ab);
+    if (VARIANT == FETODE_FERRO_TWO_D && a.gcoef) atomicAdd(a.gcoef + p, ac);
+}
+
+// prev_out for HARDGATE: the LAST batch row (train_ecg_kan_fet_nn_ode.py:131-132)
+__global__ void copy_row_kernel(const float* src, float* dst, int n) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) dst[t] = src[t];
+}
+
+static int ferro_check(const fetode_ferro_t* F) {
+    if (!F) return FETODE_EINVAL;
+    if (F->in_dim < 1 || F->num_basis < 1 || F->out_dim < 1) return FETODE_EINVAL;
+    if (!(F->k && F->Ec && F->Ps && F->bias)) return FETODE_EINVAL;
+    if (F->variant != FETODE_FERRO_HARDGATE && !F->coef) return FETODE_EINVAL;
+    if (F->variant < FETODE_FERRO_FULL || F->variant > FETODE_FERRO_HARDGATE) return FETODE_EINVAL;
+    if (F->variant != FETODE_FERRO_FULL && F->out_dim != 1) return FETODE_ESHAPE;
+    return FETODE_OK;
+}
+
+static FerroArgs ferro_args(const fetode_ferro_t* F, int64_t B) {
+    FerroArgs a{};
+    a.k = F->k; a.Ec = F->Ec; a.Ps = F->Ps; a.bias = F->bias; a.coef = F->coef;
+    a.B = B; a.I = F->in_dim; a.O = F->out_dim; a.K = F->num_basis;
+    a.g = F->gate_slope; a.alpha = F->alpha; a.apply_sigmoid = F->apply_sigmoid;
+    return a;
+}
+
+}  // namespace fetode
+
+using namespace fetode;
+
+extern "C" int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
+                                const float* br, float* out, float* basis_out, float* br_out,
+                                uint8_t* gate_out, float* prev_out, int64_t B, void* stream) {
+    int rc = ferro_check(F);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(x && out && B >= 0);
+    if (B == 0) return FETODE_OK;
+    if (!prev_is_zero) FETODE_CHECK_ARG(prev != nullptr);
+    cudaStream_t st = (cudaStream_t)stream;
+    FerroArgs a = ferro_args(F, B);
+    a.x = x; a.prev = prev; a.prev_is_zero = prev_is_zero; a.br = br; a.out = out; a.basis_out = basis_out;
+    a.br_out = br_out; a.gate_out = gate_out;
+    if (F->variant == FETODE_FERRO_FULL) {
+        FETODE_CHECK_SUPPORTED(B <= 0x7fffffffLL);
+        const dim3 grid((unsigned)B, (unsigned)((a.O + 31) / 32));
+        const size_t smem = (size_t)2 * a.I * sizeof(float);
+        FETODE_CHECK_SUPPORTED(smem <= 48 * 1024);
+        if (br) ferro_full_fwd_kernel<true><<<grid, FF_THREADS, smem, st>>>(a);
+        else ferro_full_fwd_kernel<false><<<grid, FF_THREADS, smem, st>>>(a);
+    } else {
+        const long long n = B * a.I * a.K;
+        const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
+        if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_fwd_kernel<FETODE_FERRO_TWO_D><<<blocks, 256, 0, st>>>(a);
+        else ferro_elem_fwd_kernel<FETODE_FERRO_HARDGATE><<<blocks, 256, 0, st>>>(a);
+    }
+    rc = FETODE_LAUNCH_RC();
+    if (rc) return rc;
+    if (prev_out) {
+        if (F->variant == FETODE_FERRO_HARDGATE) {
+            copy_row_kernel<<<(a.I + 127) / 128, 128, 0, st>>>(x + (B - 1) * a.I, prev_out, a.I);
+            rc = FETODE_LAUNCH_RC();
+        } else if (prev_out != x) {
+            rc = (int)cudaMemcpyAsync(prev_out, x, (size_t)B * a.I * sizeof(float), cudaMemcpyDeviceToDevice, st);
+        }
+    }
+    return rc;
+}
+
+extern "C" int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
+                                const float* br, const float* gout, float* gx,
+                                const fetode_ferro_grads_t* grads, int64_t B, void* stream) {
+    int rc = ferro_check(F);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(x && gout && B >= 0);
+    if (!prev_is_zero) FETODE_CHECK_ARG(prev != nullptr);
+    cudaStream_t st = (cudaStream_t)stream;
+    FerroArgs a = ferro_args(F, B);
+    a.x = x; a.prev = prev; a.prev_is_zero = prev_is_zero; a.br = br; a.gout = gout; a.gx = gx;
+    if (grads) { a.gk = grads->k; a.gEc = grads->Ec; a.gPs = grads->Ps; a.gbias = grads->bias; a.gcoef = grads->coef; }
+    if (gx) {
+        cudaError_t e = cudaMemsetAsync(gx, 0, (size_t)B * a.I * sizeof(float), st);
+        if (e) return (int)e;
+    }
+    if (B == 0) return FETODE_OK;
+    if (F->variant == FETODE_FERRO_FULL) {
+        const long long bz = (B + FB_BT - 1) / FB_BT;
+        FETODE_CHECK_SUPPORTED(bz <= 65535 && (a.O + 31) / 32 <= 65535);
+        const dim3 grid((unsigned)a.I, (unsigned)((a.O + 31) / 32), (unsigned)bz);
+        if (br) ferro_full_bwd_kernel<true><<<grid, FF_THREADS, 0, st>>>(a);
+        else ferro_full_bwd_kernel<false><<<grid, FF_THREADS, 0, st>>>(a);
+    } else {
+        const long long by = (B + FE_BT - 1) / FE_BT;
+        FETODE_CHECK_SUPPORTED(by <= 65535);
+        const dim3 grid((unsigned)((a.I * a.K + 127) / 128), (unsigned)by);
+        if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_bwd_kernel<FETODE_FERRO_TWO_D><<<grid, 128, 0, st>>>(a);
+        else ferro_elem_bwd_kernel<FETODE_FERRO_HARDGATE><<<grid, 128, 0, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}

@@ -189,6 +189,7 @@ typedef struct fetode_ferro_grads { float *k, *Ec, *Ps, *bias, *coef; } fetode_f
 FETODE_API int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
                      const float* br, float* out, float* basis_out /* or NULL */,
                      float* br_out /* or NULL */, uint8_t* gate_out /* or NULL */,
+                     float* prev_out /* or NULL: FULL/TWO_D [B,I] <- x ; HARDGATE [I] <- last row of x */,
                      int64_t B, void* stream);
 FETODE_API int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
                      const float* br, const float* gout, float* gx /* [B,I] overwritten, or NULL */,
