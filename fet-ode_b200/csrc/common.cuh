@@ -103,6 +103,48 @@ __device__ __forceinline__ void bspline3_local(float x, const float* kp, const f
     v[3] = left1 * t;
 }
 
+// Same evaluation plus the derivatives d/dx of the four values:
+//   N'^3_j = 3 (N^2_j / (t_{j+3}-t_j) - N^2_{j+1} / (t_{j+4}-t_{j+1}))   
+__device__ __forceinline__ void bspline3_local_d(float x, const float* kp, const float* rd1, const float* rd2,
+                                                 const float* rd3, int mp, float (&v)[4], float (&dv)[4]) {
+    const float left1 = x - kp[mp], right1 = kp[mp + 1] - x;
+    const float left2 = x - kp[mp - 1], right2 = kp[mp + 2] - x;
+    const float left3 = x - kp[mp - 2], right3 = kp[mp + 3] - x;
+    float t = rd1[mp];
+    const float a0 = right1 * t, a1 = left1 * t;
+    t = a0 * rd2[mp - 1];
+    const float b0 = right1 * t;
+    float saved = left2 * t;
+    t = a1 * rd2[mp];
+    const float b1 = saved + right2 * t;
+    const float b2 = left1 * t;
+    const float t0 = b0 * rd3[mp - 2], t1 = b1 * rd3[mp - 1], t2 = b2 * rd3[mp];
+    v[0] = right1 * t0;
+    v[1] = left3 * t0 + right2 * t1;
+    v[2] = left2 * t1 + right3 * t2;
+    v[3] = left1 * t2;
+    dv[0] = -3.0f * t0;
+    dv[1] = 3.0f * (t0 - t1);
+    dv[2] = 3.0f * (t1 - t2);
+    dv[3] = 3.0f * t2;
+}
+
+// Column sums across a warp: every lane holds 32 values v[0..31]; returns in lane l the sum over all lanes of
+// v[l].  31 shuffles for 32 columns (recursive halving) instead of 5 per column.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool hi = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = hi ? v[i] : v[i + off];
+            const float keep = hi ? v[i + off] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
 // Interval search: largest m in [0, NK-2] with t_m <= x, for x known to lie in [t_0, t_{NK-1}).
 // gi = {t_0, (NK-1)/(t_last - t_0), t_last, -}; the guess is exact for the default uniform
 // grid and the two loops repair it for the non-uniform grids update_grid() produces

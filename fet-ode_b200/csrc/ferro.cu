@@ -192,7 +192,10 @@ __global__ void __launch_bounds__(256) ferro_elem_fwd_kernel(const FerroArgs a) 
         const int p = (int)(e % IK), i = p / a.K;
         const float x = a.x[b * a.I + i];
         float out;
-        if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
+        if constexpr (VARIANT == FETODE_FERRO_LOGISTIC) {
+            out = 2.0f * sigm(a.k[p] * (x - a.Ec[p]));                          // efficientkan.py:24
+            if (a.basis_out) a.basis_out[e] = out;
+        } else if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
             const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
             const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), a.k[p], a.Ec[p], 1.0f, a.g, a.alpha);
             const float P = fmaf(a.Ps[p], s.T, a.bias[p]);
@@ -223,7 +226,8 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
     const int i = p / a.K;
     const long long b0 = (long long)blockIdx.y * FE_BT;
     const int nb = (int)min((long long)FE_BT, a.B - b0);
-    const float k = a.k[p], Ec = a.Ec[p], Ps = a.Ps[p], bias = a.bias[p];
+    const float k = a.k[p], Ec = a.Ec[p];
+    const float Ps = VARIANT == FETODE_FERRO_LOGISTIC ? 0.f : a.Ps[p], bias = VARIANT == FETODE_FERRO_LOGISTIC ? 0.f : a.bias[p];
     const float coef = VARIANT == FETODE_FERRO_TWO_D ? a.coef[p] : 1.0f;
     float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f;
     for (int t = 0; t < nb; ++t) {
@@ -231,7 +235,13 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
         const float x = a.x[b * a.I + i];
         float go = a.gout[b * IK + p];
         float dx;
-        if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
+        if constexpr (VARIANT == FETODE_FERRO_LOGISTIC) {
+            const float s = sigm(k * (x - Ec));
+            const float dz = go * 2.0f * s * (1.0f - s);                        // phi (1 - phi/2)
+            ak = fmaf(dz, x - Ec, ak);
+            aEc = fmaf(-dz, k, aEc);
+            dx = dz * k;
+        } else if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
             const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
             const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), k, Ec, 1.0f, a.g, a.alpha);
             float dm_dx, dm_dEc;
@@ -264,8 +274,8 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
     }
     if (a.gk) atomicAdd(a.gk + p, ak);
     if (a.gEc) atomicAdd(a.gEc + p, aEc);
-    if (a.gPs) atomicAdd(a.gPs + p, aPs);
-    if (a.gbias) atomicAdd(a.gbias + p, ab);
+    if (VARIANT != FETODE_FERRO_LOGISTIC && a.gPs) atomicAdd(a.gPs + p, aPs);
+    if (VARIANT != FETODE_FERRO_LOGISTIC && a.gbias) atomicAdd(a.gbias + p, ab);
     if (VARIANT == FETODE_FERRO_TWO_D && a.gcoef) atomicAdd(a.gcoef + p, ac);
 }
 
@@ -278,9 +288,10 @@ __global__ void copy_row_kernel(const float* src, float* dst, int n) {
 static int ferro_check(const fetode_ferro_t* F) {
     if (!F) return FETODE_EINVAL;
     if (F->in_dim < 1 || F->num_basis < 1 || F->out_dim < 1) return FETODE_EINVAL;
-    if (!(F->k && F->Ec && F->Ps && F->bias)) return FETODE_EINVAL;
-    if (F->variant != FETODE_FERRO_HARDGATE && !F->coef) return FETODE_EINVAL;
-    if (F->variant < FETODE_FERRO_FULL || F->variant > FETODE_FERRO_HARDGATE) return FETODE_EINVAL;
+    if (F->variant < FETODE_FERRO_FULL || F->variant > FETODE_FERRO_LOGISTIC) return FETODE_EINVAL;
+    if (!(F->k && F->Ec)) return FETODE_EINVAL;
+    if (F->variant != FETODE_FERRO_LOGISTIC && !(F->Ps && F->bias)) return FETODE_EINVAL;
+    if (F->variant <= FETODE_FERRO_TWO_D && !F->coef) return FETODE_EINVAL;
     if (F->variant != FETODE_FERRO_FULL && F->out_dim != 1) return FETODE_ESHAPE;
     return FETODE_OK;
 }
@@ -320,6 +331,7 @@ extern "C" int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const f
         const long long n = B * a.I * a.K;
         const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
         if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_fwd_kernel<FETODE_FERRO_TWO_D><<<blocks, 256, 0, st>>>(a);
+        else if (F->variant == FETODE_FERRO_LOGISTIC) ferro_elem_fwd_kernel<FETODE_FERRO_LOGISTIC><<<blocks, 256, 0, st>>>(a);
         else ferro_elem_fwd_kernel<FETODE_FERRO_HARDGATE><<<blocks, 256, 0, st>>>(a);
     }
     rc = FETODE_LAUNCH_RC();
@@ -328,7 +340,7 @@ extern "C" int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const f
         if (F->variant == FETODE_FERRO_HARDGATE) {
             copy_row_kernel<<<(a.I + 127) / 128, 128, 0, st>>>(x + (B - 1) * a.I, prev_out, a.I);
             rc = FETODE_LAUNCH_RC();
-        } else if (prev_out != x) {
+        } else if (prev_out != x && F->variant != FETODE_FERRO_LOGISTIC) {
             rc = (int)cudaMemcpyAsync(prev_out, x, (size_t)B * a.I * sizeof(float), cudaMemcpyDeviceToDevice, st);
         }
     }
@@ -362,6 +374,7 @@ extern "C" int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const f
         FETODE_CHECK_SUPPORTED(by <= 65535);
         const dim3 grid((unsigned)((a.I * a.K + 127) / 128), (unsigned)by);
         if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_bwd_kernel<FETODE_FERRO_TWO_D><<<grid, 128, 0, st>>>(a);
+        else if (F->variant == FETODE_FERRO_LOGISTIC) ferro_elem_bwd_kernel<FETODE_FERRO_LOGISTIC><<<grid, 128, 0, st>>>(a);
         else ferro_elem_bwd_kernel<FETODE_FERRO_HARDGATE><<<grid, 128, 0, st>>>(a);
     }
     return FETODE_LAUNCH_RC();

@@ -245,3 +245,61 @@ extern "C" int fetode_kanlinear_fwd(const fetode_kanlayer_t* P, const float* wca
     }
     return FETODE_EUNSUPPORTED;
 }
+
+// ------------------------------------------------------------------------------------------
+// b_splines alone (efficientkan.py:117-131): out[b,i,:] = the G+3 cubic basis values.  Works from
+// the raw knot table (no pack): interval by scan, local de Boor with true divisions.
+// ------------------------------------------------------------------------------------------
+namespace fetode {
+__global__ void __launch_bounds__(256) bspline_basis_kernel(const float* __restrict__ grid, const float* __restrict__ x,
+                                                            float* __restrict__ out, long long n, int I, int G) {
+    const int NK = G + 7, S = G + 3;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(e % I);
+        const float* t = grid + (size_t)i * NK;
+        const float xv = x[e];
+        float* o = out + e * S;
+        for (int s = 0; s < S; ++s) o[s] = 0.f;
+        if (!(xv >= t[0] && xv < t[NK - 1])) continue;
+        int m = 0;
+        while (m < NK - 2 && xv >= t[m + 1]) ++m;                   // t_m <= x < t_{m+1}
+        auto T = [&](int j) -> float {                                // knots beyond the table: extrapolated, weights 0
+            if (j < 0) return t[0] + (float)j * (t[1] - t[0]);
+            if (j >= NK) return t[NK - 1] + (float)(j - NK + 1) * (t[NK - 1] - t[NK - 2]);
+            return t[j];
+        };
+        const float left1 = xv - T(m), right1 = T(m + 1) - xv;
+        const float left2 = xv - T(m - 1), right2 = T(m + 2) - xv;
+        const float left3 = xv - T(m - 2), right3 = T(m + 3) - xv;
+        float q = 1.0f / (T(m + 1) - T(m));
+        const float a0 = right1 * q, a1 = left1 * q;
+        q = a0 / (T(m + 1) - T(m - 1));
+        const float b0 = right1 * q;
+        float saved = left2 * q;
+        q = a1 / (T(m + 2) - T(m));
+        const float b1 = saved + right2 * q, b2 = left1 * q;
+        float v[4];
+        q = b0 / (T(m + 1) - T(m - 2));
+        v[0] = right1 * q; saved = left3 * q;
+        q = b1 / (T(m + 2) - T(m - 1));
+        v[1] = saved + right2 * q; saved = left2 * q;
+        q = b2 / (T(m + 3) - T(m));
+        v[2] = saved + right3 * q; v[3] = left1 * q;
+        for (int c = 0; c < 4; ++c) {
+            const int s = m - 3 + c;
+            if (s >= 0 && s < S) o[s] = v[c];
+        }
+    }
+}
+}  // namespace fetode
+
+extern "C" int fetode_bspline_basis(const float* grid, const float* x, float* out, int64_t B, int32_t I,
+                                    int32_t grid_size, int32_t spline_order, void* stream) {
+    FETODE_CHECK_ARG(grid && x && out && B >= 0 && I >= 1 && grid_size >= 1);
+    FETODE_CHECK_SUPPORTED(spline_order == 3);
+    if (B == 0) return FETODE_OK;
+    const long long n = (long long)B * I;
+    const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
+    fetode::bspline_basis_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(grid, x, out, n, I, grid_size);
+    return FETODE_LAUNCH_RC();
+}

@@ -3,14 +3,20 @@
 Host-side mirror of the reference's module surface (sallywang147/FET-ODE @ 704a0df4):
   fetode.efficientkan   LogisticBasis, KANLinear, KAN, KANFET      (efficient_kan/efficientkan.py)
   fetode.ferro_class    *FerroelectricBasis                         (ferro_class.py)
+  fetode.ecg            hysteretic LogisticBasis, KANFeatureMixer, MLPKANODEFunc, KANFetODEFunc (ECG scripts)
+  fetode.mnist_kuramoto_kan  KANLinear, Kuramoto2D, KuramotoKANClassifier             (mnist_kuramoto_kan.py)
   fetode.odeint         odeint, integrate_euler/rk2/rk4, odeint_rk4 (torchdiffeq call sites + in-repo loops)
 All arithmetic runs in fetode/libfetode.so (C ABI: include/fetode.h); there is no CPU fallback.
 """
 from . import _lib  # noqa: F401
 from .efficientkan import KAN, KANFET, KANLinear, LogisticBasis  # noqa: F401
-from .ferro_class import TwoDimensionFerroelectricBasis  # noqa: F401
+from .ferro_class import (BatchedFerroelectricBasis, FerroelectricBasis, NoisyBatchedFerroelectricBasis,  # noqa: F401
+                          NoisyFerroelectricBasis, TwoDimensionFerroelectricBasis)
+from . import ecg, mnist_kuramoto_kan  # noqa: F401
 from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odeint,  # noqa: F401
                      odeint_rk4)
 
-__all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "odeint",
+__all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "FerroelectricBasis",
+           "NoisyFerroelectricBasis", "BatchedFerroelectricBasis", "NoisyBatchedFerroelectricBasis", "ecg",
+           "mnist_kuramoto_kan", "odeint",
            "integrate_euler", "integrate_rk2", "integrate_rk4", "odeint_rk4", "as_rhs"]

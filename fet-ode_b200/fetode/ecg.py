@@ -1,0 +1,162 @@
+"""Right-hand-side modules of the ECG scripts, same names / constructor arguments / parameter names as the
+reference (commit 704a0df4):
+
+  LogisticBasis (hysteretic, hard-gated)   train_ecg_kan_fet_nn_ode.py:54-134   (same math smooth_test_KAN_ferro.py:58-80)
+  KANFeatureMixer                          train_ecg_kan_fet_nn_ode.py:408-420
+  MLPKANODEFunc / No_MLP_KANODEFunc        train_ecg_kan_fet_nn_ode.py:423-508
+  KANFetODEFunc                            train_ecg.py:986-1013
+
+The neuron / KAN arithmetic runs in libfetode.so (csrc/ferro.cu, csrc/kanlinear*.cu).  The hard gate
+``sigmoid(5 (x - prev_x)) > 0.5`` is evaluated in the kernel with IEEE exp / add / divide so the branch
+taken is bit-identical to torch's CPU result; ``branch_state`` is the uint8 gate the kernel reports.
+The plain ``kan.KAN`` of the missing ``kan_diffusion`` submodule is substituted by fetode.efficientkan.KAN
+("parity unpinned" for that submodule).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+from .efficientkan import KAN
+from .ferro_class import FerroelectricBasis
+
+
+class LogisticBasis(nn.Module):
+    """Hysteretic two-branch logistic basis, forward(x:(B,in)) -> (B,in,num_basis)."""
+
+    def __init__(self, in_dim: int, num_basis: int, gate_slope: float = 5.0, init_prev: float = 0.0,
+                 eps: float = 1e-6, branch_breaking_point=0.5, use_noise=False, noise_std=0.05):
+        super().__init__()
+        self.in_dim, self.num_basis = in_dim, num_basis
+        self.gate_slope, self.eps = gate_slope, eps
+        self.use_noise, self.noise_std = use_noise, noise_std
+        self.branch_breaking_point = branch_breaking_point
+        self.k = nn.Parameter(torch.rand(in_dim, num_basis) * 2 + 0.5)
+        self.Ec = nn.Parameter(torch.rand(in_dim, num_basis) * 2 + 0.5)
+        self.Ps = nn.Parameter(torch.rand(in_dim, num_basis) * 1.5 + 0.5)
+        self.bias = nn.Parameter(torch.randn(in_dim, num_basis) * 0.1)
+        self.coef = nn.Parameter(torch.randn(in_dim, num_basis))          # unused by forward, as in the reference
+        self.register_buffer("prev_x", torch.zeros(1, in_dim, num_basis))
+        self.register_buffer("branch_state", torch.ones(1, in_dim, num_basis))
+        self._row = None                                                   # compact [in_dim] previous last row
+
+    def reset_state(self, value: float = 0.0):
+        self._row = None
+        self.prev_x = torch.zeros(1, self.in_dim, self.num_basis, device=self.prev_x.device)
+        self.branch_state = torch.ones(1, self.in_dim, self.num_basis, device=self.prev_x.device)
+
+    def _prev_row(self, device):
+        if self._row is None:
+            # honour a buffer written from outside (load_state_dict): first basis column carries the row
+            if bool((self.prev_x != 0).any()):
+                self._row = self.prev_x[0, :, 0].to(device).contiguous()
+        return self._row
+
+    def _call(self, x, apply_sigmoid: bool):
+        if x.dim() != 2 or x.size(1) != self.in_dim:
+            raise ValueError(f"x must be (B,{self.in_dim}), got {tuple(x.shape)}")
+        if self.branch_breaking_point != 0.5:
+            raise NotImplementedError("fetode: the bit-exact gate kernel implements branch_breaking_point=0.5")
+        ops.abort_if_tracing()
+        x2 = ops.f32c(x)
+        prev = self._prev_row(x2.device)
+        new_row = torch.empty(self.in_dim, dtype=torch.float32, device=x2.device)
+        noisy = self.use_noise and self.noise_std != 0.0
+        out, side = ops.ferro_apply(self, ops.FERRO_HARDGATE, x2, prev, want_gate=True,
+                                    apply_sigmoid=apply_sigmoid and not noisy, prev_out=new_row,
+                                    gate_slope=self.gate_slope, alpha=0.5)
+        if noisy:
+            out = out + torch.randn_like(out) * self.noise_std
+            if apply_sigmoid:
+                out = torch.sigmoid(out)
+        self._row = new_row
+        self.prev_x = new_row.view(1, -1, 1).expand(1, self.in_dim, self.num_basis)
+        self.branch_state = side["gate"]                                   # uint8 [B,in,K]: 1 = up branch
+        return out
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self._call(x, False)
+
+
+class KANFeatureMixer(nn.Module):
+    """x:(B,D) -> sigmoid(basis(x)) flattened to (B, D*num_basis); the sigmoid is fused into the kernel."""
+
+    def __init__(self, dim, num_basis, act=None):
+        super().__init__()
+        self.basis = LogisticBasis(dim, num_basis)
+        self.act = nn.Sigmoid() if act is None else act
+
+    def forward(self, x):
+        if isinstance(self.act, nn.Sigmoid):
+            phi = self.basis._call(x, True)
+        else:
+            phi = self.act(self.basis(x))
+        return phi.reshape(x.size(0), -1)
+
+
+class MLPKANODEFunc(nn.Module):
+    """train_ecg_kan_fet_nn_ode.py:423-481."""
+
+    def __init__(self, latent_dim=64, num_basis=10, hidden=128, h_bound=1.0, dh_clip=10.0, init_out_std=1e-3):
+        super().__init__()
+        self.latent_dim, self.num_basis = latent_dim, num_basis
+        self.h_bound, self.dh_clip = h_bound, dh_clip
+        self.ln = nn.LayerNorm(latent_dim)
+        self.h_feat = KANFeatureMixer(latent_dim, num_basis, act=nn.Sigmoid())
+        self.kan1 = KAN([latent_dim * num_basis, hidden])
+        self.act = nn.SiLU()
+        self.kan2 = KAN([hidden, hidden])
+        self.out = nn.Linear(hidden, latent_dim, bias=True)
+        nn.init.zeros_(self.out.bias)
+        nn.init.normal_(self.out.weight, mean=0.0, std=init_out_std)
+        self.log_alpha = nn.Parameter(torch.tensor(-3.0))
+        self.scale = nn.Parameter(torch.tensor(1.0))
+
+    def forward(self, t, h):
+        h = self.ln(h)
+        h = self.h_bound * torch.tanh(h / self.h_bound)
+        phi = self.h_feat(h)
+        phi = torch.nan_to_num(phi, nan=0.0, posinf=1e3, neginf=-1e3)
+        z = self.act(self.kan1(phi))
+        z = self.act(self.kan2(z))
+        dh = self.out(z)
+        return self.scale * F.softplus(self.log_alpha) * dh
+
+
+class No_MLP_KANODEFunc(nn.Module):
+    """train_ecg_kan_fet_nn_ode.py:483-508."""
+
+    def __init__(self, latent_dim=64, num_basis=10, hidden=128):
+        super().__init__()
+        self.latent_dim, self.num_basis = latent_dim, num_basis
+        self.feat = KANFeatureMixer(latent_dim, num_basis, act=nn.Sigmoid())
+        self.proj = nn.Linear(latent_dim * num_basis, latent_dim)
+        nn.init.zeros_(self.proj.bias)
+        nn.init.normal_(self.proj.weight, mean=0.0, std=0.01)
+
+    def forward(self, t, h):
+        dh = self.proj(self.feat(h))
+        assert dh.shape == h.shape, (dh.shape, h.shape)
+        return dh
+
+
+class KANFetODEFunc(nn.Module):
+    """train_ecg.py:986-1013: tanh-bound -> FerroelectricBasis -> tanh -> FerroelectricBasis -> nan_to_num -> clamp."""
+
+    def __init__(self, latent_dim: int, hidden_dim: int, num_basis: int, h_bound: float = 1.0):
+        super().__init__()
+        self.h_bound = h_bound
+        self.fc1 = FerroelectricBasis(latent_dim, hidden_dim, num_basis)
+        self.act = nn.Tanh()
+        self.fc2 = FerroelectricBasis(hidden_dim, latent_dim, num_basis)
+
+    def forward(self, t, h):
+        if h.dim() == 1:
+            h = h.unsqueeze(0)
+        h = self.h_bound * torch.tanh(h / self.h_bound)
+        z = self.act(self.fc1(h))
+        dh = self.fc2(z)
+        dh = torch.nan_to_num(dh, nan=0.0, posinf=1e3, neginf=-1e3)
+        return torch.clamp(dh, -50.0, 50.0)

@@ -90,8 +90,134 @@ class TwoDimensionFerroelectricBasis(_FerroState, nn.Module):
             x = x.view(x.shape[0], -1)
         x2 = ops.f32c(x)
         prev = self._prev_rows(x2.shape[0], x2.device)
-        out = ops.ferro_apply(self, ops.FERRO_TWO_D, x2, prev)
+        out, _ = ops.ferro_apply(self, ops.FERRO_TWO_D, x2, prev)
         if self.use_noise:
             out = out + (torch.randn_like(out) * self.noise_std).detach() * self.coef
         self._set_rows(x2.detach())
         return out
+
+
+class _FullFerro(_FerroState, nn.Module):
+    """Shared body of the [in, out, num_basis] neurons (ferro_class.py:329-523)."""
+
+    _always_noise = False
+    _update_branch = False
+
+    def __init__(self, in_dim, out_dim, num_basis, use_noise=False, gate_slope=10.0, alpha=0.8, noise_std=0.05):
+        super().__init__()
+        self.in_dim, self.out_dim, self.num_basis = in_dim, out_dim, num_basis
+        self.use_noise, self.noise_std = use_noise, noise_std
+        self.gate_slope, self.alpha = gate_slope, alpha
+        shape = (in_dim, out_dim, num_basis)
+        self.k = nn.Parameter(torch.rand(*shape) * 2 + 0.5)
+        self.Ec = nn.Parameter(torch.rand(*shape) * 2 + 0.5)
+        self.Ps = nn.Parameter(torch.rand(*shape) * 1.5 + 0.5)
+        self.bias = nn.Parameter(torch.randn(*shape) * 0.1)
+        self.coef = nn.Parameter(torch.randn(*shape))
+        self._init_state(shape)
+
+    # first-call rule of the reference (:373-378): buffers whose shape is not [B,I,O,K] are
+    # re-created as prev = x (dx = 0), branch_sign = 1; the initial [1,...] zeros match only B == 1.
+    def _full_prev(self, x2: torch.Tensor):
+        B = x2.shape[0]
+        r = self._rows
+        if r is None:
+            return None if B == 1 else x2
+        if r.shape[0] != B:
+            return x2
+        return r if r.is_contiguous() else r.contiguous()
+
+    def _full_branch(self, B: int):
+        br = self.branch_sign
+        if br.dim() == 4 and br.shape[0] == B and (B != 1 or self._br_live):
+            return br if br.is_contiguous() else br.contiguous()
+        return None                                     # all ones
+
+    def reset_state(self):
+        """ferro_class.py:422-424: zero_() / fill_(1) IN PLACE -- the batch shape of the buffers survives."""
+        if self._rows is not None:
+            self._set_rows(torch.zeros_like(self._rows))
+        else:
+            self.prev_x = torch.zeros(1, *self._tail, device=self.prev_x.device)
+        if self._br_live:
+            self.branch_sign.fill_(1.0)
+        else:
+            self.branch_sign = torch.ones(1, *self._tail, device=self.prev_x.device)
+
+    _br_live = False
+
+    def forward(self, x, return_activations=False):
+        ops.abort_if_tracing()
+        if x.dim() > 2:
+            x = x.view(x.shape[0], -1)
+        x2 = ops.f32c(x)
+        B = x2.shape[0]
+        prev = self._full_prev(x2.detach())
+        br = self._full_branch(B) if self._update_branch else None
+        noisy = (self._always_noise or self.use_noise) and self.noise_std != 0.0
+        want_basis = return_activations or noisy
+        out, side = ops.ferro_apply(self, ops.FERRO_FULL, x2, prev, br=br, want_basis=want_basis,
+                                    want_br_out=self._update_branch)
+        basis = side["basis"]
+        if noisy:
+            # basis + noise.detach()  (:410-412 / :508-509): the noise enters the output through coef only
+            noise = torch.randn_like(basis) * self.noise_std
+            out = out + (noise * self.coef).sum(dim=(1, 3))
+            basis = basis + noise
+        self._set_rows(x2.detach())
+        if self._update_branch:                          # :512-514
+            self.branch_sign = side["br_out"]
+            self._br_live = True
+        if return_activations:
+            return out, basis, self.coef.detach()
+        return out
+
+
+class FerroelectricBasis(_FullFerro):
+    """ferro_class.py:329-424.  branch_sign is never written by the reference => it stays 1."""
+
+
+class NoisyFerroelectricBasis(_FullFerro):
+    """ferro_class.py:427-523: noise is added unconditionally (:508-509) and branch_sign <- target_sign
+    (:512-514), a real [B,I,O,K] hysteresis state."""
+    _always_noise = True
+    _update_branch = True
+
+    def __init__(self, in_dim, out_dim, num_basis, use_noise=True, gate_slope=10.0, alpha=0.8, noise_std=0.2):
+        super().__init__(in_dim, out_dim, num_basis, use_noise, gate_slope, alpha, noise_std)
+
+
+class BatchedFerroelectricBasis(_FullFerro):
+    """ferro_class.py:107-214: per-sample loop in which row b sees row b-1 as its previous input
+    (prev_x is [1,I,O,K] and is overwritten after every sample); branch_sign is never written.
+    One launch: prev = [stored row ; x[:-1]]."""
+
+    def forward(self, x, return_activations=False):
+        ops.abort_if_tracing()
+        if x.dim() > 2:
+            x = x.view(x.shape[0], -1)
+        x2 = ops.f32c(x)
+        B = x2.shape[0]
+        if B == 0:
+            return x2.new_empty(0, self.out_dim)
+        first = self._rows if self._rows is not None else torch.zeros(1, self.in_dim, device=x2.device)
+        prev = torch.cat([first[-1:].to(x2.device), x2.detach()[:-1]], dim=0).contiguous()
+        noisy = (self._always_noise or self.use_noise) and self.noise_std != 0.0
+        out, side = ops.ferro_apply(self, ops.FERRO_FULL, x2, prev, want_basis=return_activations or noisy)
+        basis = side["basis"]
+        if noisy:
+            noise = torch.randn_like(basis) * self.noise_std
+            out = out + (noise * self.coef).sum(dim=(1, 3))
+            basis = basis + noise
+        self._set_rows(x2.detach()[-1:].contiguous())
+        if return_activations:
+            return out, basis, self.coef.detach()
+        return out
+
+
+class NoisyBatchedFerroelectricBasis(BatchedFerroelectricBasis):
+    """ferro_class.py:220-326: BatchedFerroelectricBasis with unconditional noise."""
+    _always_noise = True
+
+    def __init__(self, in_dim, out_dim, num_basis, use_noise=True, gate_slope=10.0, alpha=0.8, noise_std=0.2):
+        super().__init__(in_dim, out_dim, num_basis, use_noise, gate_slope, alpha, noise_std)

@@ -347,3 +347,155 @@ def rk_combine(y: Optional[torch.Tensor], ks: Sequence[torch.Tensor], coefs: Seq
 
 
 FERRO_FULL, FERRO_TWO_D, FERRO_HARDGATE = _lib.FERRO_FULL, _lib.FERRO_TWO_D, _lib.FERRO_HARDGATE
+FERRO_LOGISTIC = 3
+
+
+# --------------------------------------------------------------------------------------
+# stand-alone ferroelectric / logistic neurons (csrc/ferro.cu)
+# --------------------------------------------------------------------------------------
+def _ferro_struct(cfg: dict, k, Ec, Ps, bias, coef) -> _lib.Ferro:
+    s = _lib.Ferro()
+    s.variant, s.in_dim, s.out_dim, s.num_basis = cfg["variant"], cfg["I"], cfg["O"], cfg["K"]
+    for name, t in (("k", k), ("Ec", Ec), ("Ps", Ps), ("bias", bias), ("coef", coef)):
+        setattr(s, name, ptr(None if t is None else _keep(s, f32c(t.detach()))).value)
+    s.gate_slope, s.alpha = float(cfg["gate_slope"]), float(cfg["alpha"])
+    s.apply_sigmoid = int(cfg.get("apply_sigmoid", 0))
+    return s
+
+
+class FerroFn(torch.autograd.Function):
+    """One call of a ferroelectric neuron.  ``prev`` / ``br`` are constants of the graph
+    (ferro_class.py:381-382).  Side outputs (basis, new branch_sign, gate bits) are left in cfg["side"]."""
+
+    @staticmethod
+    def forward(ctx, cfg, prev, br, x, k, Ec, Ps, bias, coef):
+        _require_cuda(x, "input")
+        B = x.shape[0]
+        I, O, K = cfg["I"], cfg["O"], cfg["K"]
+        full = cfg["variant"] == FERRO_FULL
+        out = torch.empty((B, O) if full else (B, I, K), dtype=torch.float32, device=x.device)
+        side = {}
+        elem_shape = (B, I, O, K) if full else (B, I, K)
+        basis = torch.empty(elem_shape, dtype=torch.float32, device=x.device) if cfg.get("want_basis") else None
+        br_out = torch.empty(elem_shape, dtype=torch.float32, device=x.device) if cfg.get("want_br_out") else None
+        gate = torch.empty(elem_shape, dtype=torch.uint8, device=x.device) if cfg.get("want_gate") else None
+        prev_out = cfg.get("prev_out")
+        s = _ferro_struct(cfg, k, Ec, Ps, bias, coef)
+        if br_out is not None and br is None:
+            br = torch.ones(elem_shape, dtype=torch.float32, device=x.device)
+        if B > 0:
+            check(lib().fetode_ferro_fwd(C.byref(s), ptr(x), ptr(prev), C.c_int(1 if prev is None else 0), ptr(br),
+                                         ptr(out), ptr(basis), ptr(br_out), ptr(gate), ptr(prev_out),
+                                         C.c_int64(B), stream()), "ferro_fwd")
+        side.update(basis=basis, br_out=br_out, gate=gate)
+        cfg["side"] = side
+        ctx.cfg, ctx.prev, ctx.br = cfg, prev, br
+        ctx.save_for_backward(x, k, Ec, Ps, bias, coef if coef is not None else x.new_empty(0))
+        ctx.has_coef = coef is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, k, Ec, Ps, bias, coef = ctx.saved_tensors
+        if not ctx.has_coef:
+            coef = None
+        cfg = ctx.cfg
+        gout = f32c(gout)
+        B = x.shape[0]
+        s = _ferro_struct(cfg, k, Ec, Ps, bias, coef)
+        g = _lib.FerroGrads()
+        grads = []
+        for idx, (name, t) in enumerate((("k", k), ("Ec", Ec), ("Ps", Ps), ("bias", bias), ("coef", coef))):
+            gt = None
+            if t is not None and ctx.needs_input_grad[4 + idx]:
+                gt = torch.zeros(t.shape, dtype=torch.float32, device=x.device)
+            setattr(g, name, ptr(gt).value)
+            grads.append(gt)
+        gx = torch.empty_like(x) if ctx.needs_input_grad[3] else None
+        check(lib().fetode_ferro_bwd(C.byref(s), ptr(x), ptr(ctx.prev), C.c_int(1 if ctx.prev is None else 0),
+                                     ptr(ctx.br), ptr(gout), ptr(gx), C.byref(g), C.c_int64(B), stream()),
+              "ferro_bwd")
+        return (None, None, None, gx, *grads)
+
+
+def ferro_apply(module, variant: int, x2: torch.Tensor, prev: Optional[torch.Tensor], *, br=None,
+                want_basis=False, want_br_out=False, want_gate=False, apply_sigmoid=False, prev_out=None,
+                gate_slope=None, alpha=None):
+    """Launch the neuron kernel for ``module`` (parameter names k, Ec, Ps, bias, coef | a, b).
+    Returns (out, side) where side holds the optional basis / br_out / gate tensors."""
+    if variant == FERRO_LOGISTIC:
+        k, Ec, Ps, bias, coef = module.a, module.b, None, None, None
+        I, K, O = module.a.shape[0], module.a.shape[1], 1
+    else:
+        k, Ec, Ps, bias, coef = module.k, module.Ec, module.Ps, module.bias, getattr(module, "coef", None)
+        if variant == FERRO_FULL:
+            I, O, K = k.shape
+        else:
+            (I, K), O = k.shape, 1
+    cfg = dict(variant=variant, I=int(I), O=int(O), K=int(K),
+               gate_slope=module.gate_slope if gate_slope is None else gate_slope,
+               alpha=getattr(module, "alpha", 0.5) if alpha is None else alpha,
+               apply_sigmoid=int(apply_sigmoid), want_basis=want_basis, want_br_out=want_br_out,
+               want_gate=want_gate, prev_out=prev_out)
+    if variant == FERRO_LOGISTIC:
+        cfg["gate_slope"], cfg["alpha"] = 0.0, 0.0
+    out = FerroFn.apply(cfg, prev, br, x2, k, Ec, Ps, bias, coef)
+    return out, cfg["side"]
+
+
+def logistic_basis_apply(module, x2: torch.Tensor) -> torch.Tensor:
+    """efficientkan.LogisticBasis.forward :20-24 as a stand-alone call."""
+    return ferro_apply(module, FERRO_LOGISTIC, x2, None)[0]
+
+
+def bspline_basis(module, x2: torch.Tensor) -> torch.Tensor:
+    """KANLinear.b_splines efficientkan.py:117-131 for CUDA inputs -> [B, I, G+k]."""
+    _require_cuda(x2, "input")
+    B, I = x2.shape
+    S = int(module.grid_size) + int(module.spline_order)
+    out = torch.empty(B, I, S, dtype=torch.float32, device=x2.device)
+    if B:
+        check(lib().fetode_bspline_basis(ptr(f32c(module.grid)), ptr(x2), ptr(out), C.c_int64(B), C.c_int32(I),
+                                         C.c_int32(int(module.grid_size)), C.c_int32(int(module.spline_order)),
+                                         stream()), "bspline_basis")
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# Kuramoto lattice (csrc/kuramoto.cu)
+# --------------------------------------------------------------------------------------
+class KuramotoFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, K, omega, H, W, steps, dt):
+        _require_cuda(x, "input")
+        B = x.shape[0]
+        x2 = f32c(x.reshape(B, H * W))
+        feat = torch.empty(B, 2 * H * W, dtype=torch.float32, device=x.device)
+        need = any(ctx.needs_input_grad[:3])
+        ckpt = torch.empty(steps, B, H * W, dtype=torch.float32, device=x.device) if need else None
+        Kc, om = f32c(K.detach().reshape(1)), f32c(omega.detach().reshape(-1))
+        if B:
+            check(lib().fetode_kuramoto_fwd(ptr(x2), ptr(Kc), ptr(om), C.c_int32(H), C.c_int32(W), C.c_int32(steps),
+                                            C.c_float(dt), ptr(feat), ptr(ckpt), C.c_int64(B), stream()), "kuramoto_fwd")
+        ctx.dims = (H, W, steps, dt, tuple(x.shape), tuple(K.shape), tuple(omega.shape))
+        ctx.save_for_backward(ckpt if ckpt is not None else feat.new_empty(0), feat, Kc, om)
+        return feat
+
+    @staticmethod
+    def backward(ctx, gfeat):
+        ckpt, feat, Kc, om = ctx.saved_tensors
+        H, W, steps, dt, xs, Ks, oms = ctx.dims
+        B = feat.shape[0]
+        gfeat = f32c(gfeat)
+        gx = torch.empty(B, H * W, dtype=torch.float32, device=feat.device) if ctx.needs_input_grad[0] else None
+        gK = torch.zeros(1, dtype=torch.float32, device=feat.device)
+        gom = torch.zeros(H * W, dtype=torch.float32, device=feat.device)
+        if B:
+            check(lib().fetode_kuramoto_bwd(ptr(ckpt if steps else None), ptr(feat), ptr(Kc), ptr(om), C.c_int32(H),
+                                            C.c_int32(W), C.c_int32(steps), C.c_float(dt), ptr(gfeat), ptr(gx), ptr(gK),
+                                            ptr(gom), C.c_int64(B), stream()), "kuramoto_bwd")
+        return (None if gx is None else gx.reshape(xs), gK.reshape(Ks), gom.reshape(oms), None, None, None, None)
+
+
+def kuramoto_apply(x, K, omega, H, W, steps, dt):
+    return KuramotoFn.apply(x, K, omega, int(H), int(W), int(steps), float(dt))

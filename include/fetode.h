@@ -107,6 +107,11 @@ FETODE_API int fetode_kanlinear_bwd(const fetode_kanlayer_t* L, const float* wca
                          const fetode_kanlayer_grads_t* grads, float* ws,
                          int64_t B, void* stream);
 
+/* B-spline basis values alone: KANLinear.b_splines efficientkan.py:117-131 (used by update_grid :184-221 and
+ * curve2coeff :133-143 on CUDA inputs).  grid [I, G+2k+1], x [B,I] -> out [B, I, G+k]; spline_order must be 3. */
+FETODE_API int fetode_bspline_basis(const float* grid, const float* x, float* out, int64_t B, int32_t I,
+                         int32_t grid_size, int32_t spline_order, void* stream);
+
 /* ---- fused small-width KAN / KANFET network + Runge-Kutta loop -----------------------
  * Replaces, for a stack of KANLinear layers whose widths are all <= 32 (the Lotka-Volterra
  * KANFET([2,10,2]) of train_kanfet_node_predprey.py:146), the whole of
@@ -139,13 +144,28 @@ FETODE_API int64_t fetode_smallnet_state_floats(const fetode_smallnet_t* net);
  * y0 [B,D] -> y_out [B,D] after n_steps steps of size dt.  state (in/out, [B, state_floats]) is
  * ignored on input when state_is_zero != 0; may be NULL when branch != FERRO2D.
  * traj (or NULL): [n_steps/dump_every, B, D] receives y after every dump_every-th step.
- * ckpt (or NULL): [n_steps, B, D + state_floats] receives (y, state) at the START of every step
+ * ckpt (or NULL): [n_steps, D + state_floats, B] receives (y, state) at the START of every step
  * (what fetode_smallnet_rk_bwd replays from).
  */
 FETODE_API int fetode_smallnet_rk_fwd(const fetode_smallnet_t* net, const float* packed, int tableau,
                            const float* y0, float* y_out, float* state, int state_is_zero,
                            int64_t B, double dt, int32_t n_steps,
                            float* traj, int32_t dump_every, float* ckpt, void* stream);
+/*
+ * Reverse sweep of fetode_smallnet_rk_fwd (what loss.backward() does in train_kanfet_node_predprey.py:254-256:
+ * plain autograd through every solver stage; hysteresis snapshots are constants).  ckpt is the buffer the forward
+ * call filled ([n_steps, D + state_floats, B]).  g_yout [B,D] (or NULL) is d(loss)/d(y_out); g_traj (or NULL)
+ * [n_steps/dump_every, B, D] is d(loss)/d(traj).  g_y0 [B,D] is overwritten.  Parameter gradients are ADDED to
+ * gfold (fetode_smallnet_gfold_floats floats, zeroed by the caller before the first launch of a backward pass;
+ * several launches -- one per run of equal step sizes -- may accumulate into it) in folded form;
+ * fetode_smallnet_unfold then applies the chain rule and ACCUMULATES into grads[2] (one entry per layer).
+ */
+FETODE_API int64_t fetode_smallnet_gfold_floats(const fetode_smallnet_t* net);
+FETODE_API int fetode_smallnet_rk_bwd(const fetode_smallnet_t* net, const float* packed, int tableau,
+                           const float* ckpt, const float* g_yout, const float* g_traj, int32_t dump_every,
+                           float* g_y0, float* gfold, int64_t B, double dt, int32_t n_steps, void* stream);
+FETODE_API int fetode_smallnet_unfold(const fetode_smallnet_t* net, const fetode_kanlayer_t* layers, float* gfold,
+                           const fetode_kanlayer_grads_t* grads, void* stream);
 /* one RHS evaluation y -> f(y) (KAN.forward), same state rules */
 FETODE_API int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
                         float* dy, float* state, int state_is_zero, int64_t B, void* stream);
@@ -176,6 +196,8 @@ FETODE_API int fetode_rk_error_sumsq(const float* err, const float* y0, const fl
 #define FETODE_FERRO_FULL     0
 #define FETODE_FERRO_TWO_D    1
 #define FETODE_FERRO_HARDGATE 2
+#define FETODE_FERRO_LOGISTIC 3   /* LogisticBasis.forward efficientkan.py:20-24 stand-alone: k:=a, Ec:=b [I,K];
+                                     out [B,I,K] = 2/(1+exp(-a (x-b))); Ps, bias, coef unused (NULL)        */
 
 typedef struct fetode_ferro {
     int32_t variant, in_dim, out_dim, num_basis;
