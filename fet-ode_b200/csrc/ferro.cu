@@ -11,8 +11,8 @@
 // compact [B,I] row block, and the optional branch_sign state of the Noisy variant is the only
 // [B,I,O,K] array that touches HBM (one read + one write per call).
 //
-// The hard gate  (sigmoid(5 (x - prev)) > 0.5)  is evaluated with IEEE expf / add / divide so that the
-// branch taken is bit-identical to torch's CPU result (the threshold is a rounding artefact of
+// The hard gate  (sigmoid(5 (x - prev)) > 0.5)  is evaluated with a correctly rounded exp and IEEE add / divide
+// so that the branch taken is bit-identical to torch's CPU result (the threshold is a rounding artefact of
 // 1/(1+exp(-z)): true from z >= ~8.94e-8, false at z == 0); everything else uses MUFU ex2 / rcp.
 #include "common.cuh"
 
@@ -176,9 +176,13 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
 // ------------------------------------------------------------------------------------------
 // TWO_D and HARDGATE: params [I,K], out [B,I,K] (element-wise over the basis axis)
 // ------------------------------------------------------------------------------------------
-// IEEE evaluation of torch's CPU  sigmoid(z) > 0.5  (see file header)
+// torch's CPU  sigmoid(z) > 0.5  evaluated literally: e = fl32(exp(-z)) (torch's vectorised and scalar float exp are
+// both correctly rounded for the arguments that matter here; CUDA's expf is not -- it is 2 ulp -- so the exponential
+// is taken in double and rounded once), s = fl32(1 + e), r = fl32(1 / s), r > 0.5.  Net effect: true iff
+// e <= 1 - 2^-23, i.e. z > ~8.94e-8; false at z == 0.  One evaluation per (row, input) -- dx does not depend on the
+// basis index -- so the double-precision exp is off the critical path.
 __device__ __forceinline__ bool hard_gate(float z) {
-    const float e = expf(-z);
+    const float e = (float)exp(-(double)z);
     const float s = __fadd_rn(1.0f, e);
     return __fdiv_rn(1.0f, s) > 0.5f;
 }

@@ -433,7 +433,7 @@ def ferro_apply(module, variant: int, x2: torch.Tensor, prev: Optional[torch.Ten
         else:
             (I, K), O = k.shape, 1
     cfg = dict(variant=variant, I=int(I), O=int(O), K=int(K),
-               gate_slope=module.gate_slope if gate_slope is None else gate_slope,
+               gate_slope=getattr(module, "gate_slope", 0.0) if gate_slope is None else gate_slope,
                alpha=getattr(module, "alpha", 0.5) if alpha is None else alpha,
                apply_sigmoid=int(apply_sigmoid), want_basis=want_basis, want_br_out=want_br_out,
                want_gate=want_gate, prev_out=prev_out)
