@@ -14,6 +14,7 @@
 //   LogisticBasis.forward                   efficient_kan/efficientkan.py:20-24
 //   TwoDimensionFerroelectricBasis.forward  ferro_class.py:547-592 (KANFET branch slot)
 //   MNIST copy with logistic_bias           mnist_kuramoto_kan.py:112-142
+#include <cstdlib>
 #include "kanlinear.cuh"
 
 namespace fetode {
@@ -181,6 +182,14 @@ static int kl_fwd_launch(const KLFwdArgs& a, cudaStream_t st) {
     return FETODE_LAUNCH_RC();
 }
 
+// rows from which the tensor-core kernel is used; FETODE_TC=0 disables it, FETODE_TC=1 forces it for any batch
+long long kl_tc_min_rows() {
+    const char* e = getenv("FETODE_TC");
+    if (e && e[0] == '0') return (1LL << 62);
+    if (e && e[0] == '1') return 1;
+    return 64;
+}
+
 int kl_check(const fetode_kanlayer_t* P) {
     if (!P) return FETODE_EINVAL;
     if (P->in_features < 1 || P->out_features < 1) return FETODE_EINVAL;
@@ -218,7 +227,9 @@ extern "C" int fetode_kanlinear_pack(const fetode_kanlayer_t* P, float* wcat, vo
     const long long work = (long long)L.I * L.F * L.O;
     const int blocks = (int)std::min<long long>((work + 255) / 256, 148 * 8);
     kl_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(*P, L, wcat);
-    return FETODE_LAUNCH_RC();
+    rc = FETODE_LAUNCH_RC();
+    if (rc) return rc;
+    return kl_tc_pack(L, wcat, (cudaStream_t)stream);
 }
 
 extern "C" int fetode_kanlinear_fwd(const fetode_kanlayer_t* P, const float* wcat, const float* x,
@@ -238,6 +249,14 @@ extern "C" int fetode_kanlinear_fwd(const fetode_kanlayer_t* P, const float* wca
     a.gl = P->gate_slope * FETODE_LOG2E;
     a.prev_is_zero = prev_is_zero;
     cudaStream_t st = (cudaStream_t)stream;
+    if (a.L.tc_ok && B >= kl_tc_min_rows()) {           // wide layer: tcgen05 path (kanlinear_tc.cu)
+        rc = kl_tc_fwd(P, a.L, wcat, x, prev, prev_is_zero, y, B, st);
+        if (rc != FETODE_EUNSUPPORTED) {
+            if (rc == FETODE_OK && prev_out && P->branch == FETODE_BRANCH_FERRO2D)
+                rc = (int)cudaMemcpyAsync(prev_out, x, (size_t)B * P->in_features * sizeof(float), cudaMemcpyDeviceToDevice, st);
+            return rc;
+        }
+    }
     switch (P->branch) {
         case FETODE_BRANCH_NONE: return kl_fwd_launch<FETODE_BRANCH_NONE>(a, st);
         case FETODE_BRANCH_LOGISTIC: return kl_fwd_launch<FETODE_BRANCH_LOGISTIC>(a, st);

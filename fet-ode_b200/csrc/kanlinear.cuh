@@ -2,7 +2,7 @@
 // the any-width KANLinear kernels (CUDA-core forward/backward, tcgen05 forward).
 #pragma once
 #include <algorithm>
-#include "common.cuh"
+#include "smallnet.cuh"
 
 namespace fetode {
 
@@ -14,6 +14,9 @@ struct KLLayout {
     int I, O, G, NB, S, F, NK, NKP, TAB;
     int t_kn, t_rd1, t_rd2, t_rd3, t_gi, t_bp;
     long long wcat, bias, tab, total;
+    // tensor-core weight image (kanlinear_tc.cu); tc_ok == 0 when the shape is served by the CUDA-core kernels only
+    int tc_ok, tc_BN, tc_ntile, tc_units, tc_stages;
+    long long tc;
 };
 
 __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
@@ -35,6 +38,17 @@ __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
     L.wcat = o; o += ((long long)I * L.F * O + 3) / 4 * 4;
     L.bias = o; o += (O + 3) / 4 * 4;
     L.tab = o; o += (long long)I * L.TAB;
+    L.tc_ok = (G == 5 && (NB == 0 || NB == 8 || NB == 10) && (long long)I * L.F >= 1024 && O >= 8) ? 1 : 0;
+    L.tc = 0;
+    if (L.tc_ok) {
+        L.tc_BN = O <= 16 ? 16 : (O <= 32 ? 32 : (O <= 64 ? 64 : 128));
+        L.tc_ntile = (O + L.tc_BN - 1) / L.tc_BN;
+        L.tc_units = (I + 31) / 32;
+        L.tc_stages = L.tc_units * L.F;
+        o = (o + 255) / 256 * 256;                       // 1 KB alignment for the bulk copies
+        L.tc = o;
+        o += (long long)L.tc_ntile * L.tc_stages * 2 * L.tc_BN * 32;
+    }
     L.total = o;
     return L;
 }
@@ -83,5 +97,8 @@ __device__ __forceinline__ void kl_features(float x, float prev, float gl, const
 }
 
 int kl_check(const fetode_kanlayer_t* P);
+int kl_tc_pack(const KLLayout& L, float* blob, cudaStream_t st);
+int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
+              int prev_is_zero, float* y, long long B, cudaStream_t st);
 
 }  // namespace fetode

@@ -1,0 +1,368 @@
+// kanlinear_tc.cu -- wide KANLinear forward on the 5th-generation tensor cores (sm_100a): tcgen05.mma with the
+// accumulator in TMEM, the weight operand streamed by the TMA bulk-copy engine and the feature operand
+// (SiLU | cubic B-spline basis | logistic / ferroelectric branch basis) evaluated in the kernel's PROLOGUE and
+// written straight into the 128B-swizzled UMMA shared-memory layout -- the [B, I*(1+G+k+nb)] feature matrix the
+// reference materialises level by level in HBM (efficient_kan/efficientkan.py:117-131, 166-179) never exists.
+//
+// Reference arithmetic being replaced: KANLinear.forward efficientkan.py:160-182 for the wide layers of the
+// ECG / ETT / diffusion configurations (kan.KAN([768,128]), ([128,128]) train_ecg_kan_fet_nn_ode.py:441-443;
+// KAN([ctx*F,128]) train_kan_fet_ett.py:676-681; KANFET([in,256]).. kan_diffusion_ett.py:421-425).
+//
+// Precision: the 1e-5 per-evaluation bar rules out plain TF32 (10-bit mantissa, ~3e-4).  Both operands are split
+// x = hi + lo (hi = top 19 bits, lo = x - hi exactly) and three MMAs are issued per K-slice,
+// hi*hi + hi*lo + lo*hi, accumulating in fp32 in TMEM; the dropped lo*lo term is ~2^-22 relative.
+//
+// CTA = 128 rows x BN outputs x one contiguous range of 32-input units (split-K over the grid's z axis).
+//   warps 0-3  producers: thread r owns row r; per group of 4 inputs it evaluates 4*F features, splits them and
+//              stores 16-byte chunks (conflict-free under the 128B swizzle) into the A ring; afterwards the same
+//              warps are the epilogue (TMEM lane quarter == warp index): tcgen05.ld -> (+bias) -> y / atomics
+//   warp 4     lane 0: cp.async.bulk of the pre-split, pre-swizzled weight stage (hi+lo) into the B ring;
+//              whole warp: TMEM alloc / dealloc
+//   warp 5     lane 0: tcgen05.mma issue (12 per 32-wide K stage), tcgen05.commit to release ring slots
+#include "kanlinear.cuh"
+
+namespace fetode {
+namespace tc {
+
+constexpr int BM = 128, BK = 32, NSTAGE = 3, THREADS = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    }
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// K-major, SWIZZLE_128B operand tile: 8-row atoms of 128 B, atoms 1024 B apart along M/N
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);            // start address
+    d |= (uint64_t)1 << 16;                             // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                   // stride byte offset
+    d |= (uint64_t)1 << 46;                             // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                             // SWIZZLE_128B
+    return d;
+}
+// float offset of element (row, col) inside a [rows x 32] swizzled tile
+__host__ __device__ __forceinline__ int swz(int row, int col) {
+    return (row >> 3) * 256 + (row & 7) * 32 + ((((col >> 2) ^ (row & 7)) << 2) | (col & 3));
+}
+
+struct TCArgs {
+    const float* blob;      // standard layer image (bias, per-input tables)
+    const float* wtc;       // tensor-core weight image
+    const float* x;
+    const float* prev;
+    float* y;
+    long long B;
+    KLLayout L;
+    float gl;
+    int prev_is_zero, BN, units_total, units_per_split, stages_total;
+};
+
+
+// all F = 9 + NB features of one (row, input) pair in registers: [silu | N_0..N_7 | r_0..r_{NB-1}]
+template <int NB, int BR>
+__device__ __forceinline__ void tc_features(float x, float prev, float gl, const float* __restrict__ tab,
+                                            const KLLayout& L, float* f) {
+    f[0] = x * rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));                     // efficientkan.py:166
+    int m = -1;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    const float4 gi = *reinterpret_cast<const float4*>(tab + L.t_gi);
+    if (x >= gi.x && x < gi.z) {                                                     // :122 half-open test
+        const float* kp = tab + L.t_kn;
+        m = bspline_interval(x, kp, gi.x, gi.y, L.NK);
+        bspline3_local(x, kp, tab + L.t_rd1, tab + L.t_rd2, tab + L.t_rd3, m + 3, v);
+    }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        float r = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) r = (s == m - 3 + c) ? v[c] : r;
+        f[1 + s] = (m >= 0) ? r : 0.f;
+    }
+    if constexpr (NB > 0) {
+        float omu = 0.f;
+        if constexpr (BR == FETODE_BRANCH_FERRO2D) omu = rcp_approx(1.0f + ex2_approx(gl * (x - prev)));
+        float r[NB];
+        branch_eval<NB, BR>(x, omu, gl, reinterpret_cast<const float4*>(tab + L.t_bp), r);
+#pragma unroll
+        for (int j = 0; j < NB; ++j) f[9 + j] = r[j];
+    }
+}
+
+template <int NB, int BR>
+__global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
+    constexpr int F = 9 + NB;
+    extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
+    const int BN = a.BN;
+    // carve: A ring (hi, lo per stage), B ring (hi, lo per stage), barriers
+    const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
+    unsigned char* gbase = tc_smem_raw + (base - smem_u32(tc_smem_raw));
+    constexpr uint32_t A_TILE = BM * BK * 4;                     // 16 KB
+    const uint32_t B_TILE = (uint32_t)BN * BK * 4;
+    const uint32_t offA = 0, offB = NSTAGE * 2 * A_TILE, offBar = offB + NSTAGE * 2 * B_TILE;
+    const uint32_t barFullA = base + offBar, barFullB = barFullA + 8 * NSTAGE, barEmpty = barFullB + 8 * NSTAGE,
+                   barDone = barEmpty + 8 * NSTAGE;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + offBar + 8 * (3 * NSTAGE + 1));
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long m0 = (long long)blockIdx.x * BM;
+    const int ntile = blockIdx.y, split = blockIdx.z;
+    const int unit0 = split * a.units_per_split;
+    const int nunits = min(a.units_per_split, a.units_total - unit0);
+    const int nit = nunits * F;                                   // 32-wide K stages of this CTA
+    const int stage0 = unit0 * F;
+    const uint32_t tmem_cols = BN < 32 ? 32u : (uint32_t)BN;
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) {
+            mbar_init(barFullA + 8 * s, 128);
+            mbar_init(barFullB + 8 * s, 1);
+            mbar_init(barEmpty + 8 * s, 1);
+        }
+        mbar_init(barDone, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32((const void*)tmem_slot)), "r"(tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 4) {
+        // ===================== producers: A operand =====================
+        const int r = tid;
+        const long long b = m0 + r;
+        const bool live = b < a.B;
+        const KLLayout& L = a.L;
+        const int I = L.I;
+        const float* xrow = a.x + (live ? b : 0) * I;
+        const float* prow = a.prev + (live ? b : 0) * I;
+        const bool has_prev = BR == FETODE_BRANCH_FERRO2D && !a.prev_is_zero;
+        const uint32_t rowoff = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+        const uint32_t rx = (uint32_t)(r & 7);
+        int it = 0, cs = 0;                                      // stage iteration, 16-byte chunk inside the stage
+        uint32_t dstA = 0;
+        for (int u = 0; u < nunits; ++u) {
+#pragma unroll 1
+            for (int g = 0; g < 8; ++g) {
+                const int i0 = (unit0 + u) * 32 + g * 4;
+                float f[4 * F];
+#pragma unroll
+                for (int ii = 0; ii < 4; ++ii) {
+                    const int i = i0 + ii;
+                    const bool ok = live && i < I;
+                    const float x = ok ? __ldg(xrow + i) : 0.f;
+                    const float pv = (ok && has_prev) ? __ldg(prow + i) : 0.f;
+                    tc_features<NB, BR>(x, pv, a.gl, a.blob + L.tab + (size_t)(i < I ? i : 0) * L.TAB, L, f + ii * F);
+                }
+#pragma unroll
+                for (int c = 0; c < F; ++c) {
+                    if (cs == 0) {
+                        const int s = it % NSTAGE;
+                        mbar_wait(barEmpty + 8 * s, ((it / NSTAGE) & 1) ^ 1);
+                        dstA = base + offA + (uint32_t)s * 2 * A_TILE + rowoff;
+                    }
+                    float hi[4], lo[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float v = f[4 * c + e];
+                        hi[e] = __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+                        lo[e] = v - hi[e];
+                    }
+                    const uint32_t addr = dstA + ((((uint32_t)cs) ^ rx) << 4);
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + A_TILE), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
+                    if (++cs == 8) {
+                        fence_proxy_async();
+                        mbar_arrive(barFullA + 8 * (it % NSTAGE));
+                        cs = 0;
+                        ++it;
+                    }
+                }
+            }
+        }
+        // ===================== epilogue =====================
+        mbar_wait(barDone, 0);
+        tc_fence_after();
+        const float* bias = a.blob + L.bias;
+        const int O = L.O, n0 = ntile * BN;
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+            uint32_t v[16];
+            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                : "r"(taddr) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (live) {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int n = n0 + c0 + e;
+                    if (n < O) {
+                        const float val = __uint_as_float(v[e]);
+                        if (gridDim.z == 1) a.y[b * O + n] = val + bias[n];
+                        else atomicAdd(a.y + b * O + n, split == 0 ? val + bias[n] : val);
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+    } else if (warp == 4) {
+        // ===================== TMA: B operand =====================
+        if (lane == 0) {
+            const uint32_t bytes = 2 * B_TILE;
+            const float* src = a.wtc + ((size_t)ntile * a.stages_total + stage0) * (size_t)(2 * BN * BK);
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % NSTAGE;
+                mbar_wait(barEmpty + 8 * s, ((it / NSTAGE) & 1) ^ 1);
+                mbar_arrive_expect_tx(barFullB + 8 * s, bytes);
+                bulk_g2s(base + offB + (uint32_t)s * 2 * B_TILE, src + (size_t)it * (2 * BN * BK), bytes, barFullB + 8 * s);
+            }
+        }
+    } else {
+        // ===================== MMA issue =====================
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % NSTAGE;
+                const uint32_t ph = (it / NSTAGE) & 1;
+                mbar_wait(barFullA + 8 * s, ph);
+                mbar_wait(barFullB + 8 * s, ph);
+                tc_fence_after();
+                const uint32_t aHi = base + offA + (uint32_t)s * 2 * A_TILE, aLo = aHi + A_TILE;
+                const uint32_t bHi = base + offB + (uint32_t)s * 2 * B_TILE, bLo = bHi + B_TILE;
+#pragma unroll
+                for (int j = 0; j < BK / 8; ++j) {
+                    const uint64_t dAh = umma_desc(aHi + j * 32), dAl = umma_desc(aLo + j * 32);
+                    const uint64_t dBh = umma_desc(bHi + j * 32), dBl = umma_desc(bLo + j * 32);
+                    umma_tf32(tmem_base, dAh, dBh, idesc, (it | j) != 0);
+                    umma_tf32(tmem_base, dAh, dBl, idesc, 1);
+                    umma_tf32(tmem_base, dAl, dBh, idesc, 1);
+                }
+                umma_commit(barEmpty + 8 * s);
+            }
+            umma_commit(barDone);
+        }
+    }
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+    }
+}
+
+// weight image: [ntile][stage][hi|lo][BN x 32] tiles, pre-split and pre-swizzled so that one bulk copy per stage
+// lands a ready-to-use UMMA operand.  K index k = 32*stage + col is the flattened (input, feature) row of wcat.
+__global__ void __launch_bounds__(256) kl_tc_pack_kernel(KLLayout L, float* blob) {
+    const int BN = L.tc_BN;
+    const long long per_tile = (long long)BN * BK;
+    const long long n = (long long)L.tc_ntile * L.tc_stages * per_tile;
+    const long long KF = (long long)L.I * L.F;
+    const float* wcat = blob + L.wcat;
+    float* dst = blob + L.tc;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(idx % BK);
+        const int row = (int)((idx / BK) % BN);
+        const long long ts = idx / per_tile;                      // ntile * stages + stage
+        const int stage = (int)(ts % L.tc_stages), nt = (int)(ts / L.tc_stages);
+        const long long k = (long long)stage * BK + c;
+        const int o = nt * BN + row;
+        float w = 0.f;
+        if (k < KF && o < L.O) w = wcat[k * L.O + o];
+        const float hi = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
+        float* tile = dst + ts * 2 * per_tile;
+        tile[swz(row, c)] = hi;
+        tile[per_tile + swz(row, c)] = w - hi;
+    }
+}
+
+template <int NB, int BR>
+static int tc_launch_k(const TCArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
+    auto k = kl_tc_fwd_kernel<NB, BR>;
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e) return (int)e;
+    k<<<grid, THREADS, smem, st>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+}  // namespace tc
+
+int kl_tc_pack(const KLLayout& L, float* blob, cudaStream_t st) {
+    if (!L.tc_ok) return FETODE_OK;
+    const long long n = (long long)L.tc_ntile * L.tc_stages * L.tc_BN * tc::BK;
+    const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 8);
+    tc::kl_tc_pack_kernel<<<blocks, 256, 0, st>>>(L, blob);
+    return FETODE_LAUNCH_RC();
+}
+
+// returns FETODE_EUNSUPPORTED when the caller should use the CUDA-core path instead
+int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
+              int prev_is_zero, float* y, long long B, cudaStream_t st) {
+    if (!L.tc_ok) return FETODE_EUNSUPPORTED;
+    tc::TCArgs a{};
+    a.blob = blob; a.wtc = blob + L.tc; a.x = x; a.prev = prev; a.y = y; a.B = B; a.L = L;
+    a.gl = P->gate_slope * FETODE_LOG2E;
+    a.prev_is_zero = prev_is_zero; a.BN = L.tc_BN; a.units_total = L.tc_units; a.stages_total = L.tc_stages;
+    const long long mt = (B + tc::BM - 1) / tc::BM;
+    if (mt > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
+    long long splits = std::max(1LL, 148LL / (mt * L.tc_ntile));
+    splits = std::min<long long>(splits, L.tc_units);
+    a.units_per_split = (int)((L.tc_units + splits - 1) / splits);
+    splits = (L.tc_units + a.units_per_split - 1) / a.units_per_split;
+    if (splits > 1) {
+        cudaError_t e = cudaMemsetAsync(y, 0, (size_t)B * L.O * sizeof(float), st);
+        if (e) return (int)e;
+    }
+    const size_t smem = (size_t)tc::NSTAGE * 2 * (tc::BM * tc::BK * 4 + (size_t)L.tc_BN * tc::BK * 4) + 1024 + 256;
+    const dim3 grid((unsigned)mt, (unsigned)L.tc_ntile, (unsigned)splits);
+    switch (P->branch) {
+        case FETODE_BRANCH_NONE: return tc::tc_launch_k<0, FETODE_BRANCH_NONE>(a, grid, smem, st);
+        case FETODE_BRANCH_LOGISTIC:
+            if (L.NB == 10) return tc::tc_launch_k<10, FETODE_BRANCH_LOGISTIC>(a, grid, smem, st);
+            if (L.NB == 8) return tc::tc_launch_k<8, FETODE_BRANCH_LOGISTIC>(a, grid, smem, st);
+            break;
+        case FETODE_BRANCH_FERRO2D:
+            if (L.NB == 10) return tc::tc_launch_k<10, FETODE_BRANCH_FERRO2D>(a, grid, smem, st);
+            break;
+    }
+    return FETODE_EUNSUPPORTED;
+}
+
+}  // namespace fetode
