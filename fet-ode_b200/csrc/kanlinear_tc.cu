@@ -19,12 +19,13 @@
 //   warp 4     lane 0: cp.async.bulk of the pre-split, pre-swizzled weight stage (hi+lo) into the B ring;
 //              whole warp: TMEM alloc / dealloc
 //   warp 5     lane 0: tcgen05.mma issue (12 per 32-wide K stage), tcgen05.commit to release ring slots
+#include <cstdlib>
 #include "kanlinear.cuh"
 
 namespace fetode {
 namespace tc {
 
-constexpr int BM = 128, BK = 32, NSTAGE = 3, THREADS = 192;
+constexpr int BM = 128, BK = 32, NSTAGE = 3;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -91,10 +92,12 @@ struct TCArgs {
 };
 
 
-// all F = 9 + NB features of one (row, input) pair in registers: [silu | N_0..N_7 | r_0..r_{NB-1}]
-template <int NB, int BR>
-__device__ __forceinline__ void tc_features(float x, float prev, float gl, const float* __restrict__ tab,
-                                            const KLLayout& L, float* f) {
+// The K axis is ordered per group of 4 inputs as [ (input ii, silu | N_0..N_7) x 4 | (input ii, r_0..r_{NB-1}) x 4 ]
+// (the weight image is permuted to match, kl_tc_pack_kernel), so that the 9 spline-side chunks and the NB
+// branch-side chunks of a group are produced by two different sets of warps.
+
+// silu and the dense cubic B-spline row of one (row, input) pair: f[0..8]
+__device__ __forceinline__ void tc_spline_features(float x, const float* __restrict__ tab, const KLLayout& L, float* f) {
     f[0] = x * rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));                     // efficientkan.py:166
     int m = -1;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
@@ -111,18 +114,22 @@ __device__ __forceinline__ void tc_features(float x, float prev, float gl, const
         for (int c = 0; c < 4; ++c) r = (s == m - 3 + c) ? v[c] : r;
         f[1 + s] = (m >= 0) ? r : 0.f;
     }
-    if constexpr (NB > 0) {
-        float omu = 0.f;
-        if constexpr (BR == FETODE_BRANCH_FERRO2D) omu = rcp_approx(1.0f + ex2_approx(gl * (x - prev)));
-        float r[NB];
-        branch_eval<NB, BR>(x, omu, gl, reinterpret_cast<const float4*>(tab + L.t_bp), r);
+}
+
+// the NB branch-basis factors of one (row, input) pair (LogisticBasis efficientkan.py:20-24 or the 2-D ferro neuron)
+template <int NB, int BR>
+__device__ __forceinline__ void tc_branch_features(float x, float prev, float gl, const float* __restrict__ tab,
+                                                   const KLLayout& L, float* f) {
+    float omu = 0.f;
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) omu = rcp_approx(1.0f + ex2_approx(gl * (x - prev)));
+    float r[NB > 0 ? NB : 1];
+    branch_eval<NB, BR>(x, omu, gl, reinterpret_cast<const float4*>(tab + L.t_bp), r);
 #pragma unroll
-        for (int j = 0; j < NB; ++j) f[9 + j] = r[j];
-    }
+    for (int j = 0; j < NB; ++j) f[j] = r[j];
 }
 
 template <int NB, int BR>
-__global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
+__global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const TCArgs a) {
     constexpr int F = 9 + NB;
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const int BN = a.BN;
@@ -143,18 +150,18 @@ __global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
     const int nunits = min(a.units_per_split, a.units_total - unit0);
     const int nit = nunits * F;                                   // 32-wide K stages of this CTA
     const int stage0 = unit0 * F;
-    const uint32_t tmem_cols = BN < 32 ? 32u : (uint32_t)BN;
+    const uint32_t tmem_cols = 4 * BN < 32 ? 32u : (uint32_t)(4 * BN);   // 3 rotating main accumulators + 1 correction
 
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(barFullA + 8 * s, 128);
+            mbar_init(barFullA + 8 * s, 128 * (NB > 0 ? 2 : 1));
             mbar_init(barFullB + 8 * s, 1);
             mbar_init(barEmpty + 8 * s, 1);
         }
         mbar_init(barDone, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) {
+    if (warp == (NB > 0 ? 8 : 4)) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      ::"r"(smem_u32((const void*)tmem_slot)), "r"(tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -164,9 +171,12 @@ __global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 4) {
+    constexpr int NSETS = NB > 0 ? 2 : 1;
+    constexpr int TMA_WARP = 4 * NSETS, MMA_WARP = TMA_WARP + 1;
+    if (warp < 4 * NSETS) {
         // ===================== producers: A operand =====================
-        const int r = tid;
+        const int set = warp >> 2;
+        const int r = tid & 127;
         const long long b = m0 + r;
         const bool live = b < a.B;
         const KLLayout& L = a.L;
@@ -176,67 +186,96 @@ __global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
         const bool has_prev = BR == FETODE_BRANCH_FERRO2D && !a.prev_is_zero;
         const uint32_t rowoff = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
         const uint32_t rx = (uint32_t)(r & 7);
-        int it = 0, cs = 0;                                      // stage iteration, 16-byte chunk inside the stage
+        int cur = -1;                                            // stage this thread has acquired and not yet published
         uint32_t dstA = 0;
-        for (int u = 0; u < nunits; ++u) {
+        // every thread visits every stage in order: acquire (empty barrier), write its own chunks, publish
+        auto advance = [&](int target) {
+            while (cur < target) {
+                if (cur >= 0) { fence_proxy_async(); mbar_arrive(barFullA + 8 * (cur % NSTAGE)); }
+                ++cur;
+                mbar_wait(barEmpty + 8 * (cur % NSTAGE), ((cur / NSTAGE) & 1) ^ 1);
+                dstA = base + offA + (uint32_t)(cur % NSTAGE) * 2 * A_TILE + rowoff;
+            }
+        };
+        auto put = [&](int q, const float* v4) {                 // 16-byte chunk q of this CTA's K stream
+            const int t = q >> 3;
+            if (t != cur) advance(t);
+            float hi[4], lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                hi[e] = __uint_as_float(__float_as_uint(v4[e]) & 0xffffe000u);
+                lo[e] = v4[e] - hi[e];
+            }
+            const uint32_t addr = dstA + ((((uint32_t)q & 7u) ^ rx) << 4);
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + A_TILE), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
+        };
+        const int ngroups = nunits * 8;
+        if (set == 0) {
 #pragma unroll 1
-            for (int g = 0; g < 8; ++g) {
-                const int i0 = (unit0 + u) * 32 + g * 4;
-                float f[4 * F];
+            for (int gg = 0; gg < ngroups; ++gg) {
+                const int i0 = (unit0 * 8 + gg) * 4;
+                float f[36];
 #pragma unroll
                 for (int ii = 0; ii < 4; ++ii) {
                     const int i = i0 + ii;
-                    const bool ok = live && i < I;
-                    const float x = ok ? __ldg(xrow + i) : 0.f;
-                    const float pv = (ok && has_prev) ? __ldg(prow + i) : 0.f;
-                    tc_features<NB, BR>(x, pv, a.gl, a.blob + L.tab + (size_t)(i < I ? i : 0) * L.TAB, L, f + ii * F);
+                    const float x = (live && i < I) ? __ldg(xrow + i) : 0.f;
+                    tc_spline_features(x, a.blob + L.tab + (size_t)(i < I ? i : 0) * L.TAB, L, f + ii * 9);
                 }
 #pragma unroll
-                for (int c = 0; c < F; ++c) {
-                    if (cs == 0) {
-                        const int s = it % NSTAGE;
-                        mbar_wait(barEmpty + 8 * s, ((it / NSTAGE) & 1) ^ 1);
-                        dstA = base + offA + (uint32_t)s * 2 * A_TILE + rowoff;
-                    }
-                    float hi[4], lo[4];
+                for (int c = 0; c < 9; ++c) put(gg * F + c, f + 4 * c);
+            }
+        } else {
+            if constexpr (NB > 0) {
+#pragma unroll 1
+                for (int gg = 0; gg < ngroups; ++gg) {
+                    const int i0 = (unit0 * 8 + gg) * 4;
+                    float f[4 * NB];
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float v = f[4 * c + e];
-                        hi[e] = __uint_as_float(__float_as_uint(v) & 0xffffe000u);
-                        lo[e] = v - hi[e];
+                    for (int ii = 0; ii < 4; ++ii) {
+                        const int i = i0 + ii;
+                        const bool ok = live && i < I;
+                        const float x = ok ? __ldg(xrow + i) : 0.f;
+                        const float pv = (ok && has_prev) ? __ldg(prow + i) : 0.f;
+                        tc_branch_features<NB, BR>(x, pv, a.gl, a.blob + L.tab + (size_t)(i < I ? i : 0) * L.TAB, L, f + ii * NB);
                     }
-                    const uint32_t addr = dstA + ((((uint32_t)cs) ^ rx) << 4);
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + A_TILE), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
-                    if (++cs == 8) {
-                        fence_proxy_async();
-                        mbar_arrive(barFullA + 8 * (it % NSTAGE));
-                        cs = 0;
-                        ++it;
-                    }
+#pragma unroll
+                    for (int c = 0; c < NB; ++c) put(gg * F + 9 + c, f + 4 * c);
                 }
             }
         }
+        advance(nit - 1);
+        fence_proxy_async();
+        mbar_arrive(barFullA + 8 * (cur % NSTAGE));
         // ===================== epilogue =====================
         mbar_wait(barDone, 0);
         tc_fence_after();
         const float* bias = a.blob + L.bias;
         const int O = L.O, n0 = ntile * BN;
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-            uint32_t v[16];
-            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                : "r"(taddr) : "memory");
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int nacc = nit < 3 ? nit : 3;
+        for (int c0 = 16 * set; c0 < BN; c0 += 16 * NSETS) {
+            float acc[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) acc[e] = 0.f;
+            for (int q = 0; q <= nacc; ++q) {                     // q == nacc: the correction accumulator
+                uint32_t v[16];
+                const uint32_t col = (uint32_t)((q == nacc ? 3 : q) * BN + c0);
+                const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + col;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                    : "r"(taddr) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int e = 0; e < 16; ++e) acc[e] += __uint_as_float(v[e]);
+            }
             if (live) {
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
                     const int n = n0 + c0 + e;
                     if (n < O) {
-                        const float val = __uint_as_float(v[e]);
+                        const float val = acc[e];
                         if (gridDim.z == 1) a.y[b * O + n] = val + bias[n];
                         else atomicAdd(a.y + b * O + n, split == 0 ? val + bias[n] : val);
                     }
@@ -244,7 +283,7 @@ __global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
             }
         }
         tc_fence_before();
-    } else if (warp == 4) {
+    } else if (warp == TMA_WARP) {
         // ===================== TMA: B operand =====================
         if (lane == 0) {
             const uint32_t bytes = 2 * B_TILE;
@@ -272,9 +311,13 @@ __global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
                 for (int j = 0; j < BK / 8; ++j) {
                     const uint64_t dAh = umma_desc(aHi + j * 32), dAl = umma_desc(aLo + j * 32);
                     const uint64_t dBh = umma_desc(bHi + j * 32), dBl = umma_desc(bLo + j * 32);
-                    umma_tf32(tmem_base, dAh, dBh, idesc, (it | j) != 0);
-                    umma_tf32(tmem_base, dAh, dBl, idesc, 1);
-                    umma_tf32(tmem_base, dAl, dBh, idesc, 1);
+                    // The tensor core truncates when it adds into the fp32 accumulator, so the error of a chain grows
+                    // linearly with its length (measured: 4.5e-6 of the max-norm per 228 MMAs).  The hi*hi products
+                    // rotate over three accumulators and the 2^-11-times-smaller corrections go to a fourth; the
+                    // epilogue adds the four in registers (round-to-nearest).
+                    umma_tf32(tmem_base + (uint32_t)((it % 3) * BN), dAh, dBh, idesc, !(it < 3 && j == 0));
+                    umma_tf32(tmem_base + (uint32_t)(3 * BN), dAh, dBl, idesc, (it | j) != 0);
+                    umma_tf32(tmem_base + (uint32_t)(3 * BN), dAl, dBh, idesc, 1);
                 }
                 umma_commit(barEmpty + 8 * s);
             }
@@ -282,7 +325,7 @@ __global__ void __launch_bounds__(THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
         }
     }
     __syncthreads();
-    if (warp == 4) {
+    if (warp == (NB > 0 ? 8 : 4)) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
     }
@@ -302,10 +345,16 @@ __global__ void __launch_bounds__(256) kl_tc_pack_kernel(KLLayout L, float* blob
         const int row = (int)((idx / BK) % BN);
         const long long ts = idx / per_tile;                      // ntile * stages + stage
         const int stage = (int)(ts % L.tc_stages), nt = (int)(ts / L.tc_stages);
-        const long long k = (long long)stage * BK + c;
+        // position in the CTA K stream -> (input, feature) row of wcat (see the ordering note above tc_spline_features)
+        const long long kpos = (long long)stage * BK + c;
+        const long long grp = kpos / (4 * L.F);
+        const int p = (int)(kpos % (4 * L.F));
+        const int ii = p < 36 ? p / 9 : (p - 36) / (L.NB > 0 ? L.NB : 1);
+        const int f = p < 36 ? p % 9 : 9 + (p - 36) % (L.NB > 0 ? L.NB : 1);
+        const long long k = (grp * 4 + ii) * L.F + f;
         const int o = nt * BN + row;
         float w = 0.f;
-        if (k < KF && o < L.O) w = wcat[k * L.O + o];
+        if (grp * 4 + ii < L.I && k < KF && o < L.O) w = wcat[k * L.O + o];
         const float hi = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
         float* tile = dst + ts * 2 * per_tile;
         tile[swz(row, c)] = hi;
@@ -318,7 +367,7 @@ static int tc_launch_k(const TCArgs& a, dim3 grid, size_t smem, cudaStream_t st)
     auto k = kl_tc_fwd_kernel<NB, BR>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e) return (int)e;
-    k<<<grid, THREADS, smem, st>>>(a);
+    k<<<grid, NB > 0 ? 320 : 192, smem, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 
@@ -345,6 +394,11 @@ int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, 
     long long splits = std::max(1LL, 148LL / (mt * L.tc_ntile));
     splits = std::min<long long>(splits, L.tc_units);
     a.units_per_split = (int)((L.tc_units + splits - 1) / splits);
+    a.units_per_split = std::min(a.units_per_split, 6);        // bounds the accumulation chains (see the MMA loop)
+    if (const char* e = getenv("FETODE_TC_UPS")) {         // tuning / diagnostics: 32-input units per K split
+        const int v = atoi(e);
+        if (v >= 1) a.units_per_split = std::min(v, L.tc_units);
+    }
     splits = (L.tc_units + a.units_per_split - 1) / a.units_per_split;
     if (splits > 1) {
         cudaError_t e = cudaMemsetAsync(y, 0, (size_t)B * L.O * sizeof(float), st);

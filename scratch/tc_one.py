@@ -1,0 +1,13 @@
+import os, sys
+sys.path[:0] = ["/root/repo", "/root/repo/fet-ode_b200"]
+os.environ["FETODE_TC"] = "1"
+import torch, fetode
+dev = torch.device("cuda:0")
+torch.manual_seed(0)
+layer = fetode.KANLinear(768, 128, num_basis=10).to(dev)
+x = torch.randn(4096, 768, device=dev)
+with torch.no_grad():
+    for _ in range(4):
+        y = layer(x)
+torch.cuda.synchronize()
+print("ok", float(y.abs().max()))
