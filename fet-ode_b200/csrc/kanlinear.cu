@@ -54,8 +54,12 @@ __global__ void kl_pack_kernel(fetode_kanlayer_t P, KLLayout L, float* blob) {
         blob[L.bias + o] = (float)b;
     }
     // per-input tables
-    for (long long i = tid; i < I; i += nt) {
+    for (long long i = tid; i < L.tab_rows; i += nt) {
         float* t = blob + L.tab + i * L.TAB;
+        if (i >= I) {                                   // padding rows: finite features, never inside a grid
+            for (int q = 0; q < L.TAB; ++q) t[q] = 0.f;
+            continue;
+        }
         pack_knots_row(P.grid + (size_t)i * L.NK, L.NK, L.NKP, t + L.t_kn, t + L.t_rd1, t + L.t_rd2, t + L.t_rd3,
                        t + L.t_gi);
         for (int j = 0; j < NB; ++j) reinterpret_cast<float4*>(t + L.t_bp)[j] = branch_params(P, (int)i * NB + j);

@@ -11,7 +11,7 @@ namespace fetode {
 //   bias [O]        branch_bias + the input-independent part of the folded FERRO2D branch
 //   tab  [I, TAB]   per input: padded knots kp[NKP], 1/(kp[j+p]-kp[j]) p=1..3, gi[4], bp[NB][4]
 struct KLLayout {
-    int I, O, G, NB, S, F, NK, NKP, TAB;
+    int I, O, G, NB, S, F, NK, NKP, TAB, tab_rows;
     int t_kn, t_rd1, t_rd2, t_rd3, t_gi, t_bp;
     long long wcat, bias, tab, total;
     // tensor-core weight image (kanlinear_tc.cu); tc_ok == 0 when the shape is served by the CUDA-core kernels only
@@ -37,8 +37,9 @@ __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
     long long o = 0;
     L.wcat = o; o += ((long long)I * L.F * O + 3) / 4 * 4;
     L.bias = o; o += (O + 3) / 4 * 4;
-    L.tab = o; o += (long long)I * L.TAB;
-    L.tc_ok = (G == 5 && (NB == 0 || NB == 8 || NB == 10) && (long long)I * L.F >= 1024 && O >= 8) ? 1 : 0;
+    L.tc_ok = (G == 5 && (NB == 0 || NB == 8 || NB == 10) && (long long)I * L.F >= 1024 && O >= 8 && I % 4 == 0) ? 1 : 0;
+    L.tab_rows = L.tc_ok ? round_up(I, 32) : I;          // the tcgen05 kernel streams whole 32-input slabs of the table
+    L.tab = o; o += (long long)L.tab_rows * L.TAB;
     L.tc = 0;
     if (L.tc_ok) {
         L.tc_BN = O <= 16 ? 16 : (O <= 32 ? 32 : (O <= 64 ? 64 : 128));

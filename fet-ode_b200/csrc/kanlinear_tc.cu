@@ -129,7 +129,7 @@ __device__ __forceinline__ void tc_branch_features(float x, float prev, float gl
 }
 
 template <int NB, int BR>
-__global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const TCArgs a) {
+__global__ void __launch_bounds__(NB > 0 ? 352 : 224, 1) kl_tc_fwd_kernel(const TCArgs a) {
     constexpr int F = 9 + NB;
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const int BN = a.BN;
@@ -138,10 +138,12 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const 
     unsigned char* gbase = tc_smem_raw + (base - smem_u32(tc_smem_raw));
     constexpr uint32_t A_TILE = BM * BK * 4;                     // 16 KB
     const uint32_t B_TILE = (uint32_t)BN * BK * 4;
-    const uint32_t offA = 0, offB = NSTAGE * 2 * A_TILE, offBar = offB + NSTAGE * 2 * B_TILE;
+    const uint32_t TAB_SLAB = (uint32_t)(32 * a.L.TAB * 4);        // per-input tables of one 32-input unit
+    const uint32_t offA = 0, offB = NSTAGE * 2 * A_TILE, offTab = offB + NSTAGE * 2 * B_TILE, offBar = offTab + 2 * TAB_SLAB;
     const uint32_t barFullA = base + offBar, barFullB = barFullA + 8 * NSTAGE, barEmpty = barFullB + 8 * NSTAGE,
-                   barDone = barEmpty + 8 * NSTAGE;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + offBar + 8 * (3 * NSTAGE + 1));
+                   barDone = barEmpty + 8 * NSTAGE, barTabFull = barDone + 8, barTabEmpty = barTabFull + 16;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + offBar + 8 * (3 * NSTAGE + 1 + 4));
+    const float* tabs = reinterpret_cast<const float*>(gbase + offTab);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long long m0 = (long long)blockIdx.x * BM;
@@ -159,6 +161,10 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const 
             mbar_init(barEmpty + 8 * s, 1);
         }
         mbar_init(barDone, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(barTabFull + 8 * s, 1);
+            mbar_init(barTabEmpty + 8 * s, 128 * (NB > 0 ? 2 : 1));
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == (NB > 0 ? 8 : 4)) {
@@ -172,7 +178,7 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const 
     const uint32_t tmem_base = *tmem_slot;
 
     constexpr int NSETS = NB > 0 ? 2 : 1;
-    constexpr int TMA_WARP = 4 * NSETS, MMA_WARP = TMA_WARP + 1;
+    constexpr int TMA_WARP = 4 * NSETS, MMA_WARP = TMA_WARP + 1, TAB_WARP = MMA_WARP + 1;
     if (warp < 4 * NSETS) {
         // ===================== producers: A operand =====================
         const int set = warp >> 2;
@@ -211,36 +217,50 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const 
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + A_TILE), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
         };
         const int ngroups = nunits * 8;
+        // 4 consecutive inputs of this row (16-byte aligned: I % 4 == 0), zeros for padding inputs / rows
+        auto ldx = [&](const float* rowp, int i) -> float4 {
+            if (!live || i >= I) return make_float4(0.f, 0.f, 0.f, 0.f);
+            return __ldg(reinterpret_cast<const float4*>(rowp + i));
+        };
         if (set == 0) {
 #pragma unroll 1
+            float4 xn = ldx(xrow, unit0 * 32);
             for (int gg = 0; gg < ngroups; ++gg) {
-                const int i0 = (unit0 * 8 + gg) * 4;
+                const int u = gg >> 3, g = gg & 7;
+                if (g == 0) mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
+                const float4 xc = xn;
+                if (gg + 1 < ngroups) xn = ldx(xrow, (unit0 * 8 + gg + 1) * 4);
+                const float xs[4] = {xc.x, xc.y, xc.z, xc.w};
+                const float* tg = tabs + (size_t)((u & 1) * 32 + g * 4) * L.TAB;
                 float f[36];
 #pragma unroll
-                for (int ii = 0; ii < 4; ++ii) {
-                    const int i = i0 + ii;
-                    const float x = (live && i < I) ? __ldg(xrow + i) : 0.f;
-                    tc_spline_features(x, a.blob + L.tab + (size_t)(i < I ? i : 0) * L.TAB, L, f + ii * 9);
-                }
+                for (int ii = 0; ii < 4; ++ii) tc_spline_features(xs[ii], tg + ii * L.TAB, L, f + ii * 9);
 #pragma unroll
                 for (int c = 0; c < 9; ++c) put(gg * F + c, f + 4 * c);
+                if (g == 7) mbar_arrive(barTabEmpty + 8 * (u & 1));
             }
         } else {
             if constexpr (NB > 0) {
 #pragma unroll 1
+                float4 xn = ldx(xrow, unit0 * 32);
+                float4 pn = has_prev ? ldx(prow, unit0 * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
                 for (int gg = 0; gg < ngroups; ++gg) {
-                    const int i0 = (unit0 * 8 + gg) * 4;
+                    const int u = gg >> 3, g = gg & 7;
+                    if (g == 0) mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
+                    const float4 xc = xn, pc = pn;
+                    if (gg + 1 < ngroups) {
+                        xn = ldx(xrow, (unit0 * 8 + gg + 1) * 4);
+                        if (has_prev) pn = ldx(prow, (unit0 * 8 + gg + 1) * 4);
+                    }
+                    const float xs[4] = {xc.x, xc.y, xc.z, xc.w}, ps[4] = {pc.x, pc.y, pc.z, pc.w};
+                    const float* tg = tabs + (size_t)((u & 1) * 32 + g * 4) * L.TAB;
                     float f[4 * NB];
 #pragma unroll
-                    for (int ii = 0; ii < 4; ++ii) {
-                        const int i = i0 + ii;
-                        const bool ok = live && i < I;
-                        const float x = ok ? __ldg(xrow + i) : 0.f;
-                        const float pv = (ok && has_prev) ? __ldg(prow + i) : 0.f;
-                        tc_branch_features<NB, BR>(x, pv, a.gl, a.blob + L.tab + (size_t)(i < I ? i : 0) * L.TAB, L, f + ii * NB);
-                    }
+                    for (int ii = 0; ii < 4; ++ii)
+                        tc_branch_features<NB, BR>(xs[ii], ps[ii], a.gl, tg + ii * L.TAB, L, f + ii * NB);
 #pragma unroll
                     for (int c = 0; c < NB; ++c) put(gg * F + 9 + c, f + 4 * c);
+                    if (g == 7) mbar_arrive(barTabEmpty + 8 * (u & 1));
                 }
             }
         }
@@ -293,6 +313,16 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_fwd_kernel(const 
                 mbar_wait(barEmpty + 8 * s, ((it / NSTAGE) & 1) ^ 1);
                 mbar_arrive_expect_tx(barFullB + 8 * s, bytes);
                 bulk_g2s(base + offB + (uint32_t)s * 2 * B_TILE, src + (size_t)it * (2 * BN * BK), bytes, barFullB + 8 * s);
+            }
+        }
+    } else if (warp == TAB_WARP) {
+        // ===================== TMA: per-input tables of the next unit =====================
+        if (lane == 0) {
+            const float* src = a.blob + a.L.tab + (size_t)unit0 * 32 * a.L.TAB;
+            for (int u = 0; u < nunits; ++u) {
+                mbar_wait(barTabEmpty + 8 * (u & 1), ((u >> 1) & 1) ^ 1);
+                mbar_arrive_expect_tx(barTabFull + 8 * (u & 1), TAB_SLAB);
+                bulk_g2s(base + offTab + (uint32_t)(u & 1) * TAB_SLAB, src + (size_t)u * 32 * a.L.TAB, TAB_SLAB, barTabFull + 8 * (u & 1));
             }
         }
     } else {
@@ -367,7 +397,7 @@ static int tc_launch_k(const TCArgs& a, dim3 grid, size_t smem, cudaStream_t st)
     auto k = kl_tc_fwd_kernel<NB, BR>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e) return (int)e;
-    k<<<grid, NB > 0 ? 320 : 192, smem, st>>>(a);
+    k<<<grid, NB > 0 ? 352 : 224, smem, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 
@@ -404,7 +434,8 @@ int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, 
         cudaError_t e = cudaMemsetAsync(y, 0, (size_t)B * L.O * sizeof(float), st);
         if (e) return (int)e;
     }
-    const size_t smem = (size_t)tc::NSTAGE * 2 * (tc::BM * tc::BK * 4 + (size_t)L.tc_BN * tc::BK * 4) + 1024 + 256;
+    const size_t smem = (size_t)tc::NSTAGE * 2 * (tc::BM * tc::BK * 4 + (size_t)L.tc_BN * tc::BK * 4) + (size_t)2 * 32 * L.TAB * 4 + 1024 + 256;
+    if (((uintptr_t)x & 15) || (prev && ((uintptr_t)prev & 15))) return FETODE_EUNSUPPORTED;
     const dim3 grid((unsigned)mt, (unsigned)L.tc_ntile, (unsigned)splits);
     switch (P->branch) {
         case FETODE_BRANCH_NONE: return tc::tc_launch_k<0, FETODE_BRANCH_NONE>(a, grid, smem, st);

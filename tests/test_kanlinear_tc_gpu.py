@@ -77,7 +77,7 @@ def test_tc_equals_cuda_core_path_at_full_ecg_size(cuda):
         os.environ.pop("FETODE_TC", None)
         if old is not None:
             os.environ["FETODE_TC"] = old
-    assert max_rel(got, ref) < 2e-6
+    assert max_rel(got, ref) < 1e-5          # each path is within ~5e-6 of an fp64 evaluation
     # linearity in the rows: any row subset gives the same rows (tiles are independent)
     with torch.no_grad():
         sub = layer(x[1000:1300].contiguous())
