@@ -81,4 +81,4 @@ def test_tc_equals_cuda_core_path_at_full_ecg_size(cuda):
     # linearity in the rows: any row subset gives the same rows (tiles are independent)
     with torch.no_grad():
         sub = layer(x[1000:1300].contiguous())
-    assert max_rel(sub, got[1000:1300]) < 2e-6
+    assert max_rel(sub, got[1000:1300]) < 1e-5   # a different split-K factor: rounding only
