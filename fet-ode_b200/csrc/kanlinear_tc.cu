@@ -12,13 +12,19 @@
 // x = hi + lo (hi = top 19 bits, lo = x - hi exactly) and three MMAs are issued per K-slice,
 // hi*hi + hi*lo + lo*hi, accumulating in fp32 in TMEM; the dropped lo*lo term is ~2^-22 relative.
 //
-// CTA = 128 rows x BN outputs x one contiguous range of 32-input units (split-K over the grid's z axis).
-//   warps 0-3  producers: thread r owns row r; per group of 4 inputs it evaluates 4*F features, splits them and
-//              stores 16-byte chunks (conflict-free under the 128B swizzle) into the A ring; afterwards the same
-//              warps are the epilogue (TMEM lane quarter == warp index): tcgen05.ld -> (+bias) -> y / atomics
-//   warp 4     lane 0: cp.async.bulk of the pre-split, pre-swizzled weight stage (hi+lo) into the B ring;
-//              whole warp: TMEM alloc / dealloc
-//   warp 5     lane 0: tcgen05.mma issue (12 per 32-wide K stage), tcgen05.commit to release ring slots
+// CTA = 128 rows x BN outputs x one contiguous range of 32-input units (split-K over the grid's z axis, at most 6
+// units per CTA so that the truncating tensor-core accumulation chains stay short -- see the MMA loop).
+//   warps 0-3   producer set 0 (thread r owns row r): silu + dense cubic B-spline row of 4 inputs at a time, split
+//               hi/lo, 16-byte chunks stored conflict-free into the 128B-swizzled A ring
+//   warps 4-7   producer set 1 (NB > 0 only): the NB branch-basis factors of the same 4 inputs (the K axis is
+//               permuted per group of 4 inputs so the two sets own disjoint chunks of every stage)
+//               both sets double as the epilogue (TMEM lane quarter == warp & 3): tcgen05.ld of the 3 rotating
+//               accumulators + the correction accumulator, summed in registers, (+bias) -> y / atomics
+//   next warp   lane 0: cp.async.bulk (TMA bulk engine) of the pre-split, pre-swizzled weight stage (hi+lo) into the
+//               B ring; whole warp: TMEM alloc / dealloc
+//   next warp   lane 0: tcgen05.mma issue (12 per 32-wide K stage), tcgen05.commit releases ring slots
+//   next warp   lane 0: cp.async.bulk of the next unit's per-input tables (knots, reciprocal differences, folded
+//               branch constants: 32 x TAB floats) into a 2-slot shared-memory ring
 #include <cstdlib>
 #include "kanlinear.cuh"
 
