@@ -1,0 +1,180 @@
+#!/usr/bin/env python
+"""Secondary measurements for the BASELINE.json configurations other than the headline ensemble: fwd+bwd(+optimiser)
+step times of the training configurations on one B200 next to the reference's CPU arithmetic (oracle port, all host
+cores) on a bounded sample.  One JSON object per configuration; `python bench.py` stays the driver's contract.
+
+    python bench_configs.py [--skip-cpu]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "fet-ode_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+import torch  # noqa: E402
+import torch.nn.functional as F  # noqa: E402
+
+import fetode  # noqa: E402
+from fetode import ecg, mnist_kuramoto_kan as MK  # noqa: E402
+
+DEV = torch.device("cuda:0")
+
+
+def gpu_ms(step, iters=5, warm=3):
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def cpu_ms(step, iters=2, warm=1):
+    for _ in range(warm):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        step()
+    return 1e3 * (time.perf_counter() - t0) / iters
+
+
+def layers_of(model):
+    sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()
+          if k.split(".")[-1] not in ("prev_x", "branch_sign", "branch_state")}
+    n = len(model.layers)
+    return [{k[len(f"layers.{i}."):]: v.requires_grad_(v.is_floating_point() and not k.endswith("grid"))
+             for k, v in sd.items() if k.startswith(f"layers.{i}.")} for i in range(n)]
+
+
+def lv_train(B, skip_cpu):
+    from oracle import layers as OL, solvers as OS
+    torch.manual_seed(0)
+    model = fetode.KANFET([2, 10, 2], grid_size=5)
+    lay = layers_of(model)
+    model = model.to(DEV)
+    opt = torch.optim.Adam(model.parameters(), lr=2e-3)
+    n, T = 34, 3.5
+    t = torch.linspace(0, T, n + 1, dtype=torch.float64)
+    gen = torch.Generator().manual_seed(1)
+    x0 = (torch.rand(B, 2, generator=gen) * 6.75 + 0.25) if B > 1 else torch.ones(1, 2)
+    target = torch.randn(n + 1, B, 2, generator=gen)
+    x0d, tgt = x0.to(DEV), target.to(DEV)
+
+    def step():
+        model.reset_state()
+        opt.zero_grad(set_to_none=True)
+        pred = fetode.odeint(lambda tt, X: model(X), x0d, t, method="rk4_classic")
+        ((pred - tgt) ** 2).mean().backward()
+        opt.step()
+    out = {"config": f"1: LV KANFET([2,10,2]) NODE training, classic RK4 x {n}, MSE, Adam (train_kanfet_node_predprey.py), B={B}",
+           "gpu_fwd_bwd_opt_ms": gpu_ms(step), "traj_steps": B * n}
+    out["gpu_traj_steps_per_s"] = B * n / out["gpu_fwd_bwd_opt_ms"] * 1e3
+    if not skip_cpu:
+        Bc = min(B, 2048)
+        params = [v for l in lay for v in l.values() if v.requires_grad]
+
+        def cstep():
+            for p in params:
+                p.grad = None
+            states = OL.kanfet_states(lay)
+            f = lambda tt, h: OL.kan_forward(h, lay, branch="ferro2d", states=states)
+            pred = OS.rk4_classic(f, x0[:Bc], 0.0, T, n, trajectory=True)
+            ((pred - target[:, :Bc]) ** 2).mean().backward()
+        ms = cpu_ms(cstep)
+        out.update(cpu_fwd_bwd_ms=ms, cpu_rows=Bc, cpu_traj_steps_per_s=Bc * n / ms * 1e3, cpu_cores=os.cpu_count())
+    return out
+
+
+def ecg_train(B, skip_cpu):
+    torch.manual_seed(0)
+    model = ecg.KanFet_MLP_NODE(T=96, num_classes=2, latent_dim=64, num_basis=12, ode_hidden=128, dropout=0.0)
+    model.ode_method = "rk4_classic"
+    model = model.to(DEV)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+    gen = torch.Generator().manual_seed(1)
+    x = torch.randn(B, 96, generator=gen)
+    x = ((x - x.mean(1, keepdim=True)) / x.std(1, keepdim=True)).to(DEV)
+    y = torch.randint(0, 2, (B,), generator=gen).to(DEV)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        F.cross_entropy(model(x), y).backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+
+    def fwd():
+        with torch.no_grad():
+            model(x)
+    ms, fms = gpu_ms(step, iters=3, warm=2), gpu_ms(fwd, iters=3, warm=2)
+    return {"config": f"3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, AdamW, clip 1.0, B={B}",
+            "gpu_fwd_bwd_opt_ms": ms, "gpu_fwd_ms": fms, "sample_steps_per_s": B * 8 / ms * 1e3}
+
+
+def ett_encoder(B, skip_cpu):
+    from oracle import layers as OL
+    torch.manual_seed(0)
+    enc = torch.nn.Sequential(torch.nn.Flatten(), fetode.KAN([336 * 7, 128]), torch.nn.ReLU(), fetode.KAN([128, 64])).to(DEV)
+    x = torch.randn(B, 336, 7, device=DEV)
+
+    def step():
+        enc.zero_grad(set_to_none=True)
+        enc(x).square().mean().backward()
+
+    def fwd():
+        with torch.no_grad():
+            enc(x)
+    out = {"config": f"4: ETT encoder Flatten -> KAN([2352,128]) -> ReLU -> KAN([128,64]) (train_kan_fet_ett.py:676-681), B={B}",
+           "gpu_fwd_ms": gpu_ms(fwd), "gpu_fwd_bwd_ms": gpu_ms(step, iters=3, warm=2)}
+    if not skip_cpu:
+        Bc = min(B, 256)
+        l1 = {k: v.detach().cpu() for k, v in enc[1].layers[0].state_dict().items()}
+        l2 = {k: v.detach().cpu() for k, v in enc[3].layers[0].state_dict().items()}
+        xc = x[:Bc].reshape(Bc, -1).cpu()
+
+        def cfwd():
+            with torch.no_grad():
+                OL.kanlinear_forward(torch.relu(OL.kanlinear_forward(xc, l1)), l2)
+        ms = cpu_ms(cfwd)
+        out.update(cpu_fwd_ms=ms, cpu_rows=Bc, cpu_fwd_ms_scaled_to_B=ms * B / Bc, cpu_cores=os.cpu_count())
+    return out
+
+
+def mnist_train(B, skip_cpu):
+    torch.manual_seed(0)
+    model = MK.KuramotoKANClassifier(kuramoto_steps=10, num_basis=8).to(DEV)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+    x = torch.rand(B, 1, 28, 28, device=DEV)
+    y = torch.randint(0, 10, (B,), device=DEV)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        F.cross_entropy(model(x), y).backward()
+        opt.step()
+    ms = gpu_ms(step)
+    return {"config": f"5: MNIST KuramotoKANClassifier(steps=10, nb=8), CE, AdamW, B={B}", "gpu_fwd_bwd_opt_ms": ms,
+            "image_steps_per_s": B / ms * 1e3}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--skip-cpu", action="store_true")
+    a = ap.parse_args()
+    torch.set_num_threads(os.cpu_count() or 1)
+    for fn, args in ((lv_train, (1,)), (lv_train, (65536,)), (ecg_train, (4096,)), (ett_encoder, (4096,)),
+                     (ett_encoder, (64,)), (mnist_train, (128,)), (mnist_train, (1024,))):
+        try:
+            print(json.dumps(fn(*args, a.skip_cpu)), flush=True)
+        except Exception as e:                      # keep going: this is a survey, not the contract bench
+            print(json.dumps({"config": f"{fn.__name__}{args}", "error": repr(e)[:300]}), flush=True)
+
+
+if __name__ == "__main__":
+    main()

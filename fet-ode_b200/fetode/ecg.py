@@ -160,3 +160,29 @@ class KANFetODEFunc(nn.Module):
         dh = self.fc2(z)
         dh = torch.nan_to_num(dh, nan=0.0, posinf=1e3, neginf=-1e3)
         return torch.clamp(dh, -50.0, 50.0)
+
+
+class KanFet_MLP_NODE(nn.Module):
+    """train_ecg_kan_fet_nn_ode.py:985-1048: Linear(T -> latent) -> odeint(MLPKANODEFunc, linspace(0,1,9)) ->
+    Dropout -> KANFeatureMixer -> Linear(latent*num_basis -> classes).  The reference hard-codes method="dopri5";
+    ``ode_method`` (default "dopri5") additionally accepts "rk4" / "rk4_classic" / "midpoint" / "euler"."""
+
+    def __init__(self, T: int, num_classes: int, latent_dim: int = 64, num_basis: int = 10, ode_hidden: int = 128,
+                 dropout: float = 0.1, solver: str = "dopri5", rtol: float = 1e-3, atol: float = 1e-4):
+        super().__init__()
+        self.T, self.num_classes, self.latent_dim = T, num_classes, latent_dim
+        self.solver, self.rtol, self.atol = solver, rtol, atol
+        self.ode_method = "dopri5"
+        self.encoder = nn.Linear(T, latent_dim)
+        self.odefunc = MLPKANODEFunc(latent_dim=latent_dim, num_basis=num_basis, hidden=ode_hidden)
+        self.dropout = nn.Dropout(dropout)
+        self.cls_feat = KANFeatureMixer(latent_dim, num_basis, act=nn.Sigmoid())
+        self.cls = nn.Linear(latent_dim * num_basis, num_classes)
+
+    def forward(self, x):
+        from .odeint import odeint
+        h0 = self.encoder(x)
+        t_eval = torch.linspace(0.0, 1.0, 9, device=x.device, dtype=torch.float64)
+        h_traj = odeint(self.odefunc, h0, t_eval, method=self.ode_method, rtol=self.rtol, atol=self.atol)
+        hT = self.dropout(h_traj[-1])
+        return self.cls(self.cls_feat(hT))
