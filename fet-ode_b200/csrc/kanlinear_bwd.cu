@@ -348,7 +348,12 @@ static int kl_bwd_launch(KLBwdArgs& a, cudaStream_t st) {
         if (e) return (int)e;
         e = cudaMemsetAsync(a.ws, 0, ((size_t)L.I * L.F * L.O + L.O) * 4, st);
         if (e) return (int)e;
-        k<<<dim3(ngroups, gy_, (unsigned)split), KB_THREADS, smem, st>>>(a);
+        int rc_tc = FETODE_EUNSUPPORTED;
+        if (a.L.tc_ok && a.B / 4 >= kl_tc_min_rows())           // wide layer: tcgen05 weight gradient (kanlinear_tc_bwd.cu)
+            rc_tc = kl_tc_dw(&a.P, a.L, a.blob, a.x, a.prev, a.prev_is_zero, a.gy, a.ws, a.B, st);
+        if (rc_tc != FETODE_OK && rc_tc != FETODE_EUNSUPPORTED) return rc_tc;
+        if (rc_tc == FETODE_EUNSUPPORTED)
+            k<<<dim3(ngroups, gy_, (unsigned)split), KB_THREADS, smem, st>>>(a);
         const long long by = std::max(1LL, std::min<long long>((a.B + 63) / 64, 64));
         kl_colsum_kernel<<<dim3((L.O + 31) / 32, (unsigned)by), 256, 0, st>>>(a.gy, a.ws + (size_t)L.I * L.F * L.O, a.B, L.O);
     }

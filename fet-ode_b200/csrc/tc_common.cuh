@@ -46,14 +46,15 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // SWIZZLE_128B operand tile made of 1024-byte atoms (8 x 128 B).  K-major: atoms sbo apart along M/N.
-// MN-major: atoms lbo apart along M/N and sbo apart along K (each atom = 32 M/N elements x 8 K rows).
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes = 16, uint32_t sbo_bytes = 1024) {
+// MN-major tf32 operands must use SWIZZLE_128B_BASE32B (layout 1): atoms of 32 M/N elements (128 B) x 4 K rows,
+// 32-byte chunks XOR-ed with the row index; atoms lbo apart along M/N and sbo apart along K.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes = 16, uint32_t sbo_bytes = 1024, uint32_t layout = 2) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3FFFF) >> 4);            // start address
     d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;   // leading byte offset (unused for swizzled K-major)
     d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;   // stride byte offset
     d |= (uint64_t)1 << 46;                             // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;                             // SWIZZLE_128B
+    d |= (uint64_t)layout << 61;                        // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B (MN-major tf32)
     return d;
 }
 // float offset of element (row, col) inside a [rows x 32] swizzled tile
