@@ -233,7 +233,9 @@ extern "C" int fetode_kanlinear_pack(const fetode_kanlayer_t* P, float* wcat, vo
     kl_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(*P, L, wcat);
     rc = FETODE_LAUNCH_RC();
     if (rc) return rc;
-    return kl_tc_pack(L, wcat, (cudaStream_t)stream);
+    rc = kl_tc_pack(L, wcat, (cudaStream_t)stream);
+    if (rc) return rc;
+    return kl_td_pack(L, wcat, (cudaStream_t)stream);
 }
 
 extern "C" int fetode_kanlinear_fwd(const fetode_kanlayer_t* P, const float* wcat, const float* x,

@@ -17,6 +17,9 @@ struct KLLayout {
     // tensor-core weight image (kanlinear_tc.cu); tc_ok == 0 when the shape is served by the CUDA-core kernels only
     int tc_ok, tc_BN, tc_ntile, tc_units, tc_stages;
     long long tc;
+    // input-gradient weight image (kanlinear_tc_dx.cu): [I/4 chunks][ceil(O/32) K slabs][hi|lo][4*td_FP x 32]
+    int td_groups, td_KS, td_FP;
+    long long td;
 };
 
 __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
@@ -49,6 +52,12 @@ __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
         o = (o + 255) / 256 * 256;                       // 1 KB alignment for the bulk copies
         L.tc = o;
         o += (long long)L.tc_ntile * L.tc_stages * 2 * L.tc_BN * 32;
+        L.td_groups = I / 4;
+        L.td_KS = (O + 31) / 32;
+        L.td_FP = NB > 0 ? 20 : 12;
+        o = (o + 255) / 256 * 256;
+        L.td = o;
+        o += (long long)L.td_groups * L.td_KS * 2 * (4 * L.td_FP) * 32;
     }
     L.total = o;
     return L;
@@ -101,6 +110,9 @@ int kl_check(const fetode_kanlayer_t* P);
 int kl_tc_pack(const KLLayout& L, float* blob, cudaStream_t st);
 int kl_tc_dw(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
              int prev_is_zero, const float* gy, float* ws, long long B, cudaStream_t st);
+int kl_tc_dx(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
+             int prev_is_zero, const float* gy, float* gx, float* gbp0, float* gbp1, long long B, cudaStream_t st);
+int kl_td_pack(const KLLayout& L, float* blob, cudaStream_t st);
 long long kl_tc_min_rows();
 int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
               int prev_is_zero, float* y, long long B, cudaStream_t st);

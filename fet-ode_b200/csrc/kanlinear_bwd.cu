@@ -364,10 +364,16 @@ static int kl_bwd_launch(KLBwdArgs& a, cudaStream_t st) {
         gy_ = std::max(1LL, std::min<long long>(gy_, ngroups));
         if (ntile > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
         const size_t smem = (size_t)(KB_OC * KB_GST + KB_KCMAX * (KB_OC + 1) + KB_KCMAX * KB_BM) * 4;
-        auto k = kl_bwd_dx_kernel<BR>;
-        e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e) return (int)e;
-        k<<<dim3((unsigned)ntile, (unsigned)gy_), KB_THREADS, smem, st>>>(a);
+        int rc_tc = FETODE_EUNSUPPORTED;
+        if (a.L.tc_ok && a.B >= kl_tc_min_rows())              // wide layer: tcgen05 input gradient (kanlinear_tc_dx.cu)
+            rc_tc = kl_tc_dx(&a.P, a.L, a.blob, a.x, a.prev, a.prev_is_zero, a.gy, a.gx, a.g.bp[0], a.g.bp[1], a.B, st);
+        if (rc_tc != FETODE_OK && rc_tc != FETODE_EUNSUPPORTED) return rc_tc;
+        if (rc_tc == FETODE_EUNSUPPORTED) {
+            auto k = kl_bwd_dx_kernel<BR>;
+            e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e) return (int)e;
+            k<<<dim3((unsigned)ntile, (unsigned)gy_), KB_THREADS, smem, st>>>(a);
+        }
     }
     // 3. unfold
     {

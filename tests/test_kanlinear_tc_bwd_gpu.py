@@ -40,6 +40,8 @@ def force_tc():
     (100, 130, 10, "logistic", 77),       # ragged 8-input blocks, two output tiles, ragged row chunk
     (96, 64, 10, "ferro2d", 200),
     (256, 10, 8, "logistic", 130),
+    (64, 256, 10, "logistic", 140),       # two 128-output slices: the input gradient accumulates across CTAs
+    (2352, 128, 10, "logistic", 64),      # ETT encoder width at the script's batch size
 ])
 def test_tc_gradients_match_oracle_autograd(cuda, force_tc, I, O, nb, branch, B):
     p, layer, gen = _layer(I, O, nb, branch, cuda, I * 3 + O)
