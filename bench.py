@@ -171,6 +171,10 @@ def run_ours(args):
     from fetode._lib import TABLEAU, lib
 
     rank, world, local = _dist_env()
+    # libraries (NCCL's version banner) write to fd 1; keep stdout clean for the one JSON line
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("launch with torchrun --nproc-per-node N for --gpus N > 1")
@@ -286,6 +290,8 @@ def run_ours(args):
             "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{n_traj} trajectories x {n_steps} classic-RK4 steps (oracle port, torch CPU, no_grad)"},
         }
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

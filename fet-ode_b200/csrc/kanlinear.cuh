@@ -48,7 +48,7 @@ __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
         L.tc_BN = O <= 16 ? 16 : (O <= 32 ? 32 : (O <= 64 ? 64 : 128));
         L.tc_ntile = (O + L.tc_BN - 1) / L.tc_BN;
         L.tc_units = (I + 31) / 32;
-        L.tc_stages = L.tc_units * L.F;
+        L.tc_stages = L.tc_units * 2 * (5 + NB / 2);       // 16 input pairs x (5 + NB/2) 16-byte chunks, 8 chunks per stage
         o = (o + 255) / 256 * 256;                       // 1 KB alignment for the bulk copies
         L.tc = o;
         o += (long long)L.tc_ntile * L.tc_stages * 2 * L.tc_BN * 32;

@@ -14,11 +14,14 @@
 //
 // CTA = 128 rows x BN outputs x one contiguous range of 32-input units (split-K over the grid's z axis, at most 6
 // units per CTA so that the truncating tensor-core accumulation chains stay short -- see the MMA loop).
-//   warps 0-3   producer set 0 (thread r owns row r): silu + dense cubic B-spline row of 4 inputs at a time, split
-//               hi/lo, 16-byte chunks stored conflict-free into the 128B-swizzled A ring
-//   warps 4-7   producer set 1 (NB > 0 only): the NB branch-basis factors of the same 4 inputs (the K axis is
-//               permuted per group of 4 inputs so the two sets own disjoint chunks of every stage)
-//               both sets double as the epilogue (TMEM lane quarter == warp & 3): tcgen05.ld of the 3 rotating
+//   producers   (thread r of every producer set owns row r)  The feature evaluation is a long dependent chain
+//               (interval search, Cox-de Boor, MUFU ex2/rcp), so it is latency-bound per thread: 4 sets (NB > 0) or
+//               2 sets (NB == 0) of 4 warps share the stream.  Inputs are taken in pairs; pair g2 goes to the sets
+//               of parity g2 & 1:  "spline" set: silu + dense cubic B-spline row of the 2 inputs,
+//               "branch" set (NB > 0): their NB branch-basis factors.  Values are split hi/lo and stored as 16-byte
+//               chunks, conflict-free, into the 128B-swizzled A ring (the K axis is permuted per pair of inputs so
+//               that every set owns whole chunks).
+//               All sets double as the epilogue (TMEM lane quarter == warp & 3): tcgen05.ld of the 3 rotating
 //               accumulators + the correction accumulator, summed in registers, (+bias) -> y / atomics
 //   next warp   lane 0: cp.async.bulk (TMA bulk engine) of the pre-split, pre-swizzled weight stage (hi+lo) into the
 //               B ring; whole warp: TMEM alloc / dealloc
@@ -44,9 +47,10 @@ struct TCArgs {
 };
 
 
-// The K axis is ordered per group of 4 inputs as [ (input ii, silu | N_0..N_7) x 4 | (input ii, r_0..r_{NB-1}) x 4 ]
-// (the weight image is permuted to match, kl_tc_pack_kernel), so that the 9 spline-side chunks and the NB
-// branch-side chunks of a group are produced by two different sets of warps.
+// The K axis is ordered per pair of inputs as [ (input ii, silu | N_0..N_7) x 2, 0, 0 | (input ii, r_0..r_{NB-1}) x 2 ]
+// (the weight image is permuted to match, kl_tc_pack_kernel): 5 spline-side chunks and NB/2 branch-side chunks of
+// 4 values each, produced by two different sets of warps; CPG = 5 + NB/2 chunks per pair, 2*CPG stages per
+// 32-input unit.
 
 // silu and the dense cubic B-spline row of one (row, input) pair: f[0..8]
 __device__ __forceinline__ void tc_spline_features(float x, const float* __restrict__ tab, const KLLayout& L, float* f) {
@@ -81,8 +85,12 @@ __device__ __forceinline__ void tc_branch_features(float x, float prev, float gl
 }
 
 template <int NB, int BR>
-__global__ void __launch_bounds__(NB > 0 ? 352 : 224, 1) kl_tc_fwd_kernel(const TCArgs a) {
-    constexpr int F = 9 + NB;
+__global__ void __launch_bounds__(NB > 0 ? 608 : 352, 1) kl_tc_fwd_kernel(const TCArgs a) {
+    constexpr int CPG = 5 + NB / 2;                               // 16-byte chunks per pair of inputs
+    constexpr int SPU = 2 * CPG;                                  // 32-wide K stages per 32-input unit
+    constexpr int NROLE = NB > 0 ? 2 : 1;                         // spline | branch
+    constexpr int NSETS = 2 * NROLE;                              // x 2 pair parities
+    constexpr int NPROD = 128 * NSETS;
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const int BN = a.BN;
     // carve: A ring (hi, lo per stage), B ring (hi, lo per stage), barriers
@@ -102,24 +110,25 @@ __global__ void __launch_bounds__(NB > 0 ? 352 : 224, 1) kl_tc_fwd_kernel(const 
     const int ntile = blockIdx.y, split = blockIdx.z;
     const int unit0 = split * a.units_per_split;
     const int nunits = min(a.units_per_split, a.units_total - unit0);
-    const int nit = nunits * F;                                   // 32-wide K stages of this CTA
-    const int stage0 = unit0 * F;
+    const int nit = nunits * SPU;                                 // 32-wide K stages of this CTA
+    const int stage0 = unit0 * SPU;
     const uint32_t tmem_cols = 4 * BN < 32 ? 32u : (uint32_t)(4 * BN);   // 3 rotating main accumulators + 1 correction
+    constexpr int TMA_WARP = 4 * NSETS, MMA_WARP = TMA_WARP + 1, TAB_WARP = MMA_WARP + 1;
 
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(barFullA + 8 * s, 128 * (NB > 0 ? 2 : 1));
+            mbar_init(barFullA + 8 * s, NPROD);
             mbar_init(barFullB + 8 * s, 1);
             mbar_init(barEmpty + 8 * s, 1);
         }
         mbar_init(barDone, 1);
         for (int s = 0; s < 2; ++s) {
             mbar_init(barTabFull + 8 * s, 1);
-            mbar_init(barTabEmpty + 8 * s, 128 * (NB > 0 ? 2 : 1));
+            mbar_init(barTabEmpty + 8 * s, NPROD);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == (NB > 0 ? 8 : 4)) {
+    if (warp == TMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      ::"r"(smem_u32((const void*)tmem_slot)), "r"(tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -129,11 +138,10 @@ __global__ void __launch_bounds__(NB > 0 ? 352 : 224, 1) kl_tc_fwd_kernel(const 
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    constexpr int NSETS = NB > 0 ? 2 : 1;
-    constexpr int TMA_WARP = 4 * NSETS, MMA_WARP = TMA_WARP + 1, TAB_WARP = MMA_WARP + 1;
     if (warp < 4 * NSETS) {
         // ===================== producers: A operand =====================
         const int set = warp >> 2;
+        const int role = set % NROLE, par = set / NROLE;
         const int r = tid & 127;
         const long long b = m0 + r;
         const bool live = b < a.B;
@@ -168,53 +176,41 @@ __global__ void __launch_bounds__(NB > 0 ? 352 : 224, 1) kl_tc_fwd_kernel(const 
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + A_TILE), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
         };
-        const int ngroups = nunits * 8;
-        // 4 consecutive inputs of this row (16-byte aligned: I % 4 == 0), zeros for padding inputs / rows
-        auto ldx = [&](const float* rowp, int i) -> float4 {
-            if (!live || i >= I) return make_float4(0.f, 0.f, 0.f, 0.f);
-            return __ldg(reinterpret_cast<const float4*>(rowp + i));
+        const int npairs = nunits * 16;
+        // 2 consecutive inputs of this row (8-byte aligned: I % 4 == 0), zeros for padding inputs / rows
+        auto ldx = [&](const float* rowp, int i) -> float2 {
+            if (!live || i >= I) return make_float2(0.f, 0.f);
+            return __ldg(reinterpret_cast<const float2*>(rowp + i));
         };
-        if (set == 0) {
+        float2 xn = ldx(xrow, unit0 * 32 + 2 * par);
+        float2 pn = (role == 1 && has_prev) ? ldx(prow, unit0 * 32 + 2 * par) : make_float2(0.f, 0.f);
 #pragma unroll 1
-            float4 xn = ldx(xrow, unit0 * 32);
-            for (int gg = 0; gg < ngroups; ++gg) {
-                const int u = gg >> 3, g = gg & 7;
-                if (g == 0) mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
-                const float4 xc = xn;
-                if (gg + 1 < ngroups) xn = ldx(xrow, (unit0 * 8 + gg + 1) * 4);
-                const float xs[4] = {xc.x, xc.y, xc.z, xc.w};
-                const float* tg = tabs + (size_t)((u & 1) * 32 + g * 4) * L.TAB;
-                float f[36];
-#pragma unroll
-                for (int ii = 0; ii < 4; ++ii) tc_spline_features(xs[ii], tg + ii * L.TAB, L, f + ii * 9);
-#pragma unroll
-                for (int c = 0; c < 9; ++c) put(gg * F + c, f + 4 * c);
-                if (g == 7) mbar_arrive(barTabEmpty + 8 * (u & 1));
+        for (int g2 = par; g2 < npairs; g2 += 2) {
+            const int u = g2 >> 4, g = g2 & 15;
+            if (g == par) mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
+            const float2 xc = xn, pc = pn;
+            if (g2 + 2 < npairs) {
+                xn = ldx(xrow, unit0 * 32 + 2 * (g2 + 2));
+                if (role == 1 && has_prev) pn = ldx(prow, unit0 * 32 + 2 * (g2 + 2));
             }
-        } else {
-            if constexpr (NB > 0) {
-#pragma unroll 1
-                float4 xn = ldx(xrow, unit0 * 32);
-                float4 pn = has_prev ? ldx(prow, unit0 * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int gg = 0; gg < ngroups; ++gg) {
-                    const int u = gg >> 3, g = gg & 7;
-                    if (g == 0) mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
-                    const float4 xc = xn, pc = pn;
-                    if (gg + 1 < ngroups) {
-                        xn = ldx(xrow, (unit0 * 8 + gg + 1) * 4);
-                        if (has_prev) pn = ldx(prow, (unit0 * 8 + gg + 1) * 4);
-                    }
-                    const float xs[4] = {xc.x, xc.y, xc.z, xc.w}, ps[4] = {pc.x, pc.y, pc.z, pc.w};
-                    const float* tg = tabs + (size_t)((u & 1) * 32 + g * 4) * L.TAB;
-                    float f[4 * NB];
+            const float* tg = tabs + (size_t)((u & 1) * 32 + g * 2) * L.TAB;
+            if (role == 0) {
+                float f[20];
+                tc_spline_features(xc.x, tg, L, f);
+                tc_spline_features(xc.y, tg + L.TAB, L, f + 9);
+                f[18] = f[19] = 0.f;
 #pragma unroll
-                    for (int ii = 0; ii < 4; ++ii)
-                        tc_branch_features<NB, BR>(xs[ii], ps[ii], a.gl, tg + ii * L.TAB, L, f + ii * NB);
+                for (int c = 0; c < 5; ++c) put(g2 * CPG + c, f + 4 * c);
+            } else {
+                if constexpr (NB > 0) {
+                    float f[2 * NB];
+                    tc_branch_features<NB, BR>(xc.x, pc.x, a.gl, tg, L, f);
+                    tc_branch_features<NB, BR>(xc.y, pc.y, a.gl, tg + L.TAB, L, f + NB);
 #pragma unroll
-                    for (int c = 0; c < NB; ++c) put(gg * F + 9 + c, f + 4 * c);
-                    if (g == 7) mbar_arrive(barTabEmpty + 8 * (u & 1));
+                    for (int c = 0; c < NB / 2; ++c) put(g2 * CPG + 5 + c, f + 4 * c);
                 }
             }
+            if (g == 14 + par) mbar_arrive(barTabEmpty + 8 * (u & 1));
         }
         advance(nit - 1);
         fence_proxy_async();
@@ -307,7 +303,7 @@ __global__ void __launch_bounds__(NB > 0 ? 352 : 224, 1) kl_tc_fwd_kernel(const 
         }
     }
     __syncthreads();
-    if (warp == (NB > 0 ? 8 : 4)) {
+    if (warp == TMA_WARP) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
     }
@@ -328,15 +324,18 @@ __global__ void __launch_bounds__(256) kl_tc_pack_kernel(KLLayout L, float* blob
         const long long ts = idx / per_tile;                      // ntile * stages + stage
         const int stage = (int)(ts % L.tc_stages), nt = (int)(ts / L.tc_stages);
         // position in the CTA K stream -> (input, feature) row of wcat (see the ordering note above tc_spline_features)
+        const int CPG = 5 + L.NB / 2;
         const long long kpos = (long long)stage * BK + c;
-        const long long grp = kpos / (4 * L.F);
-        const int p = (int)(kpos % (4 * L.F));
-        const int ii = p < 36 ? p / 9 : (p - 36) / (L.NB > 0 ? L.NB : 1);
-        const int f = p < 36 ? p % 9 : 9 + (p - 36) % (L.NB > 0 ? L.NB : 1);
-        const long long k = (grp * 4 + ii) * L.F + f;
+        const long long pair = kpos / (4 * CPG);
+        const int p = (int)(kpos % (4 * CPG));
+        int ii, f;
+        if (p < 18) { ii = p / 9; f = p % 9; }
+        else if (p < 20) { ii = 0; f = -1; }                      // padding slots of the spline side
+        else { ii = (p - 20) / (L.NB > 0 ? L.NB : 1); f = 9 + (p - 20) % (L.NB > 0 ? L.NB : 1); }
+        const long long k = (pair * 2 + ii) * L.F + f;
         const int o = nt * BN + row;
         float w = 0.f;
-        if (grp * 4 + ii < L.I && k < KF && o < L.O) w = wcat[k * L.O + o];
+        if (f >= 0 && pair * 2 + ii < L.I && k < KF && o < L.O) w = wcat[k * L.O + o];
         const float hi = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
         float* tile = dst + ts * 2 * per_tile;
         tile[swz(row, c)] = hi;
@@ -349,7 +348,7 @@ static int tc_launch_k(const TCArgs& a, dim3 grid, size_t smem, cudaStream_t st)
     auto k = kl_tc_fwd_kernel<NB, BR>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e) return (int)e;
-    k<<<grid, NB > 0 ? 352 : 224, smem, st>>>(a);
+    k<<<grid, NB > 0 ? 608 : 352, smem, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 
