@@ -349,7 +349,7 @@ static int kl_bwd_launch(KLBwdArgs& a, cudaStream_t st) {
         e = cudaMemsetAsync(a.ws, 0, ((size_t)L.I * L.F * L.O + L.O) * 4, st);
         if (e) return (int)e;
         int rc_tc = FETODE_EUNSUPPORTED;
-        if (a.L.tc_ok && a.B / 4 >= kl_tc_min_rows())           // wide layer: tcgen05 weight gradient (kanlinear_tc_bwd.cu)
+        if (a.L.tc_ok && a.B >= kl_tc_min_rows())               // wide layer: tcgen05 weight gradient (kanlinear_tc_bwd.cu)
             rc_tc = kl_tc_dw(&a.P, a.L, a.blob, a.x, a.prev, a.prev_is_zero, a.gy, a.ws, a.B, st);
         if (rc_tc != FETODE_OK && rc_tc != FETODE_EUNSUPPORTED) return rc_tc;
         if (rc_tc == FETODE_EUNSUPPORTED)

@@ -10,8 +10,12 @@
 //
 // Same 3xTF32 split as the forward (hi*hi + hi*lo + lo*hi) with the hi*hi products rotated over two TMEM
 // accumulators and the corrections in a third (the tensor core truncates when it accumulates, see kanlinear_tc.cu).
-// Per CTA: 8 inputs (two groups of 4, K-stream padded to FP = 4*ceil(F/4) chunks per group so that a 64-row chunk
-// is a whole number of 32-feature stages), all rows of its row range in chunks of 64, one 128-wide output tile.
+// Per CTA: 8 inputs = 4 pairs, one 128-wide output tile, a contiguous range of 32-row chunks.  One chunk =
+// one shared-memory buffer holding the gy tile [32 x 128] and the feature tile [32 x NCOLS] (NCOLS = 4 pairs x
+// (20 spline-side + 2 NB branch-side columns)), both hi/lo; the MMA takes the whole feature tile as ONE N = NCOLS
+// operand (M = 128 outputs, K = 32 rows: 12 instructions per chunk), so the 4 KB gy operand is re-read from shared
+// memory once per 80-cycle instruction instead of once per 16-cycle N = 32 slice.  NPAR producer groups (spline
+// role + branch role, thread = (row, pair)) own one buffer each and take every NPAR-th chunk.
 #include <cstdlib>
 #include "tc_common.cuh"
 
@@ -20,9 +24,8 @@ namespace tcb {
 
 using namespace tc;
 
-constexpr int RC = 64;                 // rows per chunk
-constexpr int NSA = 5;                 // feature-stage ring depth ([64 x 32] hi+lo = 16 KB per stage)
-constexpr uint32_t STAGE_BYTES = RC * 32 * 4;            // one of hi / lo
+constexpr int RC = 32;                 // rows per chunk
+constexpr uint32_t STAGE_BYTES = RC * 32 * 4;            // one [32 rows x 32 features] group, hi or lo
 constexpr uint32_t GY_BYTES = RC * 128 * 4;              // one of hi / lo
 
 struct DWArgs {
@@ -69,24 +72,34 @@ __device__ __forceinline__ void branch_features(float x, float prev, float gl, c
 }
 
 
+
+template <int NB> struct DWShape {
+    static constexpr int NROLE = NB > 0 ? 2 : 1;             // spline | branch producer roles
+    static constexpr int NPAR = 2;                           // producer groups = shared-memory buffers
+    static constexpr int FPP = 20 + 2 * NB;                  // columns per pair of inputs
+    static constexpr int NCOLS = 4 * FPP;                    // features per CTA (MMA N)
+    static constexpr int NSTG = (NCOLS + 31) / 32;           // 32-feature groups per chunk
+    static constexpr int NPROD = 128 * NROLE * NPAR;
+    static constexpr int THREADS = NPROD + 64;
+    static constexpr uint32_t BUF_BYTES = 2 * GY_BYTES + NSTG * 2 * STAGE_BYTES;
+};
+
 template <int NB, int BR>
-__global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const DWArgs a) {
+__global__ void __launch_bounds__(DWShape<NB>::THREADS, 1) kl_tc_dw_kernel(const DWArgs a) {
+    using SH = DWShape<NB>;
     constexpr int F = 9 + NB;
-    constexpr int FP = (F + 3) / 4 * 4;                 // 16-byte chunks per group of 4 inputs (padded)
-    constexpr int NST = FP / 4;                         // 32-feature stages per 64-row chunk (2 groups)
-    constexpr int NCOLS = 8 * FP;                       // features per CTA
-    constexpr int NSETS = NB > 0 ? 2 : 1;
-    constexpr int NPROD = 128 * NSETS;
+    constexpr int NROLE = SH::NROLE, NPAR = SH::NPAR, FPP = SH::FPP, NCOLS = SH::NCOLS, NSTG = SH::NSTG;
+    constexpr int NSETS = NROLE * NPAR;
     constexpr int TMA_WARP = 4 * NSETS, MMA_WARP = TMA_WARP + 1;
+    static_assert(NCOLS % 16 == 0 && 3 * NCOLS <= 512, "feature tile must be a legal MMA N and fit three accumulators");
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
     unsigned char* gbase = tc_smem_raw + (base - smem_u32(tc_smem_raw));
     const KLLayout& L = a.L;
-    const uint32_t offA = 0, offG = NSA * 2 * STAGE_BYTES, offTab = offG + 2 * 2 * GY_BYTES,
-                   offBar = offTab + (uint32_t)(8 * L.TAB * 4 + 127) / 128 * 128;
-    const uint32_t barFullA = base + offBar, barEmpty = barFullA + 8 * NSA, barGyFull = barEmpty + 8 * NSA,
-                   barGyEmpty = barGyFull + 16, barDone = barGyEmpty + 16;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + offBar + 8 * (2 * NSA + 5));
+    // buffer p: [gy hi | gy lo | NSTG x (features hi | lo)]
+    const uint32_t offTab = NPAR * SH::BUF_BYTES, offBar = offTab + (uint32_t)(8 * L.TAB * 4 + 127) / 128 * 128;
+    const uint32_t barFull = base + offBar, barEmpty = barFull + 8 * NPAR, barDone = barEmpty + 8 * NPAR;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + offBar + 8 * (2 * NPAR + 1));
     float* tabs = reinterpret_cast<float*>(gbase + offTab);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -99,8 +112,7 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const D
     constexpr uint32_t tmem_cols = 512;                 // 2 rotating main accumulators + 1 correction, NCOLS each
 
     if (tid == 0) {
-        for (int s = 0; s < NSA; ++s) { mbar_init(barFullA + 8 * s, NPROD); mbar_init(barEmpty + 8 * s, 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(barGyFull + 8 * s, NPROD); mbar_init(barGyEmpty + 8 * s, 1); }
+        for (int s = 0; s < NPAR; ++s) { mbar_init(barFull + 8 * s, 128 * NROLE); mbar_init(barEmpty + 8 * s, 1); }
         mbar_init(barDone, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -117,27 +129,19 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const D
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp < 4 * NSETS) {
-        // ===================== producers: gy tiles (A operand) and feature stages (B operand) =====================
+        // ===================== producers: gy tile (A operand) and feature tile (B operand) of every NPAR-th chunk =====
         const int set = warp >> 2;
-        const int t = tid & 127, row = t & 63, grp = t >> 6;
+        const int role = set % NROLE, par = set / NROLE;
+        const int t = tid & 127, row = t & 31, pg = t >> 5;          // pair pg: inputs i0 + 2 pg, + 1
+        const int tg = (role * 128 + t);                             // index inside the parity group (gy tile work split)
         const bool has_prev = BR == FETODE_BRANCH_FERRO2D && !a.prev_is_zero;
         // MN-major tf32 tiles (SWIZZLE_128B_BASE32B): 4-row atoms of 512 B, 32-byte chunks XOR-ed with row & 3
         const uint32_t rowoff = (uint32_t)((row >> 2) * 512 + (row & 3) * 128);
         const uint32_t rx = (uint32_t)(row & 3);
-        const int ig = i0 + 4 * grp;                     // first input of this thread's group
-        int cur = -1;
-        uint32_t dst = 0;
-        auto advance = [&](int target) {
-            while (cur < target) {
-                if (cur >= 0) { fence_proxy_async(); mbar_arrive(barFullA + 8 * (cur % NSA)); }
-                ++cur;
-                mbar_wait(barEmpty + 8 * (cur % NSA), ((cur / NSA) & 1) ^ 1);
-                dst = base + offA + (uint32_t)(cur % NSA) * 2 * STAGE_BYTES + rowoff;
-            }
-        };
-        auto put = [&](int q, const float* v4) {
-            const int st = q >> 3;
-            if (st != cur) advance(st);
+        const int ig = i0 + 2 * pg;
+        const uint32_t buf = base + (uint32_t)par * SH::BUF_BYTES;
+        const uint32_t fbase = buf + 2 * GY_BYTES + rowoff;
+        auto put = [&](int q, const float* v4) {                     // 16-byte chunk q of the chunk's feature tile
             float hi[4], lo[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -145,77 +149,78 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const D
                 lo[e] = v4[e] - hi[e];
             }
             const uint32_t cs = (uint32_t)q & 7u;
-            const uint32_t addr = dst + ((((cs >> 1) ^ rx) << 5) | ((cs & 1u) << 4));
+            const uint32_t addr = fbase + (uint32_t)(q >> 3) * 2 * STAGE_BYTES + ((((cs >> 1) ^ rx) << 5) | ((cs & 1u) << 4));
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + STAGE_BYTES), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
         };
-        auto ldx = [&](const float* p, long long b) -> float4 {
-            if (b >= a.B || ig >= I) return make_float4(0.f, 0.f, 0.f, 0.f);
-            return __ldg(reinterpret_cast<const float4*>(p + b * I + ig));
+        auto ldx = [&](const float* p, long long b) -> float2 {
+            if (b >= a.B || ig >= I) return make_float2(0.f, 0.f);
+            return __ldg(reinterpret_cast<const float2*>(p + b * I + ig));
         };
-        const float* tg = tabs + (size_t)(4 * grp) * L.TAB;
-        const float zero4[4] = {0.f, 0.f, 0.f, 0.f};
-        float4 xn = ldx(a.x, chunk0 * RC + row);
-        float4 pn = has_prev ? ldx(a.prev, chunk0 * RC + row) : make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int c = 0; c < nchunks; ++c) {
+        const float* tgp = tabs + (size_t)(2 * pg) * L.TAB;
+        float2 xn = make_float2(0.f, 0.f), pn = xn;
+        if (par < nchunks) {
+            xn = ldx(a.x, (chunk0 + par) * RC + row);
+            if (role == 1 && has_prev) pn = ldx(a.prev, (chunk0 + par) * RC + row);
+        }
+#pragma unroll 1
+        for (int c = par; c < nchunks; c += NPAR) {
             const long long r0 = (chunk0 + c) * RC;
-            // ---- gy tile of this chunk: [64 rows x 128 outputs] -> hi / lo, MN-major SWIZZLE_128B_BASE32B atoms
-            {
-                mbar_wait(barGyEmpty + 8 * (c & 1), ((c >> 1) & 1) ^ 1);
-                const uint32_t gdst = base + offG + (uint32_t)(c & 1) * 2 * GY_BYTES;
-                for (int q = tid; q < RC * 32; q += NPROD) {
-                    const int b = q >> 5, o4 = q & 31;
-                    const int o = otile * 128 + o4 * 4;
-                    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (r0 + b < a.B && o < O) {
-                        const float* gp = a.gy + (r0 + b) * O + o;
-                        if (o + 3 < O && (O & 3) == 0) g = __ldg(reinterpret_cast<const float4*>(gp));
-                        else { g.x = gp[0]; if (o + 1 < O) g.y = gp[1]; if (o + 2 < O) g.z = gp[2]; if (o + 3 < O) g.w = gp[3]; }
-                    }
-                    float4 h;
-                    h.x = __uint_as_float(__float_as_uint(g.x) & 0xffffe000u); h.y = __uint_as_float(__float_as_uint(g.y) & 0xffffe000u);
-                    h.z = __uint_as_float(__float_as_uint(g.z) & 0xffffe000u); h.w = __uint_as_float(__float_as_uint(g.w) & 0xffffe000u);
-                    const uint32_t addr = gdst + (uint32_t)((o4 >> 3) * 8192 + (b >> 2) * 512 + (b & 3) * 128 + (((((o4 & 7) >> 1) ^ (b & 3)) << 5) | ((o4 & 1) << 4)));
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w) : "memory");
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + GY_BYTES), "f"(g.x - h.x), "f"(g.y - h.y), "f"(g.z - h.z), "f"(g.w - h.w) : "memory");
-                }
-                fence_proxy_async();
-                mbar_arrive(barGyFull + 8 * (c & 1));
+            const int use = c / NPAR;                                // how many times this buffer was filled before
+            // ---- features of (row, pair) in registers first: the buffer may still be in use by the MMA
+            const float2 xc = xn, pc = pn;
+            if (c + NPAR < nchunks) {
+                xn = ldx(a.x, r0 + NPAR * RC + row);
+                if (role == 1 && has_prev) pn = ldx(a.prev, r0 + NPAR * RC + row);
             }
-            // ---- features of (row, 4 inputs)
-            const float4 xc = xn, pc = pn;
-            if (c + 1 < nchunks) {
-                xn = ldx(a.x, r0 + RC + row);
-                if (has_prev) pn = ldx(a.prev, r0 + RC + row);
-            }
-            const float xs[4] = {xc.x, xc.y, xc.z, xc.w}, ps[4] = {pc.x, pc.y, pc.z, pc.w};
-            const int q0 = c * (2 * FP) + grp * FP;
-            if (set == 0) {
-                float f[36];
-#pragma unroll
-                for (int ii = 0; ii < 4; ++ii) spline_features(xs[ii], tg + ii * L.TAB, L, f + ii * 9);
-#pragma unroll
-                for (int k = 0; k < 9; ++k) put(q0 + k, f + 4 * k);
-                if constexpr (NB == 0) {
-#pragma unroll
-                    for (int k = 9; k < FP; ++k) put(q0 + k, zero4);
-                }
+            float f[20];
+            if (role == 0) {
+                spline_features(xc.x, tgp, L, f);
+                spline_features(xc.y, tgp + L.TAB, L, f + 9);
+                f[18] = f[19] = 0.f;
             } else {
                 if constexpr (NB > 0) {
-                    float f[4 * NB];
-#pragma unroll
-                    for (int ii = 0; ii < 4; ++ii) branch_features<NB, BR>(xs[ii], ps[ii], a.gl, tg + ii * L.TAB, L, f + ii * NB);
-#pragma unroll
-                    for (int k = 0; k < NB; ++k) put(q0 + 9 + k, f + 4 * k);
-#pragma unroll
-                    for (int k = 9 + NB; k < FP; ++k) put(q0 + k, zero4);
+                    branch_features<NB, BR>(xc.x, pc.x, a.gl, tgp, L, f);
+                    branch_features<NB, BR>(xc.y, pc.y, a.gl, tgp + L.TAB, L, f + NB);
                 }
             }
-        }
-        if (nchunks > 0) {
-            advance(nchunks * NST - 1);
+            // ---- this thread's share of the gy tile: [32 rows x 128 outputs] = 1024 float4
+            float4 gv[1024 / (128 * NROLE)];
+#pragma unroll
+            for (int k = 0; k < 1024 / (128 * NROLE); ++k) {
+                const int q = tg + k * 128 * NROLE;
+                const int b = q >> 5, o4 = q & 31;
+                const int o = otile * 128 + o4 * 4;
+                float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r0 + b < a.B && o < O) {
+                    const float* gp = a.gy + (r0 + b) * O + o;
+                    if (o + 3 < O && (O & 3) == 0) g = __ldg(reinterpret_cast<const float4*>(gp));
+                    else { g.x = gp[0]; if (o + 1 < O) g.y = gp[1]; if (o + 2 < O) g.z = gp[2]; if (o + 3 < O) g.w = gp[3]; }
+                }
+                gv[k] = g;
+            }
+            mbar_wait(barEmpty + 8 * par, (use & 1) ^ 1);
+#pragma unroll
+            for (int k = 0; k < 1024 / (128 * NROLE); ++k) {
+                const int q = tg + k * 128 * NROLE;
+                const int b = q >> 5, o4 = q & 31;
+                const float4 g = gv[k];
+                float4 h;
+                h.x = __uint_as_float(__float_as_uint(g.x) & 0xffffe000u); h.y = __uint_as_float(__float_as_uint(g.y) & 0xffffe000u);
+                h.z = __uint_as_float(__float_as_uint(g.z) & 0xffffe000u); h.w = __uint_as_float(__float_as_uint(g.w) & 0xffffe000u);
+                const uint32_t addr = buf + (uint32_t)((o4 >> 3) * (RC * 128) + (b >> 2) * 512 + (b & 3) * 128 + (((((o4 & 7) >> 1) ^ (b & 3)) << 5) | ((o4 & 1) << 4)));
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w) : "memory");
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr + GY_BYTES), "f"(g.x - h.x), "f"(g.y - h.y), "f"(g.z - h.z), "f"(g.w - h.w) : "memory");
+            }
+            if (role == 0) {
+#pragma unroll
+                for (int k = 0; k < 5; ++k) put(pg * (FPP / 4) + k, f + 4 * k);
+            } else {
+#pragma unroll
+                for (int k = 0; k < NB / 2; ++k) put(pg * (FPP / 4) + 5 + k, f + 4 * k);
+            }
             fence_proxy_async();
-            mbar_arrive(barFullA + 8 * (cur % NSA));
+            mbar_arrive(barFull + 8 * par);
         }
         // ===================== epilogue: TMEM [o lanes x features] -> folded-weight gradient =====================
         mbar_wait(barDone, 0);
@@ -242,12 +247,12 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const D
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
                     const int col = c0 + e;
-                    const int g = col / (4 * FP), p = col % (4 * FP);
+                    const int g = col / FPP, p = col % FPP;
                     int ii, f;
-                    if (p < 36) { ii = p / 9; f = p % 9; }
-                    else if (p < 36 + 4 * NB) { ii = (p - 36) / (NB > 0 ? NB : 1); f = 9 + (p - 36) % (NB > 0 ? NB : 1); }
-                    else continue;
-                    const int i = i0 + 4 * g + ii;
+                    if (p < 18) { ii = p / 9; f = p % 9; }
+                    else if (p < 20) continue;
+                    else { ii = (p - 20) / (NB > 0 ? NB : 1); f = 9 + (p - 20) % (NB > 0 ? NB : 1); }
+                    const int i = i0 + 2 * g + ii;
                     if (i >= I) continue;
                     float* dstp = a.ws + ((size_t)i * F + f) * O + o;
                     if (gridDim.z == 1) *dstp = acc[e]; else atomicAdd(dstp, acc[e]);
@@ -258,30 +263,27 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const D
     } else if (warp == MMA_WARP) {
         // ===================== MMA issue =====================
         if (lane == 0) {
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(32 >> 3) << 17) |
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(NCOLS >> 3) << 17) |
                                    ((uint32_t)(128 >> 4) << 24);
             for (int c = 0; c < nchunks; ++c) {
-                mbar_wait(barGyFull + 8 * (c & 1), (c >> 1) & 1);
-                const uint32_t gHi = base + offG + (uint32_t)(c & 1) * 2 * GY_BYTES, gLo = gHi + GY_BYTES;
-                for (int s = 0; s < NST; ++s) {
-                    const int it = c * NST + s;
-                    mbar_wait(barFullA + 8 * (it % NSA), (it / NSA) & 1);
-                    tc_fence_after();
-                    const uint32_t fHi = base + offA + (uint32_t)(it % NSA) * 2 * STAGE_BYTES, fLo = fHi + STAGE_BYTES;
-                    const uint32_t dMain = tmem_base + (uint32_t)((c & 1) * NCOLS + s * 32);
-                    const uint32_t dCorr = tmem_base + (uint32_t)(2 * NCOLS + s * 32);
+                const int p = c % NPAR;
+                mbar_wait(barFull + 8 * p, (c / NPAR) & 1);
+                tc_fence_after();
+                const uint32_t gHi = base + (uint32_t)p * SH::BUF_BYTES, gLo = gHi + GY_BYTES;
+                const uint32_t fHi = gHi + 2 * GY_BYTES, fLo = fHi + STAGE_BYTES;
+                const uint32_t dMain = tmem_base + (uint32_t)((c & 1) * NCOLS);
+                const uint32_t dCorr = tmem_base + (uint32_t)(2 * NCOLS);
 #pragma unroll
-                    for (int ks = 0; ks < RC / 8; ++ks) {
-                        // one K = 8 slice = two 4-row atoms, 512 B apart (SBO); output atoms of gy are 8 KB apart (LBO)
-                        const uint64_t dGh = umma_desc(gHi + ks * 1024, 8192, 512, 1), dGl = umma_desc(gLo + ks * 1024, 8192, 512, 1);
-                        const uint64_t dFh = umma_desc(fHi + ks * 1024, 4096, 512, 1), dFl = umma_desc(fLo + ks * 1024, 4096, 512, 1);
-                        umma_tf32(dMain, dGh, dFh, idesc, !(c < 2 && ks == 0));
-                        umma_tf32(dCorr, dGh, dFl, idesc, !(c == 0 && ks == 0));
-                        umma_tf32(dCorr, dGl, dFh, idesc, 1);
-                    }
-                    umma_commit(barEmpty + 8 * (it % NSA));
+                for (int ks = 0; ks < RC / 8; ++ks) {
+                    // one K = 8 slice = two 4-row atoms, 512 B apart (SBO); 32-element groups along M / N are LBO apart:
+                    // RC*128 B for gy, 2*STAGE_BYTES for the features (hi and lo groups interleave)
+                    const uint64_t dGh = umma_desc(gHi + ks * 1024, RC * 128, 512, 1), dGl = umma_desc(gLo + ks * 1024, RC * 128, 512, 1);
+                    const uint64_t dFh = umma_desc(fHi + ks * 1024, 2 * STAGE_BYTES, 512, 1), dFl = umma_desc(fLo + ks * 1024, 2 * STAGE_BYTES, 512, 1);
+                    umma_tf32(dMain, dGh, dFh, idesc, !(c < 2 && ks == 0));
+                    umma_tf32(dCorr, dGh, dFl, idesc, !(c == 0 && ks == 0));
+                    umma_tf32(dCorr, dGl, dFh, idesc, 1);
                 }
-                umma_commit(barGyEmpty + 8 * (c & 1));
+                umma_commit(barEmpty + 8 * p);
             }
             umma_commit(barDone);
         }
@@ -295,11 +297,12 @@ __global__ void __launch_bounds__(NB > 0 ? 320 : 192, 1) kl_tc_dw_kernel(const D
 
 template <int NB, int BR>
 static int dw_launch_k(const DWArgs& a, dim3 grid, cudaStream_t st) {
-    const size_t smem = (size_t)NSA * 2 * STAGE_BYTES + 2 * 2 * GY_BYTES + ((size_t)8 * a.L.TAB * 4 + 127) / 128 * 128 + 1024 + 256;
+    using SH = DWShape<NB>;
+    const size_t smem = (size_t)SH::NPAR * SH::BUF_BYTES + ((size_t)8 * a.L.TAB * 4 + 127) / 128 * 128 + 1024 + 256;
     auto k = kl_tc_dw_kernel<NB, BR>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e) return (int)e;
-    k<<<grid, NB > 0 ? 320 : 192, smem, st>>>(a);
+    k<<<grid, SH::THREADS, smem, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 
@@ -317,8 +320,17 @@ int kl_tc_dw(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, c
     a.prev_is_zero = prev_is_zero;
     const long long nchunks = (B + tcb::RC - 1) / tcb::RC;
     const int blocks = (L.I + 7) / 8, otiles = (L.O + 127) / 128;
-    long long splits = std::max(1LL, (148LL + (long long)blocks * otiles - 1) / ((long long)blocks * otiles));
-    splits = std::max(splits, (nchunks + 31) / 32);          // <= 2048 rows per CTA: bounded accumulation chains
+    // fill the 148 SMs with whole waves; <= 2048 rows per CTA keeps the truncating accumulation chains short
+    const long long ctas = (long long)blocks * otiles;
+    long long splits = 1;
+    {
+        double best = 1e30;
+        for (long long s = 1; s <= 8; ++s) {
+            const double t = (double)((ctas * s + 147) / 148) / (double)s;       // waves per unit of work
+            if (t < best - 1e-9) { best = t; splits = s; }
+        }
+    }
+    splits = std::max(splits, (nchunks + 63) / 64);
     splits = std::min(splits, nchunks);
     a.chunks_per_split = (int)((nchunks + splits - 1) / splits);
     splits = (nchunks + a.chunks_per_split - 1) / a.chunks_per_split;
