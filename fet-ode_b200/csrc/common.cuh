@@ -64,6 +64,46 @@ __device__ __forceinline__ void rcp_batch(const float (&a)[N], float (&r)[N]) {
     }
 }
 
+// ---- packed fp32 pairs (Blackwell FFMA2 / FMUL2 / FADD2: one issue slot for two lanes) -------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 rcp2(f32x2 a) { float l, h; upk2(a, l, h); return pk2(rcp_approx(l), rcp_approx(h)); }
+
+// r[i] = 1 / a[i], both halves of N packed pairs, with 2*ceil(N/4) MUFU.RCP (a[i] in [1, 2^30+1]).
+template <int N>
+__device__ __forceinline__ void rcp_batch2(const f32x2 (&a)[N], f32x2 (&r)[N]) {
+    constexpr int Q = N / 4;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+        const f32x2 p01 = mul2(a[4 * q], a[4 * q + 1]), p23 = mul2(a[4 * q + 2], a[4 * q + 3]);
+        const f32x2 inv = rcp2(mul2(p01, p23));
+        const f32x2 q01 = mul2(inv, p23), q23 = mul2(inv, p01);
+        r[4 * q] = mul2(q01, a[4 * q + 1]);
+        r[4 * q + 1] = mul2(q01, a[4 * q]);
+        r[4 * q + 2] = mul2(q23, a[4 * q + 3]);
+        r[4 * q + 3] = mul2(q23, a[4 * q + 2]);
+    }
+    constexpr int R = N - 4 * Q;
+    if constexpr (R == 1) {
+        r[4 * Q] = rcp2(a[4 * Q]);
+    } else if constexpr (R == 2) {
+        const f32x2 inv = rcp2(mul2(a[4 * Q], a[4 * Q + 1]));
+        r[4 * Q] = mul2(inv, a[4 * Q + 1]);
+        r[4 * Q + 1] = mul2(inv, a[4 * Q]);
+    } else if constexpr (R == 3) {
+        const f32x2 p01 = mul2(a[4 * Q], a[4 * Q + 1]);
+        const f32x2 inv = rcp2(mul2(p01, a[4 * Q + 2]));
+        const f32x2 q01 = mul2(inv, a[4 * Q + 2]);
+        r[4 * Q] = mul2(q01, a[4 * Q + 1]);
+        r[4 * Q + 1] = mul2(q01, a[4 * Q]);
+        r[4 * Q + 2] = mul2(inv, p01);
+    }
+}
+
 // sigmoid(z) with z already multiplied by log2(e):  1 / (1 + 2^-zl)
 __device__ __forceinline__ float sigmoid_l2(float zl) { return rcp_approx(1.0f + ex2_approx(-zl)); }
 

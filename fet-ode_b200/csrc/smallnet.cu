@@ -54,6 +54,13 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
                        img + L.l1_gi + d * 4);
     for (int idx = tid; idx < D * NB; idx += nt)
         reinterpret_cast<float4*>(img + L.l1_bp)[idx] = branch_params(P1, idx);
+    for (int idx = tid; idx < D * (NB / 2); idx += nt) {                      // pair (p, p + NB/2) of input d
+        const int d = idx / (NB / 2), p = idx % (NB / 2);
+        const float4 lo = branch_params(P1, d * NB + p), hi = branch_params(P1, d * NB + p + NB / 2);
+        float4* q = reinterpret_cast<float4*>(img + L.l1_bq) + d * NB + 2 * p;
+        q[0] = make_float4(lo.x, hi.x, lo.y, hi.y);
+        q[1] = make_float4(lo.z, hi.z, lo.w, hi.w);
+    }
     for (int o = tid; o < D; o += nt) {
         double b = P2.branch_bias ? (double)P2.branch_bias[o] : 0.0;
         for (int h = 0; h < H; ++h)
@@ -72,6 +79,9 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
                 wu[1 + j] = (float)wr;
                 b += wc;
             }
+            float* wv = rec + L.r_wv1 + d * L.FU;
+            for (int p = 0; p < NB / 2; ++p) { wv[2 * p] = wu[1 + p]; wv[2 * p + 1] = wu[1 + p + NB / 2]; }
+            wv[2 * (NB / 2)] = wu[0];
             float* ws = rec + L.r_ws1 + d * L.SPP;
             const float sc = P1.spline_scaler ? P1.spline_scaler[h * D + d] : 1.0f;
             for (int s = 0; s < S; ++s) ws[s + 3] = P1.spline_weight[(h * D + d) * S + s] * sc;
@@ -80,6 +90,12 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
         pack_knots_row(P2.grid + (size_t)h * L.NK, L.NK, L.NKP, rec + L.r_kn, rec + L.r_rd1, rec + L.r_rd2,
                        rec + L.r_rd3, rec + L.r_gi);
         for (int j = 0; j < NB; ++j) reinterpret_cast<float4*>(rec + L.r_bp)[j] = branch_params(P2, h * NB + j);
+        for (int p = 0; p < NB / 2; ++p) {
+            const float4 lo = branch_params(P2, h * NB + p), hi = branch_params(P2, h * NB + p + NB / 2);
+            float4* q = reinterpret_cast<float4*>(rec + L.r_bq) + 2 * p;
+            q[0] = make_float4(lo.x, hi.x, lo.y, hi.y);
+            q[1] = make_float4(lo.z, hi.z, lo.w, hi.w);
+        }
         for (int o = 0; o < D; ++o) {
             float* wu = rec + L.r_wu2 + o;
             wu[0] = P2.base_weight[o * H + h];
@@ -93,7 +109,7 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
 
 
 template <int D, int NB, int G, int BR>
-__global__ void __launch_bounds__(SN_THREADS, 4) smallnet_rk_kernel(const SNArgs a) {
+__global__ void __launch_bounds__(SN_THREADS, 8) smallnet_rk_kernel(const SNArgs a) {
     extern __shared__ float4 sn_smem4[];
     float* sm = reinterpret_cast<float*>(sn_smem4);
     constexpr SNLayout L0 = sn_layout(D, 0, NB, G);
