@@ -258,9 +258,20 @@ def run_ours(args):
         except Exception:
             pass
         hbm_bytes = B * (8 + 8 + 4 * plan.state_floats)              # y0 in, y out, hysteresis state out
+        # DRAM bytes per launch of the same kernel from the committed `ncu --set full` capture (profiles/)
+        traffic, traffic_src = None, None
+        try:
+            import csv
+            prof = os.path.join(ROOT, "profiles", "r1_smallnet_rk_ncu_full.csv")
+            vals = {r[0]: (r[1], float(r[2])) for r in csv.reader(open(prof)) if len(r) == 3 and r[0].startswith("dram__bytes")}
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            traffic = sum(v * scale[u] for u, v in vals.values())
+            traffic_src = "profiles/r1_smallnet_rk_ncu_full.csv (dram read+write of one launch at this size; mostly register-spill lines)"
+        except Exception:
+            pass
         roofline = {
             "bound": "fp32", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
-            "traffic": None,
+            "traffic": traffic, "traffic_source": traffic_src,
             "peak_source": "live FFMA probe (fetode_probe_fp32_peak); MEASURED_PEAKS.json holds HBM/bf16 only" if rc == 0
                            else "fallback 2*128*148*1.965 GHz",
             "kernel": "smallnet_rk_kernel<2,10,5,FERRO2D>",
