@@ -172,17 +172,24 @@ class KanLinearFn(torch.autograd.Function):
         g = KanLayerGrads()
         outs = []
         tens = dict(pack.view.tensors())
-        for idx, name in enumerate(ctx.names):
+        # one zero-filled flat buffer for every wanted parameter gradient (the kernels accumulate into it):
+        # a single fill launch instead of one per parameter
+        want = [ctx.needs_input_grad[3 + idx] for idx in range(len(ctx.names))]
+        sizes = [(tens[n].numel() + 3) // 4 * 4 if w else 0 for n, w in zip(ctx.names, want)]
+        n_grad = sum(sizes)
+        n_ws = max(int(L.fetode_kanlinear_bwd_ws_floats(C.byref(s))), 1)
+        flat = torch.zeros(max(n_grad, 1), dtype=torch.float32, device=x2d.device)
+        ws = torch.empty(n_ws, dtype=torch.float32, device=x2d.device)
+        off = 0
+        for name, w, n in zip(ctx.names, want, sizes):
             t = tens[name]
-            gt = torch.zeros_like(t, dtype=torch.float32, memory_format=torch.contiguous_format) \
-                if ctx.needs_input_grad[3 + idx] else None
+            gt = flat[off:off + t.numel()].view(t.shape) if w else None
+            off += n
             outs.append(gt)
             if name.startswith("bp"):
                 g.bp[int(name[2:])] = ptr(gt).value
             else:
                 setattr(g, name, ptr(gt).value)
-        n_ws = L.fetode_kanlinear_bwd_ws_floats(C.byref(s))
-        ws = torch.empty(max(int(n_ws), 1), dtype=torch.float32, device=x2d.device)
         ferro = s.branch == BRANCH_FERRO2D
         check(L.fetode_kanlinear_bwd(C.byref(s), ptr(blob), ptr(x2d), ptr(ctx.prev) if ferro else None,
                                      C.c_int(1 if ctx.prev is None else 0), ptr(gy), ptr(gx), C.byref(g),
