@@ -15,12 +15,13 @@
 //   (<= 128 KB); the weight chunks ([NCOL x 32 outputs] hi+lo tiles, pre-split / pre-swizzled by kl_td_pack_kernel)
 //   stream through a ring via the TMA bulk-copy engine.  The contraction is only O <= 128 long (48 MMAs), so one
 //   accumulator per chunk is enough; four of them rotate in TMEM so that the epilogue warps never stall the MMA.
-//   warps 0-7   gy prologue, then epilogue: set (warp >> 2) takes every other chunk; thread = row (TMEM lane):
+//   warps 0-15  gy prologue, then epilogue: set (warp >> 2) takes every 4th chunk (the per-row derivative
+//               evaluation is a latency-bound chain, so four sets run concurrently); thread = row (TMEM lane):
 //               tcgen05.ld of the FP values of one input, derivative evaluation, gx store, branch-parameter partial
 //               sums reduced across the warp with a recursive-halving shuffle (warp_colsum) and across the CTA's
 //               four row quarters in shared memory, one global atomic per (input, parameter) per CTA
-//   warp 8      lane 0: cp.async.bulk of the weight stages; whole warp: TMEM alloc / dealloc
-//   warp 9      lane 0: tcgen05.mma issue
+//   warp 16     lane 0: cp.async.bulk of the weight stages; whole warp: TMEM alloc / dealloc
+//   warp 17     lane 0: tcgen05.mma issue
 #include <cstdlib>
 #include "tc_common.cuh"
 
@@ -31,6 +32,8 @@ using namespace tc;
 
 constexpr int NSW = 4;                  // weight-stage ring depth
 constexpr int NACC = 4;                 // TMEM accumulators in flight
+constexpr int NEPI = 4;                 // epilogue sets of 4 warps; set s owns chunks s, s + NEPI, .. (accumulator s)
+static_assert(NACC % NEPI == 0 || NEPI % NACC == 0, "every accumulator must belong to one epilogue set");
 constexpr uint32_t GY_SLAB = BM * 32 * 4;      // one [128 x 32] K-slab of gy (hi or lo): 16 KB
 
 struct DXArgs {
@@ -179,7 +182,7 @@ __device__ __forceinline__ float dx_input(const float* g, float x, float prev, c
 }
 
 template <int NB, int BR>
-__global__ void __launch_bounds__(320, 1) kl_tc_dx_kernel(const DXArgs a) {
+__global__ void __launch_bounds__(NEPI * 128 + 64, 1) kl_tc_dx_kernel(const DXArgs a) {
     constexpr int F = 9 + NB;
     constexpr int FP = NB > 0 ? 20 : 12;                // TMEM columns per input (tcgen05.ld x16+x4 / x8+x4)
     static_assert(F <= FP, "feature count exceeds the padded column count");
@@ -188,7 +191,7 @@ __global__ void __launch_bounds__(320, 1) kl_tc_dx_kernel(const DXArgs a) {
     static_assert(NV == 0 || NV == 16 || NV == 20, "warp reduction is laid out for NB = 8 or 10");
     constexpr uint32_t W_TILE = NCOL * 32 * 4;          // one of hi / lo
     constexpr uint32_t TMEM_COLS = NACC * NCOL <= 256 ? 256u : 512u;
-    constexpr int TMA_WARP = 8, MMA_WARP = 9;
+    constexpr int TMA_WARP = 4 * NEPI, MMA_WARP = TMA_WARP + 1;
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
     unsigned char* gbase = tc_smem_raw + (base - smem_u32(tc_smem_raw));
@@ -198,7 +201,7 @@ __global__ void __launch_bounds__(320, 1) kl_tc_dx_kernel(const DXArgs a) {
     const int o0 = osplit * 128;
     const int KS = min(4, (O - o0 + 31) / 32);          // 32-output K slabs of this CTA
     const uint32_t offGy = 0, offW = (uint32_t)KS * 2 * GY_SLAB, offAcc = offW + NSW * 2 * W_TILE,
-                   offBar = offAcc + 2 * 2 * 4 * (NV > 0 ? NV : 4) * 4;
+                   offBar = offAcc + NEPI * 2 * 4 * (NV > 0 ? NV : 4) * 4;
     const uint32_t barWFull = base + offBar, barWEmpty = barWFull + 8 * NSW, barAccFull = barWEmpty + 8 * NSW,
                    barAccEmpty = barAccFull + 8 * NACC, barGy = barAccEmpty + 8 * NACC;
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + offBar + 8 * (2 * NSW + 2 * NACC + 1));
@@ -212,7 +215,7 @@ __global__ void __launch_bounds__(320, 1) kl_tc_dx_kernel(const DXArgs a) {
     if (tid == 0) {
         for (int s = 0; s < NSW; ++s) { mbar_init(barWFull + 8 * s, 1); mbar_init(barWEmpty + 8 * s, 1); }
         for (int s = 0; s < NACC; ++s) { mbar_init(barAccFull + 8 * s, 1); mbar_init(barAccEmpty + 8 * s, 128); }
-        mbar_init(barGy, 256);
+        mbar_init(barGy, NEPI * 128);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == TMA_WARP) {
@@ -221,17 +224,17 @@ __global__ void __launch_bounds__(320, 1) kl_tc_dx_kernel(const DXArgs a) {
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if constexpr (NV > 0)
-        for (int q = tid; q < 2 * 2 * 4 * NV; q += blockDim.x) pacc[q] = 0.f;
+        for (int q = tid; q < NEPI * 2 * 4 * NV; q += blockDim.x) pacc[q] = 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 8) {
+    if (warp < 4 * NEPI) {
         // ===================== gy tile: [128 rows x 32*KS outputs] -> hi / lo K-major SWIZZLE_128B slabs =====================
         {
             const int c4 = KS * 8;                              // 16-byte chunks per row
-            for (int q = tid; q < BM * c4; q += 256) {
+            for (int q = tid; q < BM * c4; q += NEPI * 128) {
                 const int r = q / c4, o4 = q % c4;
                 const int o = o0 + o4 * 4;
                 float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -268,17 +271,17 @@ __global__ void __launch_bounds__(320, 1) kl_tc_dx_kernel(const DXArgs a) {
             if (has_prev) pn = ldx(a.prev, chunk0 + set);
         }
         const uint32_t tlane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        for (int lc = set; lc < nch; lc += 2) {
+        for (int lc = set; lc < nch; lc += NEPI) {
             const int chunk = chunk0 + lc;
             const int acc = lc % NACC;
             const float4 xc = xn, pc = pn;
-            if (lc + 2 < nch) {
-                xn = ldx(a.x, chunk + 2);
-                if (has_prev) pn = ldx(a.prev, chunk + 2);
+            if (lc + NEPI < nch) {
+                xn = ldx(a.x, chunk + NEPI);
+                if (has_prev) pn = ldx(a.prev, chunk + NEPI);
             }
             mbar_wait(barAccFull + 8 * acc, (lc / NACC) & 1);
             tc_fence_after();
-            float* pa = pacc + (set * 2 + ((lc >> 1) & 1)) * 4 * (NV > 0 ? NV : 4);
+            float* pa = pacc + (set * 2 + ((lc / NEPI) & 1)) * 4 * (NV > 0 ? NV : 4);
 #pragma unroll 1
             for (int ii = 0; ii < 4; ++ii) {
                 float g[FP];
@@ -405,7 +408,7 @@ static int dx_launch_k(const DXArgs& a, dim3 grid, size_t smem, cudaStream_t st)
     auto k = kl_tc_dx_kernel<NB, BR>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e) return (int)e;
-    k<<<grid, 320, smem, st>>>(a);
+    k<<<grid, NEPI * 128 + 64, smem, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 
@@ -444,7 +447,7 @@ int kl_tc_dx(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, c
     }
     const int KS = std::min(4, L.td_KS);
     const int NCOL = 4 * L.td_FP;
-    size_t smem = (size_t)KS * 2 * tcx::GY_SLAB + (size_t)tcx::NSW * 2 * NCOL * 128 + 2 * 2 * 4 * std::max(2 * L.NB, 4) * 4 + 512 + 1024;
+    size_t smem = (size_t)KS * 2 * tcx::GY_SLAB + (size_t)tcx::NSW * 2 * NCOL * 128 + tcx::NEPI * 2 * 4 * std::max(2 * L.NB, 4) * 4 + 512 + 1024;
     smem = std::max<size_t>(smem, 120 * 1024);              // one CTA per SM: the kernel allocates all of TMEM
     const dim3 grid((unsigned)mt, (unsigned)osplits, (unsigned)splits);
     switch (P->branch) {

@@ -19,6 +19,19 @@ if which == "ecg":
         F.cross_entropy(model(x), y).backward()
         torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
+elif which == "lv":
+    torch.manual_seed(0)
+    model = fetode.KANFET([2, 10, 2], grid_size=5).to(DEV)
+    opt = torch.optim.Adam(model.parameters(), lr=2e-3)
+    B = int(sys.argv[2]); n = 34
+    t = torch.linspace(0, 3.5, n + 1, dtype=torch.float64)
+    x0 = (torch.rand(B, 2) * 6.75 + 0.25).to(DEV); tgt = torch.randn(n + 1, B, 2, device=DEV)
+    def step():
+        model.reset_state()
+        opt.zero_grad(set_to_none=True)
+        pred = fetode.odeint(lambda tt, X: model(X), x0, t, method="rk4_classic")
+        ((pred - tgt) ** 2).mean().backward()
+        opt.step()
 elif which == "ett":
     torch.manual_seed(0)
     enc = torch.nn.Sequential(torch.nn.Flatten(), fetode.KAN([336 * 7, 128]), torch.nn.ReLU(), fetode.KAN([128, 64])).to(DEV)
