@@ -281,34 +281,67 @@ __global__ void __launch_bounds__(KB_THREADS) kl_bwd_dx_kernel(const KLBwdArgs a
 // ------------------------------------------------------------------------------------------
 // 3. unfold: folded-weight gradient -> the reference's parameters
 // ------------------------------------------------------------------------------------------
-// one thread per (o, i)
-__global__ void __launch_bounds__(128) kl_unfold_kernel(const KLBwdArgs a) {
+// CTA = 8 inputs x 32 outputs.  The folded gradient is read row-wise (output index contiguous), transposed through
+// shared memory, and the reference-layout gradients ([O, I, S], [O, I*NB], [O, I]) are written with the (input, s | j)
+// index contiguous, so both sides of the transpose are coalesced.
+constexpr int UF_TI = 8, UF_TO = 32, UF_THREADS = 256, UF_PAD = UF_TO + 1;
+
+__global__ void __launch_bounds__(UF_THREADS) kl_unfold_kernel(const KLBwdArgs a) {
+    extern __shared__ float uf_smem[];
     const KLLayout& L = a.L;
     const int I = L.I, O = L.O, F = L.F, S = L.S, NB = L.NB;
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)I * O) return;
-    const int o = (int)(idx % O), i = (int)(idx / O);
     const fetode_kanlayer_t& P = a.P;
-    const float* gW = a.ws + (size_t)i * F * O + o;
+    float* tile = uf_smem;                                   // [UF_TI][F][UF_PAD]
+    float* red_ls = tile + UF_TI * F * UF_PAD;               // [UF_TO]           branch_scaler partial sums
+    float* red_bp = red_ls + UF_TO;                          // [3][UF_TI][NB]    Ps, bias, coef partial sums
+    const int tid = threadIdx.x;
+    const int o0 = blockIdx.x * UF_TO, i0 = blockIdx.y * UF_TI;
     const float* gsum = a.ws + (size_t)I * F * O;
-    const size_t oi = (size_t)o * I + i;
-    if (a.g.base_weight) a.g.base_weight[oi] += gW[0];
-    {
-        const float sc = P.spline_scaler ? P.spline_scaler[oi] : 1.0f;
-        float gsc = 0.f;
-        for (int s = 0; s < S; ++s) {
-            const float g = gW[(size_t)(1 + s) * O];
-            if (a.g.spline_weight) a.g.spline_weight[oi * S + s] += g * sc;
-            gsc = fmaf(g, P.spline_weight[oi * S + s], gsc);
-        }
-        if (a.g.spline_scaler && P.spline_scaler) a.g.spline_scaler[oi] += gsc;
+    for (int q = tid; q < UF_TO + 3 * UF_TI * NB; q += UF_THREADS) red_ls[q] = 0.f;
+    for (int q = tid; q < UF_TI * F * UF_TO; q += UF_THREADS) {
+        const int oo = q % UF_TO, r = q / UF_TO;             // r = ii * F + f
+        const int i = i0 + r / F, o = o0 + oo;
+        tile[r * UF_PAD + oo] = (i < I && o < O) ? a.ws[((size_t)i0 * F + r) * O + o] : 0.f;
     }
+    __syncthreads();
+    // ---- base_weight [O, I]
+    for (int q = tid; q < UF_TO * UF_TI; q += UF_THREADS) {
+        const int ii = q % UF_TI, oo = q / UF_TI;
+        const int i = i0 + ii, o = o0 + oo;
+        if (i < I && o < O && a.g.base_weight) a.g.base_weight[(size_t)o * I + i] += tile[(ii * F) * UF_PAD + oo];
+    }
+    // ---- spline_weight [O, I, S] and spline_scaler [O, I] (S == 8 lanes per (o, i): shuffle reduction)
+    for (int q0 = 0; q0 < UF_TO * UF_TI * S; q0 += UF_THREADS) {
+        const int q = q0 + tid;
+        const int s = q % S, ii = (q / S) % UF_TI, oo = q / (S * UF_TI);
+        const int i = i0 + ii, o = o0 + oo;
+        const bool ok = oo < UF_TO && i < I && o < O;
+        float gsc = 0.f;
+        if (ok) {
+            const size_t oi = (size_t)o * I + i;
+            const float g = tile[(ii * F + 1 + s) * UF_PAD + oo];
+            const float sc = P.spline_scaler ? P.spline_scaler[oi] : 1.0f;
+            if (a.g.spline_weight) a.g.spline_weight[oi * S + s] += g * sc;
+            gsc = g * P.spline_weight[oi * S + s];
+        }
+        if (S == 8) {
+            gsc += __shfl_xor_sync(0xffffffffu, gsc, 1);
+            gsc += __shfl_xor_sync(0xffffffffu, gsc, 2);
+            gsc += __shfl_xor_sync(0xffffffffu, gsc, 4);
+            if (ok && s == 0 && a.g.spline_scaler && P.spline_scaler) a.g.spline_scaler[(size_t)o * I + i] += gsc;
+        } else if (ok && a.g.spline_scaler && P.spline_scaler) {
+            atomicAdd(a.g.spline_scaler + (size_t)o * I + i, gsc);
+        }
+    }
+    // ---- branch_weight [O, I*NB], branch_scaler [O], branch_bias [O], Ps / bias / coef [I, NB]
     if (P.branch != FETODE_BRANCH_NONE) {
-        const float lsc = P.scale_logistic * (P.branch_scaler ? P.branch_scaler[o] : 1.0f);
-        const float go = gsum[o];
-        float gls = 0.f;
-        for (int j = 0; j < NB; ++j) {
-            const float g = gW[(size_t)(1 + S + j) * O];
+        for (int q = tid; q < UF_TO * UF_TI * NB; q += UF_THREADS) {
+            const int j = q % NB, ii = (q / NB) % UF_TI, oo = q / (NB * UF_TI);
+            const int i = i0 + ii, o = o0 + oo;
+            if (i >= I || o >= O) continue;
+            const float lsc = P.scale_logistic * (P.branch_scaler ? P.branch_scaler[o] : 1.0f);
+            const float go = gsum[o];
+            const float g = tile[(ii * F + 1 + S + j) * UF_PAD + oo];
             const size_t wi = (size_t)o * I * NB + (size_t)i * NB + j;
             const float wraw = P.branch_weight[wi];
             float dw;                                   // dL / d(w = wraw * lsc)
@@ -317,18 +350,37 @@ __global__ void __launch_bounds__(128) kl_unfold_kernel(const KLBwdArgs a) {
                 const float Ps = P.bp[2][ij], bias = P.bp[3][ij], coef = P.bp[4][ij];
                 dw = g * (-2.0f * coef * Ps) + go * coef * (Ps + bias);
                 const float w = wraw * lsc;
-                if (a.g.bp[2]) atomicAdd(a.g.bp[2] + ij, g * (-2.0f * w * coef) + go * w * coef);
-                if (a.g.bp[3]) atomicAdd(a.g.bp[3] + ij, go * w * coef);
-                if (a.g.bp[4]) atomicAdd(a.g.bp[4] + ij, g * (-2.0f * w * Ps) + go * w * (Ps + bias));
+                float* rb = red_bp + ii * NB + j;
+                if (a.g.bp[2]) atomicAdd(rb, g * (-2.0f * w * coef) + go * w * coef);
+                if (a.g.bp[3]) atomicAdd(rb + UF_TI * NB, go * w * coef);
+                if (a.g.bp[4]) atomicAdd(rb + 2 * UF_TI * NB, g * (-2.0f * w * Ps) + go * w * (Ps + bias));
             } else {
                 dw = 2.0f * g;
             }
             if (a.g.branch_weight) a.g.branch_weight[wi] += dw * lsc;
-            gls = fmaf(dw, wraw * P.scale_logistic, gls);
+            if (a.g.branch_scaler && P.branch_scaler) atomicAdd(red_ls + oo, dw * wraw * P.scale_logistic);
         }
-        if (a.g.branch_scaler && P.branch_scaler) atomicAdd(a.g.branch_scaler + o, gls);
-        if (a.g.branch_bias && P.branch_bias && i == 0) a.g.branch_bias[o] += go;
+        __syncthreads();
+        if (a.g.branch_scaler && P.branch_scaler)
+            for (int oo = tid; oo < UF_TO; oo += UF_THREADS)
+                if (o0 + oo < O) atomicAdd(a.g.branch_scaler + o0 + oo, red_ls[oo]);
+        if (P.branch == FETODE_BRANCH_FERRO2D)
+            for (int q = tid; q < 3 * UF_TI * NB; q += UF_THREADS) {
+                const int which = q / (UF_TI * NB), r = q % (UF_TI * NB);
+                const int i = i0 + r / NB;
+                if (i < I && a.g.bp[2 + which]) atomicAdd(a.g.bp[2 + which] + (size_t)i * NB + r % NB, red_bp[q]);
+            }
+        if (a.g.branch_bias && P.branch_bias && blockIdx.y == 0)
+            for (int oo = tid; oo < UF_TO; oo += UF_THREADS)
+                if (o0 + oo < O) a.g.branch_bias[o0 + oo] += gsum[o0 + oo];
     }
+}
+
+static void kl_unfold_run(const KLBwdArgs& a, cudaStream_t st) {
+    const KLLayout& L = a.L;
+    const size_t smem = (size_t)(UF_TI * L.F * UF_PAD + UF_TO + 3 * UF_TI * std::max(L.NB, 1)) * 4;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kl_unfold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kl_unfold_kernel<<<dim3((L.O + UF_TO - 1) / UF_TO, (L.I + UF_TI - 1) / UF_TI), UF_THREADS, smem, st>>>(a);
 }
 
 template <int BR>
@@ -376,10 +428,7 @@ static int kl_bwd_launch(KLBwdArgs& a, cudaStream_t st) {
         }
     }
     // 3. unfold
-    {
-        const long long n = (long long)L.I * L.O;
-        kl_unfold_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(a);
-    }
+    kl_unfold_run(a, st);
     return FETODE_LAUNCH_RC();
 }
 
@@ -393,8 +442,7 @@ int kl_unfold_launch(const fetode_kanlayer_t* P, const fetode_kanlayer_grads_t* 
     if (grads) a.g = *grads;
     a.ws = ws;
     a.L = kl_layout(P->in_features, P->out_features, P->grid_size, P->num_basis);
-    const long long n = (long long)a.L.I * a.L.O;
-    kl_unfold_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(a);
+    kl_unfold_run(a, st);
     return FETODE_LAUNCH_RC();
 }
 
