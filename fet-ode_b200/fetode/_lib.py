@@ -104,7 +104,8 @@ def ptr(t: torch.Tensor | None) -> C.c_void_p:
 
 
 def stream() -> C.c_void_p:
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    """cudaStream_t of torch's current stream on the current device (raw handle, no Stream object built)."""
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))
 
 
 def f32c(t: torch.Tensor) -> torch.Tensor:

@@ -114,8 +114,44 @@ def _step_staged(kind: str, f, t0, dt: float, y, tt):
     raise ValueError(kind)
 
 
+class _TimeTable:
+    """Stage times of a fixed-grid solve as 0-dim views of ONE device tensor: a single asynchronous H2D copy per solve
+    instead of a synchronising ``torch.tensor(x, device=...)`` per right-hand-side call (which would stop the host from
+    running ahead of the GPU).  ``steps`` = [(t0, dt), ...]; the values are formed with the same float expressions
+    as _step_staged uses, so the lookup is exact; anything else falls back to a fresh tensor."""
+
+    def __init__(self, steps, dtype, device):
+        vals = []
+        for t0, dt in steps:
+            vals += [t0, t0 + 0.5 * dt, t0 + dt, t0 + dt / 3.0, t0 + 2.0 * dt / 3.0]
+        self.dtype, self.device = dtype, device
+        self.index = {}
+        for i, v in enumerate(vals):
+            self.index.setdefault(v, i)
+        self.dev = None
+        if vals:
+            host = torch.tensor(vals, dtype=dtype)
+            if torch.device(device).type == "cuda":
+                self._host = host.pin_memory()
+                self.dev = self._host.to(device, non_blocking=True)
+            else:
+                self.dev = host.to(device)
+
+    def __call__(self, x: float):
+        i = self.index.get(x)
+        if i is None or self.dev is None:
+            return torch.tensor(x, dtype=self.dtype, device=self.device)
+        return self.dev[i]
+
+
+def _time_dtype(t: torch.Tensor):
+    return t.dtype if t.is_floating_point() else torch.float32
+
+
 def _time_tensor_factory(t: torch.Tensor, device):
-    dtype = t.dtype if t.is_floating_point() else torch.float32
+    """Adaptive solvers (dopri5): the stage times are only known step by step, and the accept / reject decision
+    synchronises with the device once per step anyway."""
+    dtype = _time_dtype(t)
 
     def tt(x: float):
         return torch.tensor(x, dtype=dtype, device=device)
@@ -219,11 +255,11 @@ def _func_requires_grad(func) -> bool:
 
 
 def _staged_fixed(func, y0, t, times, kind, options):
-    tt = _time_tensor_factory(t, y0.device)
     y = ops.f32c(y0)
     sol = [y]
     step_size = options.get("step_size")
     if step_size is None:
+        tt = _TimeTable([(a, b - a) for a, b in zip(times, times[1:])], _time_dtype(t), y0.device)
         for a, b in zip(times, times[1:]):
             y = _step_staged(kind, func, a, b - a, y, tt)
             sol.append(y)
@@ -234,6 +270,7 @@ def _staged_fixed(func, y0, t, times, kind, options):
         n = int(math.ceil((t1 - t0) / step_size + 1))
         grid = [t0 + k * step_size for k in range(n)]
         grid[-1] = t1
+        tt = _TimeTable([(a, b - a) for a, b in zip(grid, grid[1:])], _time_dtype(t), y0.device)
         j = 1
         for a, b in zip(grid, grid[1:]):
             y1 = _step_staged(kind, func, a, b - a, y, tt)
@@ -272,7 +309,7 @@ def _integrate(kind, odefunc, h0, t0, t1, n_steps):
         from .training import fused_fixed_autograd
         return fused_fixed_autograd(model, h0, times, kind, uniform_dt=dt)[-1]
     h = ops.f32c(h0)
-    tt = lambda x: torch.as_tensor(x, device=h0.device, dtype=h0.dtype)
+    tt = _TimeTable([(t0 + i * dt, dt) for i in range(n_steps)], h0.dtype, h0.device)
     for i in range(n_steps):
         h = _step_staged(kind, odefunc, t0 + i * dt, dt, h, tt)
     return h
@@ -298,7 +335,8 @@ def odeint_rk4(func, z0, t, n_substeps=4):
     times = [float(v) for v in t.detach().cpu().double().tolist()]
     z = ops.f32c(z0)
     out = [z]
-    tt = lambda x: torch.as_tensor(x, device=z0.device, dtype=z0.dtype)
+    tt = _TimeTable([(a + s * ((b - a) / float(n_substeps)), (b - a) / float(n_substeps))
+                     for a, b in zip(times, times[1:]) for s in range(n_substeps)], z0.dtype, z0.device)
     for a, b in zip(times, times[1:]):
         h = (b - a) / float(n_substeps)
         for s in range(n_substeps):

@@ -41,26 +41,44 @@ class LayerView:
     @property
     def branch(self) -> int:
         m = self.m
-        if not getattr(m, "enable_logistic_basis", getattr(m, "use_logistic_basis", False)):
+        d = m.__dict__
+        if not d.get("enable_logistic_basis", d.get("use_logistic_basis", False)):
             return BRANCH_NONE
-        return BRANCH_FERRO2D if hasattr(m.logistic_basis, "Ec") else BRANCH_LOGISTIC
+        lb = m._modules.get("logistic_basis")
+        if lb is None:
+            lb = m.logistic_basis
+        return BRANCH_FERRO2D if "Ec" in lb._parameters or hasattr(lb, "Ec") else BRANCH_LOGISTIC
+
+    @staticmethod
+    def _get(m, name):
+        """Parameter / buffer `name` of module m without nn.Module.__getattr__'s fallback chain (hot path)."""
+        t = m._parameters.get(name)
+        if t is None:
+            t = m._buffers.get(name)
+        if t is None:
+            t = getattr(m, name, None)
+        return t
 
     def tensors(self) -> List[Tuple[str, Optional[torch.Tensor]]]:
         m = self.m
+        g = self._get
         br = self.branch
-        out = [("grid", m.grid), ("base_weight", m.base_weight), ("spline_weight", m.spline_weight),
-               ("spline_scaler", getattr(m, "spline_scaler", None) if getattr(m, "enable_standalone_scale_spline", True) else None)]
+        d = m.__dict__
+        out = [("grid", g(m, "grid")), ("base_weight", g(m, "base_weight")), ("spline_weight", g(m, "spline_weight")),
+               ("spline_scaler", g(m, "spline_scaler") if d.get("enable_standalone_scale_spline", True) else None)]
         if br == BRANCH_NONE:
             out += [("branch_weight", None), ("branch_scaler", None), ("branch_bias", None)]
             out += [(f"bp{i}", None) for i in range(5)]
         else:
-            out.append(("branch_weight", m.logistic_weight))
-            out.append(("branch_scaler", getattr(m, "logistic_scaler", None)
-                        if getattr(m, "enable_standalone_scale_logistic", False) else None))
-            out.append(("branch_bias", getattr(m, "logistic_bias", None)))
+            out.append(("branch_weight", g(m, "logistic_weight")))
+            out.append(("branch_scaler", g(m, "logistic_scaler") if d.get("enable_standalone_scale_logistic", False) else None))
+            out.append(("branch_bias", g(m, "logistic_bias")))
             names = _BP_NAMES[br]
+            lb = m._modules.get("logistic_basis")
+            if lb is None:
+                lb = m.logistic_basis
             for i in range(5):
-                out.append((f"bp{i}", getattr(m.logistic_basis, names[i]) if i < len(names) else None))
+                out.append((f"bp{i}", g(lb, names[i]) if i < len(names) else None))
         return out
 
     def struct(self, tensors=None) -> KanLayer:
@@ -87,9 +105,9 @@ class LayerView:
         s.alpha = float(getattr(lb, "alpha", 0.8))
         return s
 
-    def key(self):
-        return tuple((n, None if t is None else (t.data_ptr(), t._version, tuple(t.shape)))
-                     for n, t in self.tensors())
+    def key(self, tensors=None):
+        return tuple(None if t is None else (t.data_ptr(), t._version)
+                     for _, t in (tensors if tensors is not None else self.tensors()))
 
 
 def _keep(owner, t: torch.Tensor) -> torch.Tensor:
@@ -115,10 +133,10 @@ class LayerPack:
         self.blob: Optional[torch.Tensor] = None
         self.struct: Optional[KanLayer] = None
 
-    def get(self) -> Tuple[KanLayer, torch.Tensor]:
-        k = self.view.key()
+    def get(self, tensors=None) -> Tuple[KanLayer, torch.Tensor]:
+        k = self.view.key(tensors)
         if k != self._key:
-            s = self.view.struct()
+            s = self.view.struct(tensors)
             n = lib().fetode_kanlinear_wcat_floats(C.byref(s))
             if n < 0:
                 raise RuntimeError("fetode: KANLinear configuration not supported by the sm_100a kernels "
@@ -132,10 +150,10 @@ class LayerPack:
         return self.struct, self.blob
 
 
-def kanlinear_fwd(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor]) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+def kanlinear_fwd(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor], tensors=None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """y = KANLinear(x2d); returns (y, new_prev) where new_prev (FERRO2D only) is x2d itself."""
     _require_cuda(x2d, "input")
-    s, blob = pack.get()
+    s, blob = pack.get(tensors)
     B = x2d.shape[0]
     y = torch.empty(B, s.out_features, dtype=torch.float32, device=x2d.device)
     ferro = s.branch == BRANCH_FERRO2D
@@ -152,29 +170,29 @@ class KanLinearFn(torch.autograd.Function):
     graph, as in the reference (ferro_class.py:553-554 detaches the snapshots)."""
 
     @staticmethod
-    def forward(ctx, pack: LayerPack, prev, x2d, *params):
-        y, _ = kanlinear_fwd(pack, x2d, prev)
-        ctx.pack, ctx.prev = pack, prev
+    def forward(ctx, pack: LayerPack, prev, tens, x2d, *params):
+        y, _ = kanlinear_fwd(pack, x2d, prev, tens)
+        ctx.pack, ctx.prev, ctx.tens = pack, prev, tens
         ctx.save_for_backward(x2d)
-        ctx.names = [n for n, t in pack.view.tensors() if t is not None and n != "grid"]
+        ctx.names = [n for n, t in tens if t is not None and n != "grid"]
         return y
 
     @staticmethod
     def backward(ctx, gy):
         (x2d,) = ctx.saved_tensors
         pack = ctx.pack
-        s, blob = pack.get()
+        s, blob = pack.get(ctx.tens)
         L = lib()
         gy = f32c(gy)
         B = x2d.shape[0]
-        need_x = ctx.needs_input_grad[2]
+        need_x = ctx.needs_input_grad[3]
         gx = torch.empty_like(x2d) if need_x else None
         g = KanLayerGrads()
         outs = []
-        tens = dict(pack.view.tensors())
+        tens = dict(ctx.tens)
         # one zero-filled flat buffer for every wanted parameter gradient (the kernels accumulate into it):
         # a single fill launch instead of one per parameter
-        want = [ctx.needs_input_grad[3 + idx] for idx in range(len(ctx.names))]
+        want = [ctx.needs_input_grad[4 + idx] for idx in range(len(ctx.names))]
         sizes = [(tens[n].numel() + 3) // 4 * 4 if w else 0 for n, w in zip(ctx.names, want)]
         n_grad = sum(sizes)
         n_ws = max(int(L.fetode_kanlinear_bwd_ws_floats(C.byref(s))), 1)
@@ -194,14 +212,15 @@ class KanLinearFn(torch.autograd.Function):
         check(L.fetode_kanlinear_bwd(C.byref(s), ptr(blob), ptr(x2d), ptr(ctx.prev) if ferro else None,
                                      C.c_int(1 if ctx.prev is None else 0), ptr(gy), ptr(gx), C.byref(g),
                                      ptr(ws), C.c_int64(B), stream()), "kanlinear_bwd")
-        return (None, None, gx, *outs)
+        return (None, None, None, gx, *outs)
 
 
 def kanlinear_apply(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor]) -> torch.Tensor:
-    params = [t for n, t in pack.view.tensors() if t is not None and n != "grid"]
+    tens = pack.view.tensors()
+    params = [t for n, t in tens if t is not None and n != "grid"]
     if torch.is_grad_enabled() and (x2d.requires_grad or any(p.requires_grad for p in params)):
-        return KanLinearFn.apply(pack, prev, x2d, *params)
-    return kanlinear_fwd(pack, x2d, prev)[0]
+        return KanLinearFn.apply(pack, prev, tens, x2d, *params)
+    return kanlinear_fwd(pack, x2d, prev, tens)[0]
 
 
 # --------------------------------------------------------------------------------------
