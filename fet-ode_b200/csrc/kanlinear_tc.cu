@@ -84,12 +84,21 @@ __device__ __forceinline__ void tc_branch_features(float x, float prev, float gl
     for (int j = 0; j < NB; ++j) f[j] = r[j];
 }
 
+// producer groups taking every NPAR-th input pair.  Measured on B200 (768->128, B=4096): 2 groups 0.129 ms, 3 groups
+// 0.130 ms -- with a 3-stage ring (2.4 pairs of K) a third group has no free slot to fill, so 2 it is.
+template <int NB, int BR> struct TCShape {
+    static constexpr int NROLE = NB > 0 ? 2 : 1;
+    static constexpr int NPAR = 2;
+    static constexpr int THREADS = (4 * NROLE * NPAR + 3) * 32;
+};
+
 template <int NB, int BR>
-__global__ void __launch_bounds__(NB > 0 ? 608 : 352, 1) kl_tc_fwd_kernel(const TCArgs a) {
+__global__ void __launch_bounds__(TCShape<NB, BR>::THREADS, 1) kl_tc_fwd_kernel(const TCArgs a) {
     constexpr int CPG = 5 + NB / 2;                               // 16-byte chunks per pair of inputs
     constexpr int SPU = 2 * CPG;                                  // 32-wide K stages per 32-input unit
     constexpr int NROLE = NB > 0 ? 2 : 1;                         // spline | branch
-    constexpr int NSETS = 2 * NROLE;                              // x 2 pair parities
+    constexpr int NPAR = TCShape<NB, BR>::NPAR;                   // producer groups taking every NPAR-th input pair
+    constexpr int NSETS = NPAR * NROLE;
     constexpr int NPROD = 128 * NSETS;
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const int BN = a.BN;
@@ -182,16 +191,21 @@ __global__ void __launch_bounds__(NB > 0 ? 608 : 352, 1) kl_tc_fwd_kernel(const 
             if (!live || i >= I) return make_float2(0.f, 0.f);
             return __ldg(reinterpret_cast<const float2*>(rowp + i));
         };
+        int tab_u = -1;                                           // unit whose table slab this thread currently holds
         float2 xn = ldx(xrow, unit0 * 32 + 2 * par);
         float2 pn = (role == 1 && has_prev) ? ldx(prow, unit0 * 32 + 2 * par) : make_float2(0.f, 0.f);
 #pragma unroll 1
-        for (int g2 = par; g2 < npairs; g2 += 2) {
+        for (int g2 = par; g2 < npairs; g2 += NPAR) {
             const int u = g2 >> 4, g = g2 & 15;
-            if (g == par) mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
+            if (u != tab_u) {
+                if (tab_u >= 0) mbar_arrive(barTabEmpty + 8 * (tab_u & 1));
+                mbar_wait(barTabFull + 8 * (u & 1), (u >> 1) & 1);
+                tab_u = u;
+            }
             const float2 xc = xn, pc = pn;
-            if (g2 + 2 < npairs) {
-                xn = ldx(xrow, unit0 * 32 + 2 * (g2 + 2));
-                if (role == 1 && has_prev) pn = ldx(prow, unit0 * 32 + 2 * (g2 + 2));
+            if (g2 + NPAR < npairs) {
+                xn = ldx(xrow, unit0 * 32 + 2 * (g2 + NPAR));
+                if (role == 1 && has_prev) pn = ldx(prow, unit0 * 32 + 2 * (g2 + NPAR));
             }
             const float* tg = tabs + (size_t)((u & 1) * 32 + g * 2) * L.TAB;
             if (role == 0) {
@@ -210,8 +224,8 @@ __global__ void __launch_bounds__(NB > 0 ? 608 : 352, 1) kl_tc_fwd_kernel(const 
                     for (int c = 0; c < NB / 2; ++c) put(g2 * CPG + 5 + c, f + 4 * c);
                 }
             }
-            if (g == 14 + par) mbar_arrive(barTabEmpty + 8 * (u & 1));
         }
+        if (tab_u >= 0) mbar_arrive(barTabEmpty + 8 * (tab_u & 1));
         advance(nit - 1);
         fence_proxy_async();
         mbar_arrive(barFullA + 8 * (cur % NSTAGE));
@@ -294,7 +308,7 @@ __global__ void __launch_bounds__(NB > 0 ? 608 : 352, 1) kl_tc_fwd_kernel(const 
                     // rotate over three accumulators and the 2^-11-times-smaller corrections go to a fourth; the
                     // epilogue adds the four in registers (round-to-nearest).
                     umma_tf32(tmem_base + (uint32_t)((it % 3) * BN), dAh, dBh, idesc, !(it < 3 && j == 0));
-                    umma_tf32(tmem_base + (uint32_t)(3 * BN), dAh, dBl, idesc, (it | j) != 0);
+                                    umma_tf32(tmem_base + (uint32_t)(3 * BN), dAh, dBl, idesc, (it | j) != 0);
                     umma_tf32(tmem_base + (uint32_t)(3 * BN), dAl, dBh, idesc, 1);
                 }
                 umma_commit(barEmpty + 8 * s);
@@ -348,7 +362,7 @@ static int tc_launch_k(const TCArgs& a, dim3 grid, size_t smem, cudaStream_t st)
     auto k = kl_tc_fwd_kernel<NB, BR>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e) return (int)e;
-    k<<<grid, NB > 0 ? 608 : 352, smem, st>>>(a);
+    k<<<grid, TCShape<NB, BR>::THREADS, smem, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 

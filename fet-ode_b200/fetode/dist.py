@@ -52,6 +52,21 @@ def allreduce_gradients(model_or_params, average: bool = True, local_rows: Optio
     average=True divides by the world size (loss = mean over the LOCAL shard, equal shards).  With unequal shards
     pass local_rows / global_rows: gradients are weighted local_rows / global_rows before the sum, which equals
     the gradient of the mean over the global batch."""
+    if getattr(model_or_params, "built", False) and hasattr(model_or_params, "flat_grad"):
+        # fetode.optim.FlatAdam after its first step: the gradients already live in one flat buffer
+        opt = model_or_params
+        opt._sync_grads()
+        flat = opt.flat_grad
+        rank, w = world()
+        if local_rows is not None and global_rows is not None:
+            flat.mul_(float(local_rows) / float(global_rows))
+        if w > 1:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+            if average and local_rows is None:
+                flat.div_(w)
+        return flat
+    if hasattr(model_or_params, "all_params"):
+        model_or_params = model_or_params.all_params
     params = _grad_params(model_or_params.parameters() if hasattr(model_or_params, "parameters") else model_or_params)
     if not params:
         return None

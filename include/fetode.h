@@ -229,6 +229,19 @@ FETODE_API int fetode_kuramoto_bwd(const float* ckpt, const float* theta_final_f
                         const float* gfeat, float* gx /* or NULL */, float* gK /* accum */,
                         float* gomega /* accum */, int64_t B, void* stream);
 
+/* ---- fused optimiser step on one flat fp32 buffer ------------------------------
+ * Replaces torch.optim.Adam.step (train_kanfet_node_predprey.py:171,257) and
+ * clip_grad_norm_ + torch.optim.AdamW.step (train_ecg_kan_fet_nn_ode.py:1093,1110-1111) for parameters, gradients
+ * and moments that live in flat buffers of n floats (the buffer the gradient all-reduce uses).
+ * fetode_sumsq_f32: *sumsq (device double) = sum_i g_i^2.
+ * fetode_adam_flat: one Adam (decoupled == 0: weight_decay is L2, added to g) or AdamW (decoupled != 0) step number
+ *   `step` (1-based, bias correction as torch/optim/adam.py).  With sumsq != NULL the gradient is first scaled by
+ *   min(1, max_norm / (sqrt(*sumsq) + 1e-6)) and written back (clip_grad_norm_ semantics) -- no host synchronisation. */
+FETODE_API int fetode_sumsq_f32(const float* g, int64_t n, double* sumsq, void* stream);
+FETODE_API int fetode_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                     float eps, float weight_decay, int decoupled, int64_t step, float max_norm,
+                     const double* sumsq /* device, or NULL */, void* stream);
+
 /* ---- probes used by bench.py for the roofline denominators --------------------------- */
 /* runs an FFMA-only kernel and returns achieved TFLOP/s in *tflops (host) */
 FETODE_API int fetode_probe_fp32_peak(double* tflops, void* stream);
