@@ -1,6 +1,7 @@
 // tc_common.cuh -- PTX wrappers shared by the tcgen05 kernels (kanlinear_tc.cu forward, kanlinear_tc_bwd.cu backward):
 // mbarriers, the TMA bulk-copy engine, tcgen05.mma / commit / fences, UMMA shared-memory descriptors.
 #pragma once
+#include <cstdio>
 #include "kanlinear.cuh"
 
 namespace fetode {
@@ -18,14 +19,22 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// Spins on try_wait.  A wait that does not complete within ~2^28 polls (seconds; every legitimate wait in these
+// kernels is microseconds) reports itself and traps: a protocol bug then surfaces as a CUDA error instead of a hung GPU.
+static __device__ __noinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
+    printf("fetode: mbarrier wait timed out: smem 0x%x parity %u block (%d,%d,%d) thread %d\n", bar, parity,
+           (int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z, (int)threadIdx.x);
+    __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
+    uint32_t done = 0, polls = 0;
     while (!done) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
             "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && ++polls == (1u << 28)) mbar_timeout(bar, parity);
     }
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
