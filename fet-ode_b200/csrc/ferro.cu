@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(256) ferro_elem_fwd_kernel(const FerroArgs a) 
             if (a.gate_out) a.gate_out[e] = up ? 1 : 0;
             if (a.basis_out) a.basis_out[e] = out;
             if (a.apply_sigmoid) out = sigm(out);                               // KANFeatureMixer :419
+            if (a.apply_sigmoid == 2 && out != out) out = 0.f;                  // + nan_to_num(nan=0) :465 (sigmoid is never +-inf)
         }
         a.out[e] = out;
     }
@@ -266,6 +267,7 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
             if (a.apply_sigmoid) {
                 const float y = sigm(fmaf(2.0f * Ps, s, -Ps) + bias);
                 go *= y * (1.0f - y);
+                if (a.apply_sigmoid == 2 && y != y) go = 0.f;                   // nan_to_num passes no gradient at a NaN
             }
             aPs = fmaf(go, 2.0f * s - 1.0f, aPs);
             ab += go;

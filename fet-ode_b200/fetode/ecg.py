@@ -54,7 +54,9 @@ class LogisticBasis(nn.Module):
                 self._row = self.prev_x[0, :, 0].to(device).contiguous()
         return self._row
 
-    def _call(self, x, apply_sigmoid: bool):
+    def _call(self, x, apply_sigmoid):
+        """apply_sigmoid: False/0 = basis only, True/1 = sigmoid fused in (KANFeatureMixer), 2 = sigmoid followed by
+        nan_to_num(nan=0, posinf=1e3, neginf=-1e3) fused in (MLPKANODEFunc.forward :464-465)."""
         if x.dim() != 2 or x.size(1) != self.in_dim:
             raise ValueError(f"x must be (B,{self.in_dim}), got {tuple(x.shape)}")
         if self.branch_breaking_point != 0.5:
@@ -65,12 +67,14 @@ class LogisticBasis(nn.Module):
         new_row = torch.empty(self.in_dim, dtype=torch.float32, device=x2.device)
         noisy = self.use_noise and self.noise_std != 0.0
         out, side = ops.ferro_apply(self, ops.FERRO_HARDGATE, x2, prev, want_gate=True,
-                                    apply_sigmoid=apply_sigmoid and not noisy, prev_out=new_row,
+                                    apply_sigmoid=0 if noisy else int(apply_sigmoid), prev_out=new_row,
                                     gate_slope=self.gate_slope, alpha=0.5)
         if noisy:
             out = out + torch.randn_like(out) * self.noise_std
             if apply_sigmoid:
                 out = torch.sigmoid(out)
+            if int(apply_sigmoid) == 2:
+                out = torch.nan_to_num(out, nan=0.0, posinf=1e3, neginf=-1e3)
         self._row = new_row
         self.prev_x = new_row.view(1, -1, 1).expand(1, self.in_dim, self.num_basis)
         self.branch_state = side["gate"]                                   # uint8 [B,in,K]: 1 = up branch
@@ -88,11 +92,15 @@ class KANFeatureMixer(nn.Module):
         self.basis = LogisticBasis(dim, num_basis)
         self.act = nn.Sigmoid() if act is None else act
 
-    def forward(self, x):
+    def forward(self, x, nan_to_num: bool = False):
+        """nan_to_num=True additionally applies torch.nan_to_num(phi, nan=0, posinf=1e3, neginf=-1e3) -- in the same
+        kernel when the activation is the default Sigmoid."""
         if isinstance(self.act, nn.Sigmoid):
-            phi = self.basis._call(x, True)
+            phi = self.basis._call(x, 2 if nan_to_num else 1)
         else:
             phi = self.act(self.basis(x))
+            if nan_to_num:
+                phi = torch.nan_to_num(phi, nan=0.0, posinf=1e3, neginf=-1e3)
         return phi.reshape(x.size(0), -1)
 
 
@@ -113,16 +121,27 @@ class MLPKANODEFunc(nn.Module):
         nn.init.normal_(self.out.weight, mean=0.0, std=init_out_std)
         self.log_alpha = nn.Parameter(torch.tensor(-3.0))
         self.scale = nn.Parameter(torch.tensor(1.0))
+        self._gain_key, self._gain_val = None, None
+
+    def _gain(self):
+        """scale * softplus(log_alpha) (:480), one autograd node shared by every right-hand-side call between two
+        parameter updates instead of three tiny launches (and their backward) per call."""
+        key = (self.scale._version, self.log_alpha._version, self.scale.data_ptr(), self.log_alpha.data_ptr(),
+               torch.is_grad_enabled())
+        if self._gain_key != key or (self._gain_val.requires_grad and self._gain_val.grad_fn is None):
+            self._gain_val = self.scale * F.softplus(self.log_alpha)
+            self._gain_key = key
+        return self._gain_val
 
     def forward(self, t, h):
         h = self.ln(h)
-        h = self.h_bound * torch.tanh(h / self.h_bound)
-        phi = self.h_feat(h)
-        phi = torch.nan_to_num(phi, nan=0.0, posinf=1e3, neginf=-1e3)
+        # h_bound * tanh(h / h_bound) :461 ; both scalings are exact no-ops for the default h_bound = 1
+        h = torch.tanh(h) if self.h_bound == 1.0 else self.h_bound * torch.tanh(h / self.h_bound)
+        phi = self.h_feat(h, nan_to_num=True)                # sigmoid + nan_to_num fused into the neuron kernel :464-465
         z = self.act(self.kan1(phi))
         z = self.act(self.kan2(z))
         dh = self.out(z)
-        return self.scale * F.softplus(self.log_alpha) * dh
+        return self._gain() * dh
 
 
 class No_MLP_KANODEFunc(nn.Module):

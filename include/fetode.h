@@ -203,7 +203,8 @@ typedef struct fetode_ferro {
     int32_t variant, in_dim, out_dim, num_basis;
     const float *k, *Ec, *Ps, *bias, *coef;
     float gate_slope, alpha;                   /* hard gate: gate_slope=5, alpha=breaking point 0.5 */
-    int32_t apply_sigmoid;                     /* HARDGATE only: KANFeatureMixer's sigmoid :419 */
+    int32_t apply_sigmoid;                     /* HARDGATE only: 1 = KANFeatureMixer's sigmoid :419 fused in;
+                                                  2 = sigmoid then nan_to_num(nan=0) (MLPKANODEFunc.forward :464-465) */
 } fetode_ferro_t;
 
 typedef struct fetode_ferro_grads { float *k, *Ec, *Ps, *bias, *coef; } fetode_ferro_grads_t;
