@@ -131,7 +131,11 @@ def ecg_train(B, skip_cpu):
         fopt.clip_grad_norm_(1.0)
         fopt.step()
     fl = gpu_ms(fstep, iters=3, warm=2)
-    return {"gpu_fwd_bwd_flatadamw_ms": fl, "config": f"3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, AdamW, clip 1.0, B={B}",
+    # the same step captured once into a CUDA graph and replayed (fetode/graphs.py): no host work per launch
+    gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, max_norm=1.0, warmup=2)
+    gl = gpu_ms(lambda: gstep(gstep.x, gstep.y), iters=5, warm=2)
+    return {"gpu_fwd_bwd_graph_ms": gl, "gpu_fwd_bwd_flatadamw_ms": fl, "config": f"3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, AdamW, clip 1.0, B={B}",
             "gpu_fwd_bwd_opt_ms": ms, "gpu_fwd_ms": fms, "sample_steps_per_s": B * 8 / ms * 1e3}
 
 
@@ -176,8 +180,11 @@ def mnist_train(B, skip_cpu):
         F.cross_entropy(model(x), y).backward()
         opt.step()
     ms = gpu_ms(step)
+    gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, warmup=2)
+    gl = gpu_ms(lambda: gstep(gstep.x, gstep.y))
     return {"config": f"5: MNIST KuramotoKANClassifier(steps=10, nb=8), CE, AdamW, B={B}", "gpu_fwd_bwd_opt_ms": ms,
-            "image_steps_per_s": B / ms * 1e3}
+            "image_steps_per_s": B / ms * 1e3, "gpu_fwd_bwd_graph_ms": gl, "graph_image_steps_per_s": B / gl * 1e3}
 
 
 def main():

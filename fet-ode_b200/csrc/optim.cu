@@ -44,7 +44,18 @@ struct AdamArgs {
     long long n;
     float lr, beta1, beta2, eps, wd, max_norm, step_size, bc2_sqrt;
     int decoupled;
+    const float* dev_bc;           // device {step_size, bc2_sqrt} (step counter kept on the device), or null
 };
+
+// Device-resident step counter for CUDA-graph capture: state = {int64 step; float step_size; float bc2_sqrt}.
+__global__ void adam_advance_kernel(long long* state, float lr, float beta1, float beta2) {
+    const long long step = ++state[0];
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    float* f = reinterpret_cast<float*>(state + 1);
+    f[0] = (float)((double)lr / bc1);
+    f[1] = (float)sqrt(bc2);
+}
 
 __global__ void __launch_bounds__(256) adam_flat_kernel(const AdamArgs a) {
     float coef = 1.0f;
@@ -52,6 +63,8 @@ __global__ void __launch_bounds__(256) adam_flat_kernel(const AdamArgs a) {
         const float total = (float)sqrt(*a.sumsq);
         coef = fminf(a.max_norm / (total + 1e-6f), 1.0f);
     }
+    const float step_size = a.dev_bc ? a.dev_bc[0] : a.step_size;
+    const float bc2_sqrt = a.dev_bc ? a.dev_bc[1] : a.bc2_sqrt;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
         float p = a.p[i], g = a.g[i], m = a.m[i], v = a.v[i];
@@ -62,8 +75,8 @@ __global__ void __launch_bounds__(256) adam_flat_kernel(const AdamArgs a) {
         }
         m = fmaf(g - m, 1.0f - a.beta1, m);
         v = fmaf(v, a.beta2, (1.0f - a.beta2) * g * g);
-        const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
-        p = p - a.step_size * (m / denom);
+        const float denom = sqrtf(v) / bc2_sqrt + a.eps;
+        p = p - step_size * (m / denom);
         a.p[i] = p; a.m[i] = m; a.v[i] = v;
     }
 }
@@ -93,6 +106,7 @@ extern "C" int fetode_adam_flat(float* p, float* g, float* m, float* v, int64_t 
     a.p = p; a.g = g; a.m = m; a.v = v; a.sumsq = sumsq; a.n = n;
     a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay; a.max_norm = max_norm;
     a.decoupled = decoupled;
+    a.dev_bc = nullptr;
     // python-float (double) bias corrections rounded once, as torch does with scalar step counts
     const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
     const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
@@ -100,5 +114,25 @@ extern "C" int fetode_adam_flat(float* p, float* g, float* m, float* v, int64_t 
     a.bc2_sqrt = (float)std::sqrt(bc2);
     const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 8);
     adam_flat_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_adam_flat_graph(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                                      float beta2, float eps, float weight_decay, int decoupled, int64_t* state,
+                                      float max_norm, const double* sumsq, void* stream) {
+    FETODE_CHECK_ARG(p && g && m && v && n >= 0 && state);
+    FETODE_CHECK_ARG(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f);
+    cudaStream_t st = (cudaStream_t)stream;
+    adam_advance_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(state), lr, beta1, beta2);
+    int rc = FETODE_LAUNCH_RC();
+    if (rc || n == 0) return rc;
+    AdamArgs a;
+    a.p = p; a.g = g; a.m = m; a.v = v; a.sumsq = sumsq; a.n = n;
+    a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay; a.max_norm = max_norm;
+    a.decoupled = decoupled;
+    a.step_size = 0.f; a.bc2_sqrt = 1.f;
+    a.dev_bc = reinterpret_cast<const float*>(state + 1);
+    const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 8);
+    adam_flat_kernel<<<blocks, 256, 0, st>>>(a);
     return FETODE_LAUNCH_RC();
 }

@@ -12,11 +12,11 @@ from . import _lib  # noqa: F401
 from .efficientkan import KAN, KANFET, KANLinear, LogisticBasis  # noqa: F401
 from .ferro_class import (BatchedFerroelectricBasis, FerroelectricBasis, NoisyBatchedFerroelectricBasis,  # noqa: F401
                           NoisyFerroelectricBasis, TwoDimensionFerroelectricBasis)
-from . import ecg, mnist_kuramoto_kan, optim  # noqa: F401
+from . import ecg, graphs, mnist_kuramoto_kan, optim  # noqa: F401
 from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odeint,  # noqa: F401
                      odeint_rk4)
 
 __all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "FerroelectricBasis",
            "NoisyFerroelectricBasis", "BatchedFerroelectricBasis", "NoisyBatchedFerroelectricBasis", "ecg",
-           "mnist_kuramoto_kan", "optim", "odeint",
+           "mnist_kuramoto_kan", "optim", "graphs", "odeint",
            "integrate_euler", "integrate_rk2", "integrate_rk4", "odeint_rk4", "as_rhs"]

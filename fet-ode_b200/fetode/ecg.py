@@ -129,6 +129,9 @@ class MLPKANODEFunc(nn.Module):
         key = (self.scale._version, self.log_alpha._version, self.scale.data_ptr(), self.log_alpha.data_ptr(),
                torch.is_grad_enabled())
         if self._gain_key != key or (self._gain_val.requires_grad and self._gain_val.grad_fn is None):
+            # drop the stale node first: while it lives, its graph pins the parameters' AccumulateGrad nodes (and the
+            # stream they were created on), which a later CUDA-graph capture on another stream cannot use
+            self._gain_val = None
             self._gain_val = self.scale * F.softplus(self.log_alpha)
             self._gain_key = key
         return self._gain_val
@@ -197,11 +200,14 @@ class KanFet_MLP_NODE(nn.Module):
         self.dropout = nn.Dropout(dropout)
         self.cls_feat = KANFeatureMixer(latent_dim, num_basis, act=nn.Sigmoid())
         self.cls = nn.Linear(latent_dim * num_basis, num_classes)
+        self._t_eval = torch.linspace(0.0, 1.0, 9, dtype=torch.float64)
 
     def forward(self, x):
         from .odeint import odeint
         h0 = self.encoder(x)
-        t_eval = torch.linspace(0.0, 1.0, 9, device=x.device, dtype=torch.float64)
+        # the grid stays on the host (the reference builds it on x.device, :1031): odeint only reads its values, and a
+        # device tensor would cost a kernel plus a synchronising read-back per forward
+        t_eval = self._t_eval
         h_traj = odeint(self.odefunc, h0, t_eval, method=self.ode_method, rtol=self.rtol, atol=self.atol)
         hT = self.dropout(h_traj[-1])
         return self.cls(self.cls_feat(hT))

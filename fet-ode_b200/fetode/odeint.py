@@ -144,6 +144,22 @@ class _TimeTable:
         return self.dev[i]
 
 
+_TT_CACHE: dict = {}
+
+
+def _time_table(steps, dtype, device) -> _TimeTable:
+    """Training loops solve over the same grid every step: keep the table (its pinned source and the device copy)
+    so that a repeat solve costs no copy at all, and so that a solve captured in a CUDA graph never refers to a
+    pinned buffer that has been recycled."""
+    key = (tuple(steps), dtype, str(device))
+    tt = _TT_CACHE.get(key)
+    if tt is None:
+        if len(_TT_CACHE) >= 64:
+            _TT_CACHE.pop(next(iter(_TT_CACHE)))
+        tt = _TT_CACHE[key] = _TimeTable(steps, dtype, device)
+    return tt
+
+
 def _time_dtype(t: torch.Tensor):
     return t.dtype if t.is_floating_point() else torch.float32
 
@@ -259,7 +275,7 @@ def _staged_fixed(func, y0, t, times, kind, options):
     sol = [y]
     step_size = options.get("step_size")
     if step_size is None:
-        tt = _TimeTable([(a, b - a) for a, b in zip(times, times[1:])], _time_dtype(t), y0.device)
+        tt = _time_table([(a, b - a) for a, b in zip(times, times[1:])], _time_dtype(t), y0.device)
         for a, b in zip(times, times[1:]):
             y = _step_staged(kind, func, a, b - a, y, tt)
             sol.append(y)
@@ -270,7 +286,7 @@ def _staged_fixed(func, y0, t, times, kind, options):
         n = int(math.ceil((t1 - t0) / step_size + 1))
         grid = [t0 + k * step_size for k in range(n)]
         grid[-1] = t1
-        tt = _TimeTable([(a, b - a) for a, b in zip(grid, grid[1:])], _time_dtype(t), y0.device)
+        tt = _time_table([(a, b - a) for a, b in zip(grid, grid[1:])], _time_dtype(t), y0.device)
         j = 1
         for a, b in zip(grid, grid[1:]):
             y1 = _step_staged(kind, func, a, b - a, y, tt)
@@ -309,7 +325,7 @@ def _integrate(kind, odefunc, h0, t0, t1, n_steps):
         from .training import fused_fixed_autograd
         return fused_fixed_autograd(model, h0, times, kind, uniform_dt=dt)[-1]
     h = ops.f32c(h0)
-    tt = _TimeTable([(t0 + i * dt, dt) for i in range(n_steps)], h0.dtype, h0.device)
+    tt = _time_table([(t0 + i * dt, dt) for i in range(n_steps)], h0.dtype, h0.device)
     for i in range(n_steps):
         h = _step_staged(kind, odefunc, t0 + i * dt, dt, h, tt)
     return h
@@ -335,7 +351,7 @@ def odeint_rk4(func, z0, t, n_substeps=4):
     times = [float(v) for v in t.detach().cpu().double().tolist()]
     z = ops.f32c(z0)
     out = [z]
-    tt = _TimeTable([(a + s * ((b - a) / float(n_substeps)), (b - a) / float(n_substeps))
+    tt = _time_table([(a + s * ((b - a) / float(n_substeps)), (b - a) / float(n_substeps))
                      for a, b in zip(times, times[1:]) for s in range(n_substeps)], z0.dtype, z0.device)
     for a, b in zip(times, times[1:]):
         h = (b - a) / float(n_substeps)

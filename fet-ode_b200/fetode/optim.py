@@ -28,7 +28,7 @@ class FlatAdam:
     (e.g. the unused ``coef`` of the hard-gated LogisticBasis, train_ecg_kan_fet_nn_ode.py:91), and neither does this."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, decoupled: bool = False):
+                 weight_decay: float = 0.0, decoupled: bool = False, capturable: bool = False):
         self.all_params = [p for p in params if p.requires_grad]
         if not self.all_params:
             raise ValueError("FlatAdam: no parameters to optimise")
@@ -42,6 +42,9 @@ class FlatAdam:
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.weight_decay, self.decoupled = float(weight_decay), bool(decoupled)
         self.step_count = 0
+        # capturable: the step counter and bias corrections live on the device (fetode_adam_flat_graph), so a captured
+        # step() replays correctly in a CUDA graph (fetode.graphs.GraphedTrainStep); lr / betas are baked in at capture
+        self.capturable = bool(capturable)
         self.params = None                 # active parameters, once built
         self.flat_param = self.flat_grad = self.exp_avg = self.exp_avg_sq = None
         self._max_norm: Optional[float] = None
@@ -66,6 +69,9 @@ class FlatAdam:
         self.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
         self._sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
+        self._dev_state = torch.zeros(2, dtype=torch.int64, device=dev)      # {step; (step_size, bc2_sqrt) as 2 x f32}
+        if self.capturable and self.step_count:
+            self._dev_state[0] = self.step_count
         with torch.no_grad():
             for p, o in zip(self.params, self._offsets):
                 pv = self.flat_param[o:o + p.numel()].view(p.shape)
@@ -126,6 +132,17 @@ class FlatAdam:
             self._sync_grads()
         self.step_count += 1
         clip = self._max_norm is not None
+        if self.capturable:
+            check(lib().fetode_adam_flat_graph(
+                ptr(self.flat_param), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq), C.c_int64(self.n),
+                C.c_float(self.lr), C.c_float(self.betas[0]), C.c_float(self.betas[1]), C.c_float(self.eps),
+                C.c_float(self.weight_decay), C.c_int(1 if self.decoupled else 0),
+                C.c_void_p(self._dev_state.data_ptr()), C.c_float(self._max_norm if clip else 0.0),
+                C.c_void_p(self._sumsq.data_ptr() if clip else 0), stream()), "adam_flat_graph")
+            self._max_norm = None
+            for p in self.params:
+                torch.autograd.graph.increment_version(p)
+            return
         check(lib().fetode_adam_flat(ptr(self.flat_param), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),
                                      C.c_int64(self.n), C.c_float(self.lr), C.c_float(self.betas[0]),
                                      C.c_float(self.betas[1]), C.c_float(self.eps), C.c_float(self.weight_decay),
@@ -139,11 +156,11 @@ class FlatAdam:
             torch.autograd.graph.increment_version(p)
 
 
-def Adam(params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0) -> FlatAdam:
+def Adam(params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, capturable=False) -> FlatAdam:
     """torch.optim.Adam semantics (weight_decay is an L2 term added to the gradient)."""
-    return FlatAdam(params, lr, betas, eps, weight_decay, decoupled=False)
+    return FlatAdam(params, lr, betas, eps, weight_decay, decoupled=False, capturable=capturable)
 
 
-def AdamW(params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2) -> FlatAdam:
+def AdamW(params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, capturable=False) -> FlatAdam:
     """torch.optim.AdamW semantics (decoupled weight decay)."""
-    return FlatAdam(params, lr, betas, eps, weight_decay, decoupled=True)
+    return FlatAdam(params, lr, betas, eps, weight_decay, decoupled=True, capturable=capturable)

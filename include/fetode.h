@@ -242,6 +242,12 @@ FETODE_API int fetode_sumsq_f32(const float* g, int64_t n, double* sumsq, void* 
 FETODE_API int fetode_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                      float eps, float weight_decay, int decoupled, int64_t step, float max_norm,
                      const double* sumsq /* device, or NULL */, void* stream);
+/* Same update with the step counter kept on the device, so that the launch can be captured in a CUDA graph and
+ * replayed: state = 16 bytes {int64 step (incremented by this call); float lr / (1 - beta1^step); float
+ * sqrt(1 - beta2^step)}, zero-initialised by the caller.  lr and the betas are baked into the captured launch. */
+FETODE_API int fetode_adam_flat_graph(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                           float beta2, float eps, float weight_decay, int decoupled, int64_t* state /* device */,
+                           float max_norm, const double* sumsq /* device, or NULL */, void* stream);
 
 /* ---- probes used by bench.py for the roofline denominators --------------------------- */
 /* runs an FFMA-only kernel and returns achieved TFLOP/s in *tflops (host) */
