@@ -9,8 +9,10 @@ NCCL all-reduce of the parameter gradients per optimiser step (fetode.dist.allre
 One JSON line per configuration (rank 0): device-timed step (CUDA events, max over ranks), samples/s over all ranks.
 `python bench.py` stays the driver's contract; this script is the scaling evidence for the training path.
 """
+import gc
 import json
 import os
+import signal
 import sys
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -21,6 +23,7 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 import torch.nn.functional as F  # noqa: E402
 
+import fetode  # noqa: E402
 from fetode import dist as fdist, ecg, mnist_kuramoto_kan as MK  # noqa: E402
 
 
@@ -69,9 +72,15 @@ def main():
         fdist.allreduce_gradients(model)
         opt.step()
     ms = timed(mnist_step, world, dev)
+    # the same step (all-reduce included) captured into one CUDA graph per rank and replayed
+    gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, allreduce=world > 1, warmup=2)
+    gms = timed(lambda: gstep(gstep.x, gstep.y), world, dev)
     lines.append({"config": "5: MNIST KuramotoKANClassifier(steps=10, nb=8), CE, AdamW", "n_gpus": world,
                   "rows_per_gpu": B, "ms_per_step": ms, "images_per_s": B * world / ms * 1e3,
+                  "graph_ms_per_step": gms, "graph_images_per_s": B * world / gms * 1e3,
                   "allreduce_floats": sum(p.numel() for p in model.parameters())})
+    del gstep, gopt
 
     # ---- config 3: ECG KanFet_MLP_NODE, classic RK4 x 8, 4096 series per GPU
     torch.manual_seed(0)
@@ -91,15 +100,25 @@ def main():
         fdist.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
     ms = timed(ecg_step, world, dev, iters=3, warm=2)
+    gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, max_norm=1.0, allreduce=world > 1, warmup=2)
+    gms = timed(lambda: gstep(gstep.x, gstep.y), world, dev, iters=5, warm=2)
     lines.append({"config": "3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, AdamW, clip 1.0",
                   "n_gpus": world, "rows_per_gpu": B, "ms_per_step": ms, "sample_steps_per_s": B * 8 * world / ms * 1e3,
+                  "graph_ms_per_step": gms, "graph_sample_steps_per_s": B * 8 * world / gms * 1e3,
                   "allreduce_floats": sum(p.numel() for p in model.parameters())})
     if rank == 0:
         sys.stdout.flush()
         os.dup2(saved, 1)
         for ln in lines:
             print(json.dumps(ln), flush=True)
+    # graphs that captured NCCL kernels must be gone before the communicator is torn down
+    del gstep, gopt
+    gc.collect()
+    torch.cuda.synchronize()
     if world > 1:
+        signal.signal(signal.SIGALRM, lambda *_: os._exit(0))     # results are printed: never hang in teardown
+        signal.alarm(30)
         dist.barrier()
         dist.destroy_process_group()
 
