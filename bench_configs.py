@@ -85,6 +85,15 @@ def lv_train(B, skip_cpu):
         ((pred - tgt) ** 2).mean().backward()
         fopt.step()
     out["gpu_fwd_bwd_flatadam_ms"] = gpu_ms(fstep)
+    # the same iteration captured into a CUDA graph and replayed (fetode/graphs.py)
+
+    def gfwd(m, x):
+        m.reset_state()
+        return fetode.odeint(lambda tt, X: m(X), x, t, method="rk4_classic")
+    gopt = fetode.optim.Adam(model.parameters(), lr=2e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, lambda pred, y: ((pred - y) ** 2).mean(), x0d, tgt, warmup=2,
+                                           forward=gfwd)
+    out["gpu_fwd_bwd_graph_ms"] = gpu_ms(lambda: gstep(gstep.x, gstep.y))
     out["gpu_traj_steps_per_s"] = B * n / out["gpu_fwd_bwd_opt_ms"] * 1e3
     if not skip_cpu:
         Bc = min(B, 2048)

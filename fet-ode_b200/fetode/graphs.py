@@ -40,15 +40,19 @@ class GraphedTrainStep:
 
     ``opt`` must be a ``fetode.optim`` optimiser built with ``capturable=True``.  ``x`` / ``y`` fix the shapes; later
     calls copy their arguments into the captured input buffers.  The returned loss is a device tensor that the next
-    call overwrites.  ``allreduce=True`` puts fetode.dist's flat-gradient all-reduce inside the graph (NCCL)."""
+    call overwrites.  ``forward(model, x)`` replaces ``model(x)`` when the step is not a plain module call (e.g. the
+    Lotka-Volterra loop: ``reset_state()`` followed by ``odeint`` over the model, train_kanfet_node_predprey.py:250-257;
+    keep the time grid on the host).  The warm-up iterations are real optimiser steps on (x, y).  ``allreduce=True`` puts fetode.dist's flat-gradient all-reduce inside the graph (NCCL)."""
 
     def __init__(self, model: torch.nn.Module, opt: FlatAdam, loss_fn: Callable, x: torch.Tensor, y: torch.Tensor,
-                 max_norm: Optional[float] = None, allreduce: bool = False, warmup: int = 3):
+                 max_norm: Optional[float] = None, allreduce: bool = False, warmup: int = 3,
+                 forward: Optional[Callable] = None):
         if not isinstance(opt, FlatAdam) or not opt.capturable:
             raise ValueError("GraphedTrainStep needs a fetode.optim optimiser built with capturable=True")
         if not x.is_cuda:
             raise RuntimeError("GraphedTrainStep: inputs must live on a CUDA device (there is no CPU path)")
         self.model, self.opt, self.loss_fn = model, opt, loss_fn
+        self.forward = forward if forward is not None else (lambda m, inp: m(inp))
         self.max_norm, self.allreduce = max_norm, bool(allreduce)
         self.x, self.y = x.clone(), y.clone()
         side = torch.cuda.Stream()
@@ -77,7 +81,7 @@ class GraphedTrainStep:
 
     def _body(self) -> torch.Tensor:
         self.opt.zero_grad()
-        loss = self.loss_fn(self.model(self.x), self.y)
+        loss = self.loss_fn(self.forward(self.model, self.x), self.y)
         loss.backward()
         if self.allreduce:
             fdist.allreduce_gradients(self.opt)

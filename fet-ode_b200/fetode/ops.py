@@ -284,8 +284,8 @@ class SmallNetPlan:
                 self.packed = torch.empty(n, dtype=torch.float32, device=dev)
             check(lib().fetode_smallnet_pack(C.byref(self.net), structs, ptr(self.packed), stream()),
                   "smallnet_pack")
-            self._structs = structs                      # keeps the f32c() temporaries alive until the
-            torch.cuda.current_stream().synchronize()    # pack kernel has consumed them
+            # no host synchronisation: f32c() temporaries were allocated on this stream, and the caching allocator
+            # reuses their blocks only for work queued after the pack kernel on the same stream
             self._key = k
         return self.packed
 

@@ -105,7 +105,8 @@ class FusedRKFn(torch.autograd.Function):
                 else:
                     setattr(grads[li], name, ptr(gt).value)
         check(L.fetode_smallnet_unfold(C.byref(plan.net), structs, ptr(gfold), grads, stream()), "smallnet_unfold")
-        torch.cuda.current_stream().synchronize()        # the f32c() temporaries behind `structs` die with this frame
+        # no host synchronisation: any f32c() temporary behind `structs` was allocated on this stream, and the caching
+        # allocator only hands its block to work queued later on the same stream (this also keeps the step capturable)
         return (None, None, None, None, gy0 if ctx.needs_input_grad[4] else None, *outs)
 
 

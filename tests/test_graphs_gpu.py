@@ -78,6 +78,41 @@ def test_graphed_mnist_step_matches_eager(cuda):
         assert max_rel(q.detach(), p.detach()) < 5e-4, k
 
 
+def test_graphed_lv_training_matches_eager(cuda):
+    """train_kanfet_node_predprey.py:246-262 loop body (reset_state, fused RK4 solve, MSE, Adam) replayed from a graph."""
+    torch.manual_seed(0)
+    m1 = fetode.KANFET([2, 10, 2], grid_size=5)
+    m2 = copy.deepcopy(m1)
+    m1, m2 = m1.to(cuda), m2.to(cuda)
+    n = 34
+    t = torch.linspace(0, 3.5, n + 1, dtype=torch.float64)                # host grid: no read-back inside the capture
+    gen = torch.Generator().manual_seed(1)
+    x0 = (torch.rand(16, 2, generator=gen) * 3.0 + 0.5).to(cuda)
+    tgt = torch.randn(n + 1, 16, 2, generator=gen).to(cuda)
+
+    def fwd(m, x):
+        m.reset_state()
+        return fetode.odeint(lambda tt, X: m(X), x, t, method="rk4_classic")
+
+    def mse(pred, y):
+        return ((pred - y) ** 2).mean()
+    o1 = fetode.optim.Adam(m1.parameters(), lr=2e-3)
+    l1 = []
+    for _ in range(6):
+        o1.zero_grad()
+        loss = mse(fwd(m1, x0), tgt)
+        loss.backward()
+        o1.step()
+        l1.append(float(loss.detach()))
+    o2 = fetode.optim.Adam(m2.parameters(), lr=2e-3, capturable=True)
+    step = fetode.graphs.GraphedTrainStep(m2, o2, mse, x0, tgt, warmup=3, forward=fwd)
+    l2 = [float(step(x0, tgt)) for _ in range(3)]
+    for a, b in zip(l1[3:], l2):
+        assert abs(a - b) < 1e-5 * max(1.0, abs(a))
+    for (k, p), q in zip(m1.named_parameters(), m2.parameters()):
+        assert max_rel(q.detach(), p.detach()) < 1e-4, k
+
+
 def test_graphed_step_needs_capturable_optimiser(cuda):
     m = MK.KuramotoKANClassifier(kuramoto_steps=2, num_basis=8).to(cuda)
     opt = fetode.optim.AdamW(m.parameters(), lr=1e-3)
