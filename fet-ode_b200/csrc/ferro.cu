@@ -181,7 +181,12 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
 // is taken in double and rounded once), s = fl32(1 + e), r = fl32(1 / s), r > 0.5.  Net effect: true iff
 // e <= 1 - 2^-23, i.e. z > ~8.94e-8; false at z == 0.  One evaluation per (row, input) -- dx does not depend on the
 // basis index -- so the double-precision exp is off the critical path.
+// Away from the threshold the outcome is decided without the exponential: z >= 1e-6 gives exp(-z) <= 1 - 1e-6 + 5e-13,
+// far below 1 - 2^-23 (true); z <= 0 gives e >= 1, s >= 2, r <= 0.5 (false); NaN compares false both ways, as
+// NaN > 0.5 does.  Only 0 < z < 1e-6 (x within 2e-7 of prev) takes the double-precision path.
 __device__ __forceinline__ bool hard_gate(float z) {
+    if (z >= 1e-6f) return true;
+    if (!(z > 0.f)) return false;
     const float e = (float)exp(-(double)z);
     const float s = __fadd_rn(1.0f, e);
     return __fdiv_rn(1.0f, s) > 0.5f;
@@ -220,25 +225,39 @@ __global__ void __launch_bounds__(256) ferro_elem_fwd_kernel(const FerroArgs a) 
     }
 }
 
-// one thread per parameter (i,j), loop over a tile of rows; gx via atomics (K-way contention)
-constexpr int FE_BT = 128;
+// one thread per parameter (i,j), loop over a tile of rows; the K basis contributions to gx[b,i] sit in adjacent lanes
+// and are summed with a segmented shuffle scan, so each warp issues one atomic per (row, input) it touches
+constexpr int FE_BT = 32;
 
 template <int VARIANT>
 __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) {
     const int IK = a.I * a.K;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= IK) return;
-    const int i = p / a.K;
-    const long long b0 = (long long)blockIdx.y * FE_BT;
-    const int nb = (int)min((long long)FE_BT, a.B - b0);
+    const int p_raw = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = p_raw < IK;                           // dead lanes stay for the shuffles, contribute nothing
+    const int p = live ? p_raw : IK - 1;
+    const int i = live ? p / a.K : -1;
+    const int il = live ? i : 0;
+    const int lane = threadIdx.x & 31;
+    // segment structure of this warp (lanes with equal i are contiguous): fixed for the whole row loop
+    const int i_prev = __shfl_up_sync(0xffffffffu, i, 1);
+    const bool head = lane == 0 || i_prev != i;
+    bool same[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+        const int other = __shfl_down_sync(0xffffffffu, i, 1 << q);
+        same[q] = lane + (1 << q) < 32 && other == i;
+    }
     const float k = a.k[p], Ec = a.Ec[p];
     const float Ps = VARIANT == FETODE_FERRO_LOGISTIC ? 0.f : a.Ps[p], bias = VARIANT == FETODE_FERRO_LOGISTIC ? 0.f : a.bias[p];
     const float coef = VARIANT == FETODE_FERRO_TWO_D ? a.coef[p] : 1.0f;
     float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f;
+    for (long long b0 = (long long)blockIdx.y * FE_BT; b0 < a.B; b0 += (long long)gridDim.y * FE_BT) {
+    const int nb = (int)min((long long)FE_BT, a.B - b0);
+#pragma unroll 4
     for (int t = 0; t < nb; ++t) {
         const long long b = b0 + t;
-        const float x = a.x[b * a.I + i];
-        float go = a.gout[b * IK + p];
+        const float x = a.x[b * a.I + il];
+        float go = live ? a.gout[b * IK + p] : 0.f;
         float dx;
         if constexpr (VARIANT == FETODE_FERRO_LOGISTIC) {
             const float s = sigm(k * (x - Ec));
@@ -247,7 +266,7 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
             aEc = fmaf(-dz, k, aEc);
             dx = dz * k;
         } else if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
-            const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
+            const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + il];
             const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), k, Ec, 1.0f, a.g, a.alpha);
             float dm_dx, dm_dEc;
             soft_branch_grad(s, 1.0f, a.g, a.alpha, dm_dx, dm_dEc);
@@ -260,7 +279,7 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
             aEc = fmaf(dz * k, fmaf(Ec, dm_dEc, s.m), aEc);
             dx = dz * k * fmaf(Ec, dm_dx, 1.0f);
         } else {
-            const float pv = a.prev_is_zero ? 0.f : a.prev[i];
+            const float pv = a.prev_is_zero ? 0.f : a.prev[il];
             const bool up = hard_gate(a.g * (x - pv));
             const float arg = up ? x - Ec : x + Ec;
             const float s = sigm(k * arg);
@@ -276,8 +295,19 @@ __global__ void __launch_bounds__(128) ferro_elem_bwd_kernel(const FerroArgs a) 
             aEc += up ? -dz * k : dz * k;
             dx = dz * k;
         }
-        if (a.gx) atomicAdd(a.gx + b * a.I + i, dx);
+        if (a.gx) {
+            // segmented inclusive scan from the right: after log2 steps the head lane of every run of equal i holds
+            // the run's sum (runs are <= K long; K > 32 simply spans several warps' heads)
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+                const float w = __shfl_down_sync(0xffffffffu, dx, 1 << q);
+                if (same[q]) dx += w;
+            }
+            if (head && live) atomicAdd(a.gx + b * a.I + i, dx);
+        }
     }
+    }
+    if (!live) return;
     if (a.gk) atomicAdd(a.gk + p, ak);
     if (a.gEc) atomicAdd(a.gEc + p, aEc);
     if (VARIANT != FETODE_FERRO_LOGISTIC && a.gPs) atomicAdd(a.gPs + p, aPs);
@@ -376,8 +406,7 @@ extern "C" int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const f
         if (br) ferro_full_bwd_kernel<true><<<grid, FF_THREADS, 0, st>>>(a);
         else ferro_full_bwd_kernel<false><<<grid, FF_THREADS, 0, st>>>(a);
     } else {
-        const long long by = (B + FE_BT - 1) / FE_BT;
-        FETODE_CHECK_SUPPORTED(by <= 65535);
+        const long long by = std::min<long long>((B + FE_BT - 1) / FE_BT, 65535);
         const dim3 grid((unsigned)((a.I * a.K + 127) / 128), (unsigned)by);
         if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_bwd_kernel<FETODE_FERRO_TWO_D><<<grid, 128, 0, st>>>(a);
         else if (F->variant == FETODE_FERRO_LOGISTIC) ferro_elem_bwd_kernel<FETODE_FERRO_LOGISTIC><<<grid, 128, 0, st>>>(a);
