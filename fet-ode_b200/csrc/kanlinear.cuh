@@ -109,7 +109,7 @@ __device__ __forceinline__ void kl_features(float x, float prev, float gl, const
 int kl_check(const fetode_kanlayer_t* P);
 int kl_tc_pack(const KLLayout& L, float* blob, cudaStream_t st);
 int kl_tc_dw(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
-             int prev_is_zero, const float* gy, float* ws, long long B, cudaStream_t st);
+             int prev_is_zero, const float* gy, float* ws, long long B, int accumulate, cudaStream_t st);
 int kl_tc_dx(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
              int prev_is_zero, const float* gy, float* gx, float* gbp0, float* gbp1, long long B, cudaStream_t st);
 int kl_td_pack(const KLLayout& L, float* blob, cudaStream_t st);

@@ -31,6 +31,7 @@ struct KLBwdArgs {
     KLLayout L;
     float gl;
     int prev_is_zero, KI, split;
+    int accumulate;      // 1: ws already holds a partial folded gradient (deferred unfold): add to it, do not unfold
 };
 
 // ------------------------------------------------------------------------------------------
@@ -106,7 +107,7 @@ __global__ void __launch_bounds__(KB_THREADS) kl_bwd_dw_kernel(const KLBwdArgs a
         for (int c = 0; c < 4; ++c) {
             const int n = n0 + tx * 4 + c;
             if (n < O) {
-                if (gridDim.z == 1) dst[n] = acc[q][c];
+                if (gridDim.z == 1 && !a.accumulate) dst[n] = acc[q][c];
                 else atomicAdd(dst + n, acc[q][c]);
             }
         }
@@ -398,11 +399,13 @@ static int kl_bwd_launch(KLBwdArgs& a, cudaStream_t st) {
         auto k = kl_bwd_dw_kernel<BR>;
         e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e) return (int)e;
-        e = cudaMemsetAsync(a.ws, 0, ((size_t)L.I * L.F * L.O + L.O) * 4, st);
-        if (e) return (int)e;
+        if (!a.accumulate) {
+            e = cudaMemsetAsync(a.ws, 0, ((size_t)L.I * L.F * L.O + L.O) * 4, st);
+            if (e) return (int)e;
+        }
         int rc_tc = FETODE_EUNSUPPORTED;
         if (a.L.tc_ok && a.B >= kl_tc_min_rows())               // wide layer: tcgen05 weight gradient (kanlinear_tc_bwd.cu)
-            rc_tc = kl_tc_dw(&a.P, a.L, a.blob, a.x, a.prev, a.prev_is_zero, a.gy, a.ws, a.B, st);
+            rc_tc = kl_tc_dw(&a.P, a.L, a.blob, a.x, a.prev, a.prev_is_zero, a.gy, a.ws, a.B, a.accumulate, st);
         if (rc_tc != FETODE_OK && rc_tc != FETODE_EUNSUPPORTED) return rc_tc;
         if (rc_tc == FETODE_EUNSUPPORTED)
             k<<<dim3(ngroups, gy_, (unsigned)split), KB_THREADS, smem, st>>>(a);
@@ -427,8 +430,8 @@ static int kl_bwd_launch(KLBwdArgs& a, cudaStream_t st) {
             k<<<dim3((unsigned)ntile, (unsigned)gy_), KB_THREADS, smem, st>>>(a);
         }
     }
-    // 3. unfold
-    kl_unfold_run(a, st);
+    // 3. unfold (deferred by the caller when the same layer is applied many times per step)
+    if (!a.accumulate) kl_unfold_run(a, st);
     return FETODE_LAUNCH_RC();
 }
 
@@ -481,4 +484,39 @@ extern "C" int fetode_kanlinear_bwd(const fetode_kanlayer_t* P, const float* wca
         case FETODE_BRANCH_FERRO2D: return kl_bwd_launch<FETODE_BRANCH_FERRO2D>(a, st);
     }
     return FETODE_EUNSUPPORTED;
+}
+
+// Deferred-unfold pair: a layer applied many times per optimiser step (every Runge-Kutta stage) accumulates its folded
+// gradient over all the calls and is unfolded to the reference's parameters once.
+extern "C" int fetode_kanlinear_bwd_acc(const fetode_kanlayer_t* P, const float* wcat, const float* x,
+                                        const float* prev, int prev_is_zero, const float* gy, float* gx,
+                                        float* gbp0, float* gbp1, float* ws_acc, int64_t B, void* stream) {
+    int rc = kl_check(P);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(wcat && x && gy && ws_acc && B >= 0);
+    if (B == 0) return FETODE_OK;
+    if (P->branch == FETODE_BRANCH_FERRO2D && !prev_is_zero) FETODE_CHECK_ARG(prev != nullptr);
+    KLBwdArgs a{};
+    a.P = *P;
+    a.g.bp[0] = gbp0; a.g.bp[1] = gbp1;
+    a.blob = wcat; a.x = x; a.prev = prev; a.gy = gy; a.gx = gx; a.ws = ws_acc; a.B = B;
+    a.L = kl_layout(P->in_features, P->out_features, P->grid_size, P->num_basis);
+    FETODE_CHECK_SUPPORTED(a.L.F <= KB_KCMAX);
+    a.KI = std::max(1, std::min(4, KB_KCMAX / a.L.F));
+    a.gl = P->gate_slope * FETODE_LOG2E;
+    a.prev_is_zero = prev_is_zero;
+    a.accumulate = 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (P->branch) {
+        case FETODE_BRANCH_NONE: return kl_bwd_launch<FETODE_BRANCH_NONE>(a, st);
+        case FETODE_BRANCH_LOGISTIC: return kl_bwd_launch<FETODE_BRANCH_LOGISTIC>(a, st);
+        case FETODE_BRANCH_FERRO2D: return kl_bwd_launch<FETODE_BRANCH_FERRO2D>(a, st);
+    }
+    return FETODE_EUNSUPPORTED;
+}
+
+extern "C" int fetode_kanlinear_unfold(const fetode_kanlayer_t* P, float* ws_acc, const fetode_kanlayer_grads_t* grads,
+                                       void* stream) {
+    FETODE_CHECK_ARG(ws_acc && grads);
+    return kl_unfold_launch(P, grads, ws_acc, (cudaStream_t)stream);
 }

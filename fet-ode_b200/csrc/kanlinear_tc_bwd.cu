@@ -37,7 +37,7 @@ struct DWArgs {
     long long B;
     KLLayout L;
     float gl;
-    int prev_is_zero, chunks_per_split;
+    int prev_is_zero, chunks_per_split, accumulate;
 };
 
 // shared with the forward kernel (kanlinear_tc.cu)
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(DWShape<NB>::THREADS, 1) kl_tc_dw_kernel(const
                     const int i = i0 + 2 * g + ii;
                     if (i >= I) continue;
                     float* dstp = a.ws + ((size_t)i * F + f) * O + o;
-                    if (gridDim.z == 1) *dstp = acc[e]; else atomicAdd(dstp, acc[e]);
+                    if (gridDim.z == 1 && !a.accumulate) *dstp = acc[e]; else atomicAdd(dstp, acc[e]);
                 }
             }
         }
@@ -311,11 +311,11 @@ static int dw_launch_k(const DWArgs& a, dim3 grid, cudaStream_t st) {
 // gW = A^T gy on the tensor cores; ws must be zeroed by the caller (row splits accumulate with atomics).
 // Returns FETODE_EUNSUPPORTED when the caller should use the CUDA-core kernel.
 int kl_tc_dw(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, const float* x, const float* prev,
-             int prev_is_zero, const float* gy, float* ws, long long B, cudaStream_t st) {
+             int prev_is_zero, const float* gy, float* ws, long long B, int accumulate, cudaStream_t st) {
     if (!L.tc_ok) return FETODE_EUNSUPPORTED;
     if (((uintptr_t)x & 15) || (prev && ((uintptr_t)prev & 15)) || ((uintptr_t)gy & 15)) return FETODE_EUNSUPPORTED;
     tcb::DWArgs a{};
-    a.blob = blob; a.x = x; a.prev = prev; a.gy = gy; a.ws = ws; a.B = B; a.L = L;
+    a.blob = blob; a.x = x; a.prev = prev; a.gy = gy; a.ws = ws; a.B = B; a.L = L; a.accumulate = accumulate;
     a.gl = P->gate_slope * FETODE_LOG2E;
     a.prev_is_zero = prev_is_zero;
     const long long nchunks = (B + tcb::RC - 1) / tcb::RC;

@@ -132,6 +132,8 @@ class LayerPack:
         self._key = None
         self.blob: Optional[torch.Tensor] = None
         self.struct: Optional[KanLayer] = None
+        self._handle: Optional[torch.Tensor] = None
+        self._handle_key = None
 
     def get(self, tensors=None) -> Tuple[KanLayer, torch.Tensor]:
         k = self.view.key(tensors)
@@ -149,6 +151,20 @@ class LayerPack:
             self.struct, self._key = s, k
         return self.struct, self.blob
 
+    def fold(self, tensors, params) -> torch.Tensor:
+        """The FoldFn handle of the current parameter versions: one autograd node per (layer, parameter version),
+        shared by every call until the parameters change."""
+        k = (self.view.key(tensors), tuple(p.requires_grad for p in params))
+        h = self._handle
+        if h is None or k != self._handle_key or h.grad_fn is None:
+            # drop the stale node (every reference, the local one too) BEFORE building the new one: while it lives it
+            # pins the parameters' AccumulateGrad nodes and the stream they were created on
+            h = self._handle = None
+            h = self._handle = FoldFn.apply(self, tensors, *params)
+            h._fetode_shared = h.grad_fn.shared
+            self._handle_key = k
+        return h
+
 
 def kanlinear_fwd(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor], tensors=None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """y = KANLinear(x2d); returns (y, new_prev) where new_prev (FERRO2D only) is x2d itself."""
@@ -165,16 +181,74 @@ def kanlinear_fwd(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tenso
     return y, (x2d if ferro else None)
 
 
-class KanLinearFn(torch.autograd.Function):
-    """autograd node of one KANLinear call.  The hysteresis state ``prev`` is a constant of the
-    graph, as in the reference (ferro_class.py:553-554 detaches the snapshots)."""
+class FoldFn(torch.autograd.Function):
+    """The parameter fold as an autograd node: reference parameters -> packed image (``LayerPack.blob``), represented
+    in the graph by a data-less ``handle`` of the folded gradient's shape.  A layer that is applied many times between
+    two optimiser steps (once per Runge-Kutta stage: 32 times per ECG step) shares ONE fold node; every
+    ``KanLinearFn.backward`` adds its folded-weight gradient into one accumulator, and this node's backward applies the
+    chain rule to the reference's parameters (fetode_kanlinear_unfold) ONCE -- instead of an unfold plus a dozen
+    gradient-accumulation launches per call."""
 
     @staticmethod
-    def forward(ctx, pack: LayerPack, prev, tens, x2d, *params):
+    def forward(ctx, pack, tens, *params):
+        s, _ = pack.get(tens)
+        ctx.pack, ctx.tens = pack, tens
+        ctx.names = [n for n, t in tens if t is not None and n != "grid"]
+        ctx.shared = {"acc": None}
+        ctx.set_materialize_grads(False)
+        n = max(int(lib().fetode_kanlinear_bwd_ws_floats(C.byref(s))), 4) + 2 * _bp_floats(s)
+        return torch.empty(n, dtype=torch.float32, device=params[0].device)
+
+    @staticmethod
+    def backward(ctx, g_handle):
+        acc = ctx.shared["acc"]
+        n_out = 2 + len(ctx.names)
+        if g_handle is None or acc is None:
+            return (None,) * n_out
+        s, _ = ctx.pack.get(ctx.tens)
+        tens = dict(ctx.tens)
+        n_ws = acc.numel() - 2 * _bp_floats(s)
+        want = [ctx.needs_input_grad[2 + idx] for idx in range(len(ctx.names))]
+        direct = {"bp0": 0, "bp1": 1}                        # accumulated by the input-gradient kernel, not unfolded
+        sizes = [(tens[n].numel() + 3) // 4 * 4 if (w and n not in direct) else 0 for n, w in zip(ctx.names, want)]
+        flat = torch.zeros(max(sum(sizes), 1), dtype=torch.float32, device=acc.device)
+        g = KanLayerGrads()
+        outs, off = [], 0
+        for name, w, n in zip(ctx.names, want, sizes):
+            t = tens[name]
+            if not w:
+                outs.append(None)
+                continue
+            if name in direct:
+                o = n_ws + direct[name] * _bp_floats(s)
+                outs.append(acc[o:o + t.numel()].view(t.shape))
+                continue
+            gt = flat[off:off + t.numel()].view(t.shape)
+            off += n
+            outs.append(gt)
+            if name.startswith("bp"):
+                g.bp[int(name[2:])] = ptr(gt).value
+            else:
+                setattr(g, name, ptr(gt).value)
+        check(lib().fetode_kanlinear_unfold(C.byref(s), ptr(acc), C.byref(g), stream()), "kanlinear_unfold")
+        return (None, None, *outs)
+
+
+def _bp_floats(s: KanLayer) -> int:
+    return (int(s.in_features) * int(s.num_basis) + 3) // 4 * 4
+
+
+class KanLinearFn(torch.autograd.Function):
+    """autograd node of one KANLinear call: (x, fold handle) -> y.  The hysteresis state ``prev`` is a constant of the
+    graph, as in the reference (ferro_class.py:553-554 detaches the snapshots).  ``handle`` is FoldFn's output (None
+    when no parameter requires a gradient): the parameters' gradient flows through it."""
+
+    @staticmethod
+    def forward(ctx, pack: LayerPack, prev, tens, x2d, handle):
         y, _ = kanlinear_fwd(pack, x2d, prev, tens)
         ctx.pack, ctx.prev, ctx.tens = pack, prev, tens
+        ctx.shared = None if handle is None else handle._fetode_shared
         ctx.save_for_backward(x2d)
-        ctx.names = [n for n, t in tens if t is not None and n != "grid"]
         return y
 
     @staticmethod
@@ -187,39 +261,44 @@ class KanLinearFn(torch.autograd.Function):
         B = x2d.shape[0]
         need_x = ctx.needs_input_grad[3]
         gx = torch.empty_like(x2d) if need_x else None
-        g = KanLayerGrads()
-        outs = []
-        tens = dict(ctx.tens)
-        # one zero-filled flat buffer for every wanted parameter gradient (the kernels accumulate into it):
-        # a single fill launch instead of one per parameter
-        want = [ctx.needs_input_grad[4 + idx] for idx in range(len(ctx.names))]
-        sizes = [(tens[n].numel() + 3) // 4 * 4 if w else 0 for n, w in zip(ctx.names, want)]
-        n_grad = sum(sizes)
-        n_ws = max(int(L.fetode_kanlinear_bwd_ws_floats(C.byref(s))), 1)
-        flat = torch.zeros(max(n_grad, 1), dtype=torch.float32, device=x2d.device)
-        ws = torch.empty(n_ws, dtype=torch.float32, device=x2d.device)
-        off = 0
-        for name, w, n in zip(ctx.names, want, sizes):
-            t = tens[name]
-            gt = flat[off:off + t.numel()].view(t.shape) if w else None
-            off += n
-            outs.append(gt)
-            if name.startswith("bp"):
-                g.bp[int(name[2:])] = ptr(gt).value
-            else:
-                setattr(g, name, ptr(gt).value)
         ferro = s.branch == BRANCH_FERRO2D
-        check(L.fetode_kanlinear_bwd(C.byref(s), ptr(blob), ptr(x2d), ptr(ctx.prev) if ferro else None,
-                                     C.c_int(1 if ctx.prev is None else 0), ptr(gy), ptr(gx), C.byref(g),
-                                     ptr(ws), C.c_int64(B), stream()), "kanlinear_bwd")
-        return (None, None, None, gx, *outs)
+        shared = ctx.shared if ctx.needs_input_grad[4] else None
+        if shared is None:                                   # frozen parameters: input gradient only
+            if not need_x:
+                return (None, None, None, None, None)
+            ws = torch.empty(max(int(L.fetode_kanlinear_bwd_ws_floats(C.byref(s))), 1), dtype=torch.float32,
+                             device=x2d.device)
+            check(L.fetode_kanlinear_bwd(C.byref(s), ptr(blob), ptr(x2d), ptr(ctx.prev) if ferro else None,
+                                         C.c_int(1 if ctx.prev is None else 0), ptr(gy), ptr(gx),
+                                         C.byref(KanLayerGrads()), ptr(ws), C.c_int64(B), stream()), "kanlinear_bwd")
+            return (None, None, None, gx, None)
+        first = shared["acc"] is None
+        if first:
+            n_ws = max(int(L.fetode_kanlinear_bwd_ws_floats(C.byref(s))), 4)
+            shared["acc"] = torch.zeros(n_ws + 2 * _bp_floats(s), dtype=torch.float32, device=x2d.device)
+            # whatever this backward pass reaches (a partial torch.autograd.grad never runs the fold node), the
+            # accumulator never survives the pass
+            torch.autograd.Variable._execution_engine.queue_callback(lambda: shared.__setitem__("acc", None))
+        acc = shared["acc"]
+        n_ws = acc.numel() - 2 * _bp_floats(s)
+        has_bp = s.branch != BRANCH_NONE
+        gbp0 = acc[n_ws:] if has_bp else None
+        gbp1 = acc[n_ws + _bp_floats(s):] if has_bp else None
+        check(L.fetode_kanlinear_bwd_acc(C.byref(s), ptr(blob), ptr(x2d), ptr(ctx.prev) if ferro else None,
+                                         C.c_int(1 if ctx.prev is None else 0), ptr(gy), ptr(gx), ptr(gbp0), ptr(gbp1),
+                                         ptr(acc), C.c_int64(B), stream()), "kanlinear_bwd_acc")
+        # the accumulator is handed to autograd once; the later calls add into it in place
+        return (None, None, None, gx, acc if first else None)
 
 
 def kanlinear_apply(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Tensor]) -> torch.Tensor:
     tens = pack.view.tensors()
-    params = [t for n, t in tens if t is not None and n != "grid"]
-    if torch.is_grad_enabled() and (x2d.requires_grad or any(p.requires_grad for p in params)):
-        return KanLinearFn.apply(pack, prev, tens, x2d, *params)
+    if torch.is_grad_enabled():
+        params = [t for n, t in tens if t is not None and n != "grid"]
+        if any(p.requires_grad for p in params):
+            return KanLinearFn.apply(pack, prev, tens, x2d, pack.fold(tens, params))
+        if x2d.requires_grad:
+            return KanLinearFn.apply(pack, prev, tens, x2d, None)
     return kanlinear_fwd(pack, x2d, prev, tens)[0]
 
 

@@ -106,6 +106,17 @@ FETODE_API int fetode_kanlinear_bwd(const fetode_kanlayer_t* L, const float* wca
                          float* gx /* [B,I] or NULL, overwritten */,
                          const fetode_kanlayer_grads_t* grads, float* ws,
                          int64_t B, void* stream);
+/* The same backward split in two for a layer that is applied many times per optimiser step (once per Runge-Kutta
+ * stage: 32 times per step in train_ecg_kan_fet_nn_ode.py's RK4 x 8 loop).  _bwd_acc ADDS this call's folded-weight
+ * gradient ([I*F, O] then the output-gradient column sums [O]) to ws_acc (fetode_kanlinear_bwd_ws_floats(L) floats,
+ * zeroed by the caller before the first call) and the branch-basis parameter gradients to gbp0 / gbp1 ([I, nb] each,
+ * or NULL); gx is overwritten.  _unfold then applies the chain rule from the accumulated folded gradient to the
+ * reference's parameters (every non-NULL member of grads except bp[0], bp[1] is added to) -- once per step. */
+FETODE_API int fetode_kanlinear_bwd_acc(const fetode_kanlayer_t* L, const float* wcat, const float* x,
+                         const float* prev, int prev_is_zero, const float* gy, float* gx /* [B,I] or NULL */,
+                         float* gbp0, float* gbp1, float* ws_acc, int64_t B, void* stream);
+FETODE_API int fetode_kanlinear_unfold(const fetode_kanlayer_t* L, float* ws_acc, const fetode_kanlayer_grads_t* grads,
+                         void* stream);
 
 /* B-spline basis values alone: KANLinear.b_splines efficientkan.py:117-131 (used by update_grid :184-221 and
  * curve2coeff :133-143 on CUDA inputs).  grid [I, G+2k+1], x [B,I] -> out [B, I, G+k]; spline_order must be 3. */

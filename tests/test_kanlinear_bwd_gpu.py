@@ -68,3 +68,46 @@ def test_gradient_at_full_ecg_size_is_linear_in_upstream(cuda):
     _, gb = grads(x[2048:], g[2048:], 1.0)
     for n in gp1:
         assert max_rel(ga[n] + gb[n], gp1[n]) < 1e-4, n
+
+
+def test_shared_fold_node_survives_partial_and_repeated_backward(cuda):
+    """One fold node serves every call of a layer between two parameter updates and the folded gradient is unfolded
+    once (ops.FoldFn).  A partial pass (autograd.grad w.r.t. the input only, which never reaches the fold node) must
+    leave nothing behind, and a second pass over fresh graphs must not see the first pass's accumulator."""
+    p, layer, gen = _make(48, 24, 10, "logistic", cuda, 5)
+    xs = [(torch.randn(64, 48, generator=gen) * 0.9).to(cuda) for _ in range(3)]
+    ws = [torch.randn(64, 24, generator=gen).to(cuda) for _ in range(3)]
+
+    def loss_of(inputs):
+        return sum((layer(x) * w).sum() for x, w in zip(inputs, ws))
+
+    layer.zero_grad()
+    loss_of(xs).backward()
+    ref = {n: t.grad.clone() for n, t in layer.named_parameters()}
+    # partial pass first: gradient w.r.t. the inputs only
+    xg = [x.clone().requires_grad_(True) for x in xs]
+    gx = torch.autograd.grad(loss_of(xg), xg)
+    layer.zero_grad()
+    xg2 = [x.clone().requires_grad_(True) for x in xs]
+    loss_of(xg2).backward()
+    for a, b in zip(gx, xg2):
+        assert max_rel(a, b.grad) < 1e-6
+    for n, t in layer.named_parameters():
+        assert max_rel(t.grad, ref[n]) < 1e-5, n
+    # per-call gradients add up to the shared-node gradient
+    tot = {n: torch.zeros_like(t) for n, t in layer.named_parameters()}
+    for x, w in zip(xs, ws):
+        layer.zero_grad()
+        (layer(x) * w).sum().backward()
+        for n, t in layer.named_parameters():
+            tot[n] += t.grad
+    for n in tot:
+        assert max_rel(tot[n], ref[n]) < 1e-5, n
+    # frozen parameters: only the input gradient is produced
+    for t in layer.parameters():
+        t.requires_grad_(False)
+    layer.zero_grad()
+    xf = xs[0].clone().requires_grad_(True)
+    (layer(xf) * ws[0]).sum().backward()
+    assert max_rel(xf.grad, xg2[0].grad) < 1e-6
+    assert all(t.grad is None for t in layer.parameters())
