@@ -252,7 +252,19 @@ __global__ void __launch_bounds__(TCShape<NB, BR>::THREADS, 1) kl_tc_fwd_kernel(
 #pragma unroll
                 for (int e = 0; e < 16; ++e) acc[e] += __uint_as_float(v[e]);
             }
-            if (live) {
+            if (live && gridDim.z > 1 && (O & 3) == 0) {
+                // split-K partial sums: 16-byte vector reductions (one L2 operation per four outputs)
+#pragma unroll
+                for (int e = 0; e < 16; e += 4) {
+                    const int n = n0 + c0 + e;
+                    if (n < O) {
+                        float v0 = acc[e], v1 = acc[e + 1], v2 = acc[e + 2], v3 = acc[e + 3];
+                        if (split == 0) { v0 += bias[n]; v1 += bias[n + 1]; v2 += bias[n + 2]; v3 += bias[n + 3]; }
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                                     ::"l"(a.y + b * O + n), "f"(v0), "f"(v1), "f"(v2), "f"(v3) : "memory");
+                    }
+                }
+            } else if (live) {
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
                     const int n = n0 + c0 + e;
@@ -400,7 +412,7 @@ int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, 
         if (e) return (int)e;
     }
     const size_t smem = (size_t)tc::NSTAGE * 2 * (tc::BM * tc::BK * 4 + (size_t)L.tc_BN * tc::BK * 4) + (size_t)2 * 32 * L.TAB * 4 + 1024 + 256;
-    if (((uintptr_t)x & 15) || (prev && ((uintptr_t)prev & 15))) return FETODE_EUNSUPPORTED;
+    if (((uintptr_t)x & 15) || (prev && ((uintptr_t)prev & 15)) || ((uintptr_t)y & 15)) return FETODE_EUNSUPPORTED;
     const dim3 grid((unsigned)mt, (unsigned)L.tc_ntile, (unsigned)splits);
     switch (P->branch) {
         case FETODE_BRANCH_NONE: return tc::tc_launch_k<0, FETODE_BRANCH_NONE>(a, grid, smem, st);
