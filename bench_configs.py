@@ -144,7 +144,16 @@ def ecg_train(B, skip_cpu):
     gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
     gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, max_norm=1.0, warmup=2)
     gl = gpu_ms(lambda: gstep(gstep.x, gstep.y), iters=5, warm=2)
-    return {"gpu_fwd_bwd_graph_ms": gl, "gpu_fwd_bwd_flatadamw_ms": fl, "config": f"3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, AdamW, clip 1.0, B={B}",
+    # the reference's own solver choice for this model: dopri5 (rtol 1e-3, atol 1e-4, :1034-1041) -- adaptive, one
+    # host read of the error norm per attempted step, so it runs eagerly
+    dp = {}
+    try:
+        model.ode_method = "dopri5"
+        dp["gpu_dopri5_fwd_bwd_opt_ms"] = gpu_ms(fstep, iters=3, warm=2)
+    except Exception as e:                                            # noqa: BLE001
+        dp["gpu_dopri5_error"] = repr(e)[:200]
+    model.ode_method = "rk4_classic"
+    return {**dp, "gpu_fwd_bwd_graph_ms": gl, "gpu_fwd_bwd_flatadamw_ms": fl, "config": f"3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, AdamW, clip 1.0, B={B}",
             "gpu_fwd_bwd_opt_ms": ms, "gpu_fwd_ms": fms, "sample_steps_per_s": B * 8 / ms * 1e3}
 
 

@@ -135,6 +135,15 @@ class LayerPack:
         self._handle: Optional[torch.Tensor] = None
         self._handle_key = None
 
+    def __deepcopy__(self, memo):
+        # copy.deepcopy(model) after a forward: the copy gets a fresh, empty pack bound to the copied module (the
+        # ctypes struct holds raw pointers and the fold handle is a non-leaf tensor: neither may be copied)
+        import copy
+        return LayerPack(copy.deepcopy(self.view.m, memo))
+
+    def __reduce__(self):
+        return (LayerPack, (self.view.m,))
+
     def get(self, tensors=None) -> Tuple[KanLayer, torch.Tensor]:
         k = self.view.key(tensors)
         if k != self._key:
@@ -324,6 +333,13 @@ class SmallNetPlan:
         self.D, self.H = widths[0], widths[1] if len(widths) > 1 else 0
         self._key = None
         self.packed: Optional[torch.Tensor] = None
+
+    def __deepcopy__(self, memo):
+        import copy
+        return SmallNetPlan([copy.deepcopy(v.m, memo) for v in self.views])
+
+    def __reduce__(self):
+        return (SmallNetPlan, ([v.m for v in self.views],))
 
     @staticmethod
     def supported(layers: Sequence) -> bool:

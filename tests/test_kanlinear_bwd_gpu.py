@@ -111,3 +111,27 @@ def test_shared_fold_node_survives_partial_and_repeated_backward(cuda):
     (layer(xf) * ws[0]).sum().backward()
     assert max_rel(xf.grad, xg2[0].grad) < 1e-6
     assert all(t.grad is None for t in layer.parameters())
+
+
+def test_deepcopy_after_training_step(cuda):
+    """copy.deepcopy(model) (best-model snapshots in the training scripts) must work after forwards / backwards have
+    populated the packed-image caches, and the copy must compute on its own parameters."""
+    import copy
+    p, layer, gen = _make(48, 24, 10, "logistic", cuda, 7)
+    x = (torch.randn(32, 48, generator=gen) * 0.9).to(cuda)
+    layer(x).sum().backward()
+    twin = copy.deepcopy(layer)
+    y0 = layer(x).detach()
+    assert torch.equal(twin(x).detach(), y0)
+    with torch.no_grad():
+        twin.base_weight.mul_(2.0)
+    assert not torch.equal(twin(x).detach(), y0)
+    assert torch.equal(layer(x).detach(), y0)
+    net = fetode.KANFET([2, 10, 2], grid_size=5).to(cuda)
+    z = torch.rand(8, 2, device=cuda) + 0.5
+    out = fetode.integrate_rk4(lambda t, h: net(h), z, 0.0, 0.1, 4)
+    net2 = copy.deepcopy(net)
+    net.reset_state(); net2.reset_state()
+    a = fetode.integrate_rk4(lambda t, h: net(h), z, 0.0, 0.1, 4)
+    b = fetode.integrate_rk4(lambda t, h: net2(h), z, 0.0, 0.1, 4)
+    assert torch.equal(a, b)
