@@ -1,0 +1,149 @@
+// linear.cu -- the small dense head of the ECG right-hand side in fp32 (sm_100a).
+//
+// Replaces  dh = self.out(z)  (nn.Linear(hidden, latent_dim), train_ecg_kan_fet_nn_ode.py:446, :475) and its
+// autograd.  The shapes are small ([4096,128] x [128,64]) and the reference computes them in fp32 (TF32 is off by
+// default), where the library's SIMT GEMM launches 64 CTAs and takes 21 us forward and 57 us backward per call --
+// 32 calls per training step.  One strided tile kernel serves all three products:
+//   forward   y[b,o]  = sum_k x[b,k] W[o,k] + bias[o]
+//   dX        gx[b,k] = sum_o gy[b,o] W[o,k]
+//   dW        gW[o,k] = sum_b gy[b,o] x[b,k]          (split over b, atomics into a zeroed buffer)
+//   dbias     gb[o]   = sum_b gy[b,o]
+// FP32 FMA pipe; 32 x 64 output tiles so that a [4096, 64] result still fills 128 CTAs.
+#include "common.cuh"
+
+namespace fetode {
+
+constexpr int LG_BM = 32, LG_BN = 64, LG_BK = 32, LG_THREADS = 256;
+
+struct GemmArgs {
+    const float* A; const float* B; const float* bias; float* C;
+    long long M, sAm, sAk, sBk, sBn;
+    int N, K, k_per_split;
+};
+
+// C[m,n] (+)= sum_k A[m*sAm + k*sAk] * B[k*sBk + n*sBn] (+ bias[n]);  C row-major [M, N]
+__global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a) {
+    __shared__ float As[LG_BK][LG_BM + 1];
+    __shared__ __align__(16) float Bs[LG_BK][LG_BN];
+    const int tid = threadIdx.x;
+    const long long m0 = (long long)blockIdx.x * LG_BM;
+    const int n0 = blockIdx.y * LG_BN;
+    const int k_begin = blockIdx.z * a.k_per_split, k_end = min(a.K, k_begin + a.k_per_split);
+    const int ty = tid / 16, tx = tid % 16;                 // thread -> rows 2 ty, 2 ty + 1 ; columns 4 tx .. 4 tx + 3
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    const bool a_k_fast = a.sAk == 1, b_n_fast = a.sBn == 1;
+    for (int k0 = k_begin; k0 < k_end; k0 += LG_BK) {
+        for (int q = tid; q < LG_BM * LG_BK; q += LG_THREADS) {
+            const int kk = a_k_fast ? q % LG_BK : q / LG_BM, mm = a_k_fast ? q / LG_BK : q % LG_BM;
+            const long long m = m0 + mm;
+            const int k = k0 + kk;
+            As[kk][mm] = (m < a.M && k < k_end) ? a.A[m * a.sAm + k * a.sAk] : 0.f;
+        }
+        for (int q = tid; q < LG_BK * LG_BN; q += LG_THREADS) {
+            const int nn = b_n_fast ? q % LG_BN : q / LG_BK, kk = b_n_fast ? q / LG_BN : q % LG_BK;
+            const int n = n0 + nn, k = k0 + kk;
+            Bs[kk][nn] = (n < a.N && k < k_end) ? a.B[k * a.sBk + n * a.sBn] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < LG_BK; ++kk) {
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][4 * tx]);
+            const float a0 = As[kk][2 * ty], a1 = As[kk][2 * ty + 1];
+            acc[0][0] = fmaf(a0, b.x, acc[0][0]); acc[0][1] = fmaf(a0, b.y, acc[0][1]);
+            acc[0][2] = fmaf(a0, b.z, acc[0][2]); acc[0][3] = fmaf(a0, b.w, acc[0][3]);
+            acc[1][0] = fmaf(a1, b.x, acc[1][0]); acc[1][1] = fmaf(a1, b.y, acc[1][1]);
+            acc[1][2] = fmaf(a1, b.z, acc[1][2]); acc[1][3] = fmaf(a1, b.w, acc[1][3]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const long long m = m0 + 2 * ty + i;
+        if (m >= a.M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + 4 * tx + j;
+            if (n >= a.N) continue;
+            float v = acc[i][j];
+            if (a.bias && blockIdx.z == 0) v += a.bias[n];
+            if (gridDim.z == 1) a.C[m * a.N + n] = v;
+            else atomicAdd(a.C + m * a.N + n, v);
+        }
+    }
+}
+
+// gb[o] += sum_b gy[b,o]
+__global__ void __launch_bounds__(256) colsum_acc_kernel(const float* gy, float* gb, long long B, int O) {
+    const int o = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int w = threadIdx.x >> 5;
+    float acc = 0.f;
+    if (o < O)
+        for (long long b = (long long)blockIdx.y * 8 + w; b < B; b += (long long)gridDim.y * 8) acc += gy[b * O + o];
+    __shared__ float part[8][33];
+    part[w][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (w == 0 && o < O) {
+        float s = 0.f;
+        for (int k = 0; k < 8; ++k) s += part[k][threadIdx.x];
+        atomicAdd(gb + o, s);
+    }
+}
+
+static int small_gemm(const GemmArgs& a0, int splits, cudaStream_t st) {
+    GemmArgs a = a0;
+    splits = std::max(1, std::min(splits, (a.K + LG_BK - 1) / LG_BK));
+    a.k_per_split = ((a.K + splits - 1) / splits + LG_BK - 1) / LG_BK * LG_BK;
+    splits = (a.K + a.k_per_split - 1) / a.k_per_split;
+    const long long mt = (a.M + LG_BM - 1) / LG_BM;
+    if (mt > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
+    const dim3 grid((unsigned)mt, (unsigned)((a.N + LG_BN - 1) / LG_BN), (unsigned)splits);
+    small_gemm_kernel<<<grid, LG_THREADS, 0, st>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+}  // namespace fetode
+
+using namespace fetode;
+
+extern "C" int fetode_linear_fwd(const float* x, const float* weight, const float* bias, float* y, int64_t B,
+                                 int32_t in_features, int32_t out_features, void* stream) {
+    FETODE_CHECK_ARG(x && weight && y && B >= 0 && in_features >= 1 && out_features >= 1);
+    if (B == 0) return FETODE_OK;
+    GemmArgs a{};
+    a.A = x; a.sAm = in_features; a.sAk = 1;
+    a.B = weight; a.sBk = 1; a.sBn = in_features;           // B(k, n) = W[n, k]
+    a.bias = bias; a.C = y; a.M = B; a.N = out_features; a.K = in_features;
+    return small_gemm(a, 1, (cudaStream_t)stream);
+}
+
+extern "C" int fetode_linear_bwd(const float* x, const float* weight, const float* gy, float* gx, float* gweight,
+                                 float* gbias, int64_t B, int32_t in_features, int32_t out_features, void* stream) {
+    FETODE_CHECK_ARG(x && weight && gy && B >= 0 && in_features >= 1 && out_features >= 1);
+    if (B == 0) return FETODE_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (gx) {                                               // gx[b, k] = sum_o gy[b, o] W[o, k]
+        GemmArgs a{};
+        a.A = gy; a.sAm = out_features; a.sAk = 1;
+        a.B = weight; a.sBk = in_features; a.sBn = 1;
+        a.C = gx; a.M = B; a.N = in_features; a.K = out_features;
+        const int rc = small_gemm(a, 1, st);
+        if (rc) return rc;
+    }
+    if (gweight) {                                          // gW[o, k] += sum_b gy[b, o] x[b, k]   (caller zeroes)
+        if (B > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
+        GemmArgs a{};
+        a.A = gy; a.sAm = 1; a.sAk = out_features;          // A(m = o, k = b) = gy[b, o]
+        a.B = x; a.sBk = in_features; a.sBn = 1;            // B(k = b, n) = x[b, n]
+        a.C = gweight; a.M = out_features; a.N = in_features; a.K = (int)B;
+        const long long tiles = ((out_features + LG_BM - 1) / LG_BM) * (long long)((in_features + LG_BN - 1) / LG_BN);
+        int splits = (int)std::max(1LL, std::min<long long>(148LL * 2 / tiles, (B + 127) / 128));
+        if (splits < 2) splits = 2;                         // always the accumulate path: the buffer is added to
+        const int rc = small_gemm(a, splits, st);
+        if (rc) return rc;
+    }
+    if (gbias) {
+        const long long by = std::max(1LL, std::min<long long>((B + 63) / 64, 64));
+        colsum_acc_kernel<<<dim3((out_features + 31) / 32, (unsigned)by), 256, 0, st>>>(gy, gbias, B, out_features);
+    }
+    return FETODE_LAUNCH_RC();
+}

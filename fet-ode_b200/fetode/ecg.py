@@ -137,13 +137,11 @@ class MLPKANODEFunc(nn.Module):
         return self._gain_val
 
     def forward(self, t, h):
-        h = self.ln(h)
-        # h_bound * tanh(h / h_bound) :461 ; both scalings are exact no-ops for the default h_bound = 1
-        h = torch.tanh(h) if self.h_bound == 1.0 else self.h_bound * torch.tanh(h / self.h_bound)
+        h = ops.ln_tanh(h, self.ln, self.h_bound)           # LayerNorm + h_bound * tanh(h / h_bound) :459-461, one kernel
         phi = self.h_feat(h, nan_to_num=True)                # sigmoid + nan_to_num fused into the neuron kernel :464-465
         z = self.act(self.kan1(phi))
         z = self.act(self.kan2(z))
-        dh = self.out(z)
+        dh = ops.linear(z, self.out)                         # nn.Linear(hidden, latent) :475, fp32 FMA kernel
         return self._gain() * dh
 
 
@@ -159,7 +157,7 @@ class No_MLP_KANODEFunc(nn.Module):
         nn.init.normal_(self.proj.weight, mean=0.0, std=0.01)
 
     def forward(self, t, h):
-        dh = self.proj(self.feat(h))
+        dh = ops.linear(self.feat(h), self.proj)
         assert dh.shape == h.shape, (dh.shape, h.shape)
         return dh
 

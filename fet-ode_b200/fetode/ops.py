@@ -312,6 +312,88 @@ def kanlinear_apply(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Ten
 
 
 # --------------------------------------------------------------------------------------
+# LayerNorm + tanh bound (prologue of the ECG right-hand side)
+# --------------------------------------------------------------------------------------
+class LnTanhFn(torch.autograd.Function):
+    """y = h_bound * tanh(LayerNorm(x) / h_bound), train_ecg_kan_fet_nn_ode.py:459-461, one launch each way."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps, h_bound):
+        B, D = x.shape
+        y = torch.empty_like(x)
+        stats = torch.empty(2, B, dtype=torch.float32, device=x.device)
+        g, b = f32c(gamma.detach()), f32c(beta.detach())
+        check(lib().fetode_ln_tanh_fwd(ptr(x), ptr(g), ptr(b), ptr(y), ptr(stats[0]), ptr(stats[1]), C.c_int64(B),
+                                       C.c_int32(D), C.c_float(eps), C.c_float(h_bound), stream()), "ln_tanh_fwd")
+        ctx.save_for_backward(x, g, stats, y)
+        ctx.h_bound = h_bound
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, g, stats, y = ctx.saved_tensors
+        B, D = x.shape
+        gy = f32c(gy)
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        gp = torch.zeros(2, D, dtype=torch.float32, device=x.device)
+        check(lib().fetode_ln_tanh_bwd(ptr(x), ptr(g), ptr(stats[0]), ptr(stats[1]), ptr(y), ptr(gy), ptr(gx),
+                                       ptr(gp[0]) if ctx.needs_input_grad[1] else None,
+                                       ptr(gp[1]) if ctx.needs_input_grad[2] else None, C.c_int64(B), C.c_int32(D),
+                                       C.c_float(ctx.h_bound), stream()), "ln_tanh_bwd")
+        return (gx, gp[0] if ctx.needs_input_grad[1] else None, gp[1] if ctx.needs_input_grad[2] else None, None, None)
+
+
+def ln_tanh(x: torch.Tensor, ln: torch.nn.LayerNorm, h_bound: float) -> torch.Tensor:
+    """Fused when the kernel has the case (CUDA fp32 [B, D], D <= 256, affine LayerNorm over the last axis); other
+    configurations keep the reference's two torch ops."""
+    if (x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and ln.elementwise_affine and ln.bias is not None
+            and tuple(ln.normalized_shape) == (x.shape[1],) and x.shape[1] <= 256 and h_bound > 0):
+        return LnTanhFn.apply(f32c(x), ln.weight, ln.bias, float(ln.eps), float(h_bound))
+    h = ln(x)
+    return torch.tanh(h) if h_bound == 1.0 else h_bound * torch.tanh(h / h_bound)
+
+
+class LinearFn(torch.autograd.Function):
+    """y = x W^T + b in fp32 FMA arithmetic (csrc/linear.cu): the dense head of the ECG right-hand side."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        B, K = x.shape
+        O = weight.shape[0]
+        y = torch.empty(B, O, dtype=torch.float32, device=x.device)
+        w = f32c(weight.detach())
+        b = None if bias is None else f32c(bias.detach())
+        check(lib().fetode_linear_fwd(ptr(x), ptr(w), ptr(b), ptr(y), C.c_int64(B), C.c_int32(K), C.c_int32(O),
+                                      stream()), "linear_fwd")
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        B, K = x.shape
+        O = w.shape[0]
+        gy = f32c(gy)
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        want_w = ctx.needs_input_grad[1]
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        flat = torch.zeros(O * K + O, dtype=torch.float32, device=x.device) if (want_w or want_b) else None
+        gw = flat[:O * K].view(O, K) if want_w else None
+        gb = flat[O * K:] if want_b else None
+        check(lib().fetode_linear_bwd(ptr(x), ptr(w), ptr(gy), ptr(gx), ptr(gw), ptr(gb), C.c_int64(B), C.c_int32(K),
+                                      C.c_int32(O), stream()), "linear_bwd")
+        return gx, gw, gb
+
+
+def linear(x: torch.Tensor, lin: torch.nn.Linear) -> torch.Tensor:
+    """nn.Linear on a CUDA fp32 [B, in] input through csrc/linear.cu; anything else keeps the module's own call."""
+    if x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and lin.weight.dtype == torch.float32:
+        return LinearFn.apply(f32c(x), lin.weight, lin.bias)
+    return lin(x)
+
+
+# --------------------------------------------------------------------------------------
 # fused small-width network + Runge-Kutta loop
 # --------------------------------------------------------------------------------------
 class SmallNetPlan:

@@ -118,6 +118,27 @@ FETODE_API int fetode_kanlinear_bwd_acc(const fetode_kanlayer_t* L, const float*
 FETODE_API int fetode_kanlinear_unfold(const fetode_kanlayer_t* L, float* ws_acc, const fetode_kanlayer_grads_t* grads,
                          void* stream);
 
+/* ---- normalise-and-bound prologue of the ECG right-hand side ------------------------------
+ * Replaces  h = self.ln(h); h = self.h_bound * torch.tanh(h / self.h_bound)  (train_ecg_kan_fet_nn_ode.py:459-461;
+ * nn.LayerNorm(latent_dim), eps 1e-5, affine) and its autograd.  x, y, gy, gx [B, D] row-major, D <= 256;
+ * mean / rstd [B] are written by _fwd and read by _bwd; ggamma / gbeta [D] are ADDED to (caller zeroes), any of
+ * gx / ggamma / gbeta may be NULL. */
+FETODE_API int fetode_ln_tanh_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean,
+                       float* rstd, int64_t B, int32_t D, float eps, float h_bound, void* stream);
+FETODE_API int fetode_ln_tanh_bwd(const float* x, const float* gamma, const float* mean, const float* rstd,
+                       const float* y, const float* gy, float* gx, float* ggamma, float* gbeta, int64_t B,
+                       int32_t D, float h_bound, void* stream);
+
+/* ---- dense head of the ECG right-hand side -----------------------------------------------
+ * Replaces  dh = self.out(z)  (nn.Linear(hidden, latent_dim), train_ecg_kan_fet_nn_ode.py:446,475; also self.proj
+ * :497,505) and its autograd, in fp32 FMA arithmetic like the reference.  x [B, in], weight [out, in] (torch layout),
+ * bias [out] or NULL, y [B, out].  _bwd: gx [B, in] overwritten (or NULL); gweight [out, in] and gbias [out] must be
+ * zero-filled by the caller and receive the sums over the batch (or NULL). */
+FETODE_API int fetode_linear_fwd(const float* x, const float* weight, const float* bias, float* y, int64_t B,
+                      int32_t in_features, int32_t out_features, void* stream);
+FETODE_API int fetode_linear_bwd(const float* x, const float* weight, const float* gy, float* gx, float* gweight,
+                      float* gbias, int64_t B, int32_t in_features, int32_t out_features, void* stream);
+
 /* B-spline basis values alone: KANLinear.b_splines efficientkan.py:117-131 (used by update_grid :184-221 and
  * curve2coeff :133-143 on CUDA inputs).  grid [I, G+2k+1], x [B,I] -> out [B, I, G+k]; spline_order must be 3. */
 FETODE_API int fetode_bspline_basis(const float* grid, const float* x, float* out, int64_t B, int32_t I,

@@ -1,0 +1,71 @@
+"""GPU parity of the fused LayerNorm + tanh-bound prologue (csrc/glue.cu) against the two torch ops the reference
+uses (train_ecg_kan_fet_nn_ode.py:459-461), forward and gradients, fp32.  Tolerance: 2e-6 of the max-norm forward
+(fp32 rounding of the statistics), 2e-5 for gradients (row reductions in a different order)."""
+import pytest
+import torch
+
+from fetode import ops
+from conftest import max_rel
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("B,D,hb", [(4096, 64, 1.0), (1, 64, 1.0), (37, 16, 2.5), (300, 200, 1.0), (5, 256, 0.7),
+                                    (129, 3, 1.0)])
+def test_ln_tanh_matches_torch(cuda, B, D, hb):
+    gen = torch.Generator().manual_seed(B * 7 + D)
+    x = (torch.randn(B, D, generator=gen) * 2.0 + 0.3).to(cuda)
+    ln = torch.nn.LayerNorm(D).to(cuda)
+    with torch.no_grad():
+        ln.weight.copy_(torch.rand(D, generator=gen) + 0.5)
+        ln.bias.copy_(torch.randn(D, generator=gen) * 0.2)
+    w = torch.randn(B, D, generator=gen).to(cuda)
+
+    def run(fused):
+        ln.zero_grad()
+        xi = x.clone().requires_grad_(True)
+        if fused:
+            y = ops.ln_tanh(xi, ln, hb)
+        else:
+            y = hb * torch.tanh(ln(xi) / hb)
+        (y * w).sum().backward()
+        return y.detach(), xi.grad, ln.weight.grad.clone(), ln.bias.grad.clone()
+
+    y0, gx0, gg0, gb0 = run(False)
+    y1, gx1, gg1, gb1 = run(True)
+    assert max_rel(y1, y0) < 2e-6
+    assert max_rel(gx1, gx0) < 2e-5
+    assert max_rel(gg1, gg0) < 2e-5
+    assert max_rel(gb1, gb0) < 2e-5
+
+
+def test_ln_tanh_falls_back_to_torch_ops_outside_the_kernel_cases(cuda):
+    x = torch.randn(8, 300, device=cuda)                     # D > 256: the reference's two ops
+    ln = torch.nn.LayerNorm(300).to(cuda)
+    assert torch.equal(ops.ln_tanh(x, ln, 1.0), torch.tanh(ln(x)))
+
+
+@pytest.mark.parametrize("B,K,O,bias", [(4096, 128, 64, True), (1, 128, 64, True), (77, 768, 64, True), (300, 10, 3, False),
+                                        (5000, 33, 130, True)])
+def test_linear_matches_torch_fp32(cuda, B, K, O, bias):
+    """csrc/linear.cu against nn.Linear in fp32 (TF32 off, the torch default): forward 2e-6 of the max-norm,
+    gradients 2e-5 (batch reductions in a different order)."""
+    gen = torch.Generator().manual_seed(B + K + O)
+    lin = torch.nn.Linear(K, O, bias=bias).to(cuda)
+    x = torch.randn(B, K, generator=gen).to(cuda)
+    w = torch.randn(B, O, generator=gen).to(cuda)
+
+    def run(fused):
+        lin.zero_grad()
+        xi = x.clone().requires_grad_(True)
+        y = ops.linear(xi, lin) if fused else lin(xi)
+        (y * w).sum().backward()
+        return y.detach(), xi.grad, lin.weight.grad.clone(), None if not bias else lin.bias.grad.clone()
+
+    y0, gx0, gw0, gb0 = run(False)
+    y1, gx1, gw1, gb1 = run(True)
+    assert max_rel(y1, y0) < 2e-6
+    assert max_rel(gx1, gx0) < 2e-6
+    assert max_rel(gw1, gw0) < 2e-5
+    if bias:
+        assert max_rel(gb1, gb0) < 2e-5
