@@ -14,7 +14,9 @@
 //   gy is loaded once, split hi/lo (3xTF32: hi*hi + hi*lo + lo*hi, see kanlinear_tc.cu) and stays resident
 //   (<= 128 KB); the weight chunks ([NCOL x 32 outputs] hi+lo tiles, pre-split / pre-swizzled by kl_td_pack_kernel)
 //   stream through a ring via the TMA bulk-copy engine.  The contraction is only O <= 128 long (48 MMAs), so one
-//   accumulator per chunk is enough; four of them rotate in TMEM so that the epilogue warps never stall the MMA.
+//   accumulator per chunk is enough.  Two consecutive chunks share every MMA (N = 2 NCOL: the kernel is bound by the
+//   shared-memory operand reads, and this reads the 128-row gy operand once per 8 inputs instead of once per 4);
+//   two such double-width accumulators alternate in TMEM.
 //   warps 0-15  gy prologue, then epilogue: set (warp >> 2) takes every 4th chunk (the per-row derivative
 //               evaluation is a latency-bound chain, so four sets run concurrently); thread = row (TMEM lane):
 //               tcgen05.ld of the FP values of one input, derivative evaluation, gx store, branch-parameter partial
@@ -30,8 +32,8 @@ namespace tcx {
 
 using namespace tc;
 
-constexpr int NSW = 4;                  // weight-stage ring depth
-constexpr int NACC = 4;                 // TMEM accumulators in flight
+constexpr int NSW = 2;                  // weight-stage ring depth (a stage = one K slab of a two-chunk group)
+constexpr int NACC = 2;                 // TMEM accumulators in flight, each two chunks (8 inputs) wide
 constexpr int NEPI = 4;                 // epilogue sets of 4 warps; set s owns chunks s, s + NEPI, .. (accumulator s)
 static_assert(NACC % NEPI == 0 || NEPI % NACC == 0, "every accumulator must belong to one epilogue set");
 constexpr uint32_t GY_SLAB = BM * 32 * 4;      // one [128 x 32] K-slab of gy (hi or lo): 16 KB
@@ -189,8 +191,11 @@ __global__ void __launch_bounds__(NEPI * 128 + 64, 1) kl_tc_dx_kernel(const DXAr
     constexpr int NCOL = 4 * FP;                        // MMA N: one chunk = 4 inputs
     constexpr int NV = 2 * NB;                          // branch-parameter partial sums per input
     static_assert(NV == 0 || NV == 16 || NV == 20, "warp reduction is laid out for NB = 8 or 10");
-    constexpr uint32_t W_TILE = NCOL * 32 * 4;          // one of hi / lo
-    constexpr uint32_t TMEM_COLS = NACC * NCOL <= 256 ? 256u : 512u;
+    constexpr int NCOL2 = 2 * NCOL;                     // two chunks share one MMA (N = NCOL2): the gy operand is read
+                                                        // from shared memory once per 8 inputs instead of once per 4
+    constexpr uint32_t W_TILE = NCOL * 32 * 4;          // one chunk, one of hi / lo
+    constexpr uint32_t W_TILE2 = 2 * W_TILE;            // a stage holds [hi: chunk 0 | chunk 1][lo: chunk 0 | chunk 1]
+    constexpr uint32_t TMEM_COLS = NACC * NCOL2 <= 256 ? 256u : 512u;
     constexpr int TMA_WARP = 4 * NEPI, MMA_WARP = TMA_WARP + 1;
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
@@ -200,7 +205,7 @@ __global__ void __launch_bounds__(NEPI * 128 + 64, 1) kl_tc_dx_kernel(const DXAr
     const int osplit = blockIdx.y;
     const int o0 = osplit * 128;
     const int KS = min(4, (O - o0 + 31) / 32);          // 32-output K slabs of this CTA
-    const uint32_t offGy = 0, offW = (uint32_t)KS * 2 * GY_SLAB, offAcc = offW + NSW * 2 * W_TILE,
+    const uint32_t offGy = 0, offW = (uint32_t)KS * 2 * GY_SLAB, offAcc = offW + NSW * 2 * W_TILE2,
                    offBar = offAcc + NEPI * 2 * 4 * (NV > 0 ? NV : 4) * 4;
     const uint32_t barWFull = base + offBar, barWEmpty = barWFull + 8 * NSW, barAccFull = barWEmpty + 8 * NSW,
                    barAccEmpty = barAccFull + 8 * NACC, barGy = barAccEmpty + 8 * NACC;
@@ -214,7 +219,7 @@ __global__ void __launch_bounds__(NEPI * 128 + 64, 1) kl_tc_dx_kernel(const DXAr
 
     if (tid == 0) {
         for (int s = 0; s < NSW; ++s) { mbar_init(barWFull + 8 * s, 1); mbar_init(barWEmpty + 8 * s, 1); }
-        for (int s = 0; s < NACC; ++s) { mbar_init(barAccFull + 8 * s, 1); mbar_init(barAccEmpty + 8 * s, 128); }
+        for (int s = 0; s < NACC; ++s) { mbar_init(barAccFull + 8 * s, 1); mbar_init(barAccEmpty + 8 * s, 256); }
         mbar_init(barGy, NEPI * 128);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -271,21 +276,31 @@ __global__ void __launch_bounds__(NEPI * 128 + 64, 1) kl_tc_dx_kernel(const DXAr
             if (has_prev) pn = ldx(a.prev, chunk0 + set);
         }
         const uint32_t tlane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        for (int lc = set; lc < nch; lc += NEPI) {
+        // set s takes chunks s, s + 4, ..: chunk lc is the (lc & 1) half of accumulator (lc >> 1) & 1, whose
+        // (lc >> 2)-th use this is; the two sets sharing an accumulator both wait for it and both release it
+        const int ncg = (nch + 1) / 2;
+        for (int lc = set; lc < 2 * ncg; lc += NEPI) {
             const int chunk = chunk0 + lc;
-            const int acc = lc % NACC;
+            const int acc = (lc >> 1) & 1;
+            if (lc >= nch) {                                    // odd tail: this half of the last group is empty
+                mbar_wait(barAccFull + 8 * acc, (lc >> 2) & 1);
+                tc_fence_after();
+                tc_fence_before();
+                mbar_arrive(barAccEmpty + 8 * acc);
+                continue;
+            }
             const float4 xc = xn, pc = pn;
             if (lc + NEPI < nch) {
                 xn = ldx(a.x, chunk + NEPI);
                 if (has_prev) pn = ldx(a.prev, chunk + NEPI);
             }
-            mbar_wait(barAccFull + 8 * acc, (lc / NACC) & 1);
+            mbar_wait(barAccFull + 8 * acc, (lc >> 2) & 1);
             tc_fence_after();
             float* pa = pacc + (set * 2 + ((lc / NEPI) & 1)) * 4 * (NV > 0 ? NV : 4);
 #pragma unroll 1
             for (int ii = 0; ii < 4; ++ii) {
                 float g[FP];
-                const uint32_t taddr = tlane + (uint32_t)(acc * NCOL + ii * FP);
+                const uint32_t taddr = tlane + (uint32_t)(acc * NCOL2 + (lc & 1) * NCOL + ii * FP);
                 if constexpr (FP == 20) { tmem_ld<16>(taddr, g); tmem_ld<4>(taddr + 16, g + 16); }
                 else { tmem_ld<8>(taddr, g); tmem_ld<4>(taddr + 8, g + 8); }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -327,36 +342,44 @@ __global__ void __launch_bounds__(NEPI * 128 + 64, 1) kl_tc_dx_kernel(const DXAr
     } else if (warp == TMA_WARP) {
         // ===================== TMA: weight stages =====================
         if (lane == 0) {
-            const uint32_t bytes = 2 * W_TILE;
-            const size_t stage_floats = (size_t)2 * NCOL * 32;
-            const int nit = nch * KS;
+            const size_t stage_floats = (size_t)2 * NCOL * 32;     // one chunk's [hi | lo] pair in the packed image
+            const int ncg = (nch + 1) / 2;
+            const int nit = ncg * KS;
             for (int it = 0; it < nit; ++it) {
                 const int s = it % NSW;
-                const int lc = it / KS, ks = it % KS;
+                const int g = it / KS, ks = it % KS;
+                const int nc = min(2, nch - 2 * g);
                 mbar_wait(barWEmpty + 8 * s, ((it / NSW) & 1) ^ 1);
-                mbar_arrive_expect_tx(barWFull + 8 * s, bytes);
-                const float* src = a.wtd + ((size_t)(chunk0 + lc) * L.td_KS + (size_t)(osplit * 4 + ks)) * stage_floats;
-                bulk_g2s(base + offW + (uint32_t)s * 2 * W_TILE, src, bytes, barWFull + 8 * s);
+                mbar_arrive_expect_tx(barWFull + 8 * s, (uint32_t)nc * 2 * W_TILE);
+                const uint32_t dst = base + offW + (uint32_t)s * 2 * W_TILE2;
+                for (int j = 0; j < nc; ++j) {
+                    const float* src = a.wtd + ((size_t)(chunk0 + 2 * g + j) * L.td_KS + (size_t)(osplit * 4 + ks)) * stage_floats;
+                    bulk_g2s(dst + (uint32_t)j * W_TILE, src, W_TILE, barWFull + 8 * s);
+                    bulk_g2s(dst + W_TILE2 + (uint32_t)j * W_TILE, src + NCOL * 32, W_TILE, barWFull + 8 * s);
+                }
             }
         }
     } else if (warp == MMA_WARP) {
         // ===================== MMA issue =====================
         if (lane == 0) {
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NCOL >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t idesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NCOL >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NCOL2 >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
             mbar_wait(barGy, 0);
             tc_fence_after();
             int it = 0;
-            for (int lc = 0; lc < nch; ++lc) {
-                const int acc = lc % NACC;
-                mbar_wait(barAccEmpty + 8 * acc, ((lc / NACC) & 1) ^ 1);
+            const int ncg = (nch + 1) / 2;
+            for (int g = 0; g < ncg; ++g) {
+                const int acc = g & 1;
+                const uint32_t idesc = nch - 2 * g >= 2 ? idesc2 : idesc1;
+                mbar_wait(barAccEmpty + 8 * acc, ((g >> 1) & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t d = tmem_base + (uint32_t)(acc * NCOL);
+                const uint32_t d = tmem_base + (uint32_t)(acc * NCOL2);
                 for (int ks = 0; ks < KS; ++ks, ++it) {
                     const int s = it % NSW;
                     mbar_wait(barWFull + 8 * s, (it / NSW) & 1);
                     tc_fence_after();
                     const uint32_t gHi = base + offGy + (uint32_t)ks * 2 * GY_SLAB, gLo = gHi + GY_SLAB;
-                    const uint32_t wHi = base + offW + (uint32_t)s * 2 * W_TILE, wLo = wHi + W_TILE;
+                    const uint32_t wHi = base + offW + (uint32_t)s * 2 * W_TILE2, wLo = wHi + W_TILE2;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const uint64_t dAh = umma_desc(gHi + j * 32), dAl = umma_desc(gLo + j * 32);
@@ -447,7 +470,7 @@ int kl_tc_dx(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, c
     }
     const int KS = std::min(4, L.td_KS);
     const int NCOL = 4 * L.td_FP;
-    size_t smem = (size_t)KS * 2 * tcx::GY_SLAB + (size_t)tcx::NSW * 2 * NCOL * 128 + tcx::NEPI * 2 * 4 * std::max(2 * L.NB, 4) * 4 + 512 + 1024;
+    size_t smem = (size_t)KS * 2 * tcx::GY_SLAB + (size_t)tcx::NSW * 2 * 2 * NCOL * 128 + tcx::NEPI * 2 * 4 * std::max(2 * L.NB, 4) * 4 + 512 + 1024;
     smem = std::max<size_t>(smem, 120 * 1024);              // one CTA per SM: the kernel allocates all of TMEM
     const dim3 grid((unsigned)mt, (unsigned)osplits, (unsigned)splits);
     switch (P->branch) {
