@@ -192,36 +192,48 @@ __device__ __forceinline__ bool hard_gate(float z) {
     return __fdiv_rn(1.0f, s) > 0.5f;
 }
 
+// thread = one parameter (i, j), held in registers; the CTA walks a tile of rows: the x load is a broadcast within each
+// run of K lanes, the stores are contiguous, and no per-element index division or parameter reload remains
+constexpr int FEF_ROWS = 16;
+
 template <int VARIANT>
 __global__ void __launch_bounds__(256) ferro_elem_fwd_kernel(const FerroArgs a) {
-    const long long n = a.B * a.I * a.K;
     const int IK = a.I * a.K;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
-        const long long b = e / IK;
-        const int p = (int)(e % IK), i = p / a.K;
-        const float x = a.x[b * a.I + i];
-        float out;
-        if constexpr (VARIANT == FETODE_FERRO_LOGISTIC) {
-            out = 2.0f * sigm(a.k[p] * (x - a.Ec[p]));                          // efficientkan.py:24
-            if (a.basis_out) a.basis_out[e] = out;
-        } else if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
-            const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
-            const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), a.k[p], a.Ec[p], 1.0f, a.g, a.alpha);
-            const float P = fmaf(a.Ps[p], s.T, a.bias[p]);
-            if (a.basis_out) a.basis_out[e] = P;
-            out = a.coef[p] * P;
-        } else {
-            const float pv = a.prev_is_zero ? 0.f : a.prev[i];                  // ONE row shared by the batch :93
-            const bool up = hard_gate(a.g * (x - pv));                          // :122-123
-            const float Ec = a.Ec[p], Ps = a.Ps[p];
-            const float s = sigm(a.k[p] * (up ? x - Ec : x + Ec));              // :116-117
-            out = fmaf(2.0f * Ps, s, -Ps) + a.bias[p];                          // :126
-            if (a.gate_out) a.gate_out[e] = up ? 1 : 0;
-            if (a.basis_out) a.basis_out[e] = out;
-            if (a.apply_sigmoid) out = sigm(out);                               // KANFeatureMixer :419
-            if (a.apply_sigmoid == 2 && out != out) out = 0.f;                  // + nan_to_num(nan=0) :465 (sigmoid is never +-inf)
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= IK) return;
+    const int i = p / a.K;
+    const float k = a.k[p], Ec = a.Ec[p];
+    const float Ps = VARIANT == FETODE_FERRO_LOGISTIC ? 0.f : a.Ps[p], bias = VARIANT == FETODE_FERRO_LOGISTIC ? 0.f : a.bias[p];
+    const float coef = VARIANT == FETODE_FERRO_TWO_D ? a.coef[p] : 1.0f;
+    const float pv_shared = (VARIANT == FETODE_FERRO_HARDGATE && !a.prev_is_zero) ? a.prev[i] : 0.f;   // ONE row shared by the batch :93
+    for (long long b0 = (long long)blockIdx.y * FEF_ROWS; b0 < a.B; b0 += (long long)gridDim.y * FEF_ROWS) {
+        const int nb = (int)min((long long)FEF_ROWS, a.B - b0);
+#pragma unroll 4
+        for (int t = 0; t < nb; ++t) {
+            const long long b = b0 + t;
+            const long long e = b * IK + p;
+            const float x = a.x[b * a.I + i];
+            float out;
+            if constexpr (VARIANT == FETODE_FERRO_LOGISTIC) {
+                out = 2.0f * sigm(k * (x - Ec));                                    // efficientkan.py:24
+                if (a.basis_out) a.basis_out[e] = out;
+            } else if constexpr (VARIANT == FETODE_FERRO_TWO_D) {
+                const float pv = a.prev_is_zero ? 0.f : a.prev[b * a.I + i];
+                const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), k, Ec, 1.0f, a.g, a.alpha);
+                const float P = fmaf(Ps, s.T, bias);
+                if (a.basis_out) a.basis_out[e] = P;
+                out = coef * P;
+            } else {
+                const bool up = hard_gate(a.g * (x - pv_shared));                   // :122-123
+                const float s = sigm(k * (up ? x - Ec : x + Ec));                   // :116-117
+                out = fmaf(2.0f * Ps, s, -Ps) + bias;                               // :126
+                if (a.gate_out) a.gate_out[e] = up ? 1 : 0;
+                if (a.basis_out) a.basis_out[e] = out;
+                if (a.apply_sigmoid) out = sigm(out);                               // KANFeatureMixer :419
+                if (a.apply_sigmoid == 2 && out != out) out = 0.f;                  // + nan_to_num(nan=0) :465 (sigmoid is never +-inf)
+            }
+            a.out[e] = out;
         }
-        a.out[e] = out;
     }
 }
 
@@ -364,11 +376,13 @@ extern "C" int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const f
         if (br) ferro_full_fwd_kernel<true><<<grid, FF_THREADS, smem, st>>>(a);
         else ferro_full_fwd_kernel<false><<<grid, FF_THREADS, smem, st>>>(a);
     } else {
-        const long long n = B * a.I * a.K;
-        const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
-        if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_fwd_kernel<FETODE_FERRO_TWO_D><<<blocks, 256, 0, st>>>(a);
-        else if (F->variant == FETODE_FERRO_LOGISTIC) ferro_elem_fwd_kernel<FETODE_FERRO_LOGISTIC><<<blocks, 256, 0, st>>>(a);
-        else ferro_elem_fwd_kernel<FETODE_FERRO_HARDGATE><<<blocks, 256, 0, st>>>(a);
+        const long long by = std::min<long long>((B + FEF_ROWS - 1) / FEF_ROWS, 65535);
+        const int IK = a.I * a.K;
+        const int threads = std::min(256, (IK + 31) / 32 * 32);        // narrow layers (LV: I*K = 20) get narrow CTAs
+        const dim3 blocks((unsigned)((IK + threads - 1) / threads), (unsigned)by);
+        if (F->variant == FETODE_FERRO_TWO_D) ferro_elem_fwd_kernel<FETODE_FERRO_TWO_D><<<blocks, threads, 0, st>>>(a);
+        else if (F->variant == FETODE_FERRO_LOGISTIC) ferro_elem_fwd_kernel<FETODE_FERRO_LOGISTIC><<<blocks, threads, 0, st>>>(a);
+        else ferro_elem_fwd_kernel<FETODE_FERRO_HARDGATE><<<blocks, threads, 0, st>>>(a);
     }
     rc = FETODE_LAUNCH_RC();
     if (rc) return rc;
