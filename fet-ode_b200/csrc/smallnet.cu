@@ -58,7 +58,7 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
         const int d = idx / (NB / 2), p = idx % (NB / 2);
         const float4 lo = branch_params(P1, d * NB + p), hi = branch_params(P1, d * NB + p + NB / 2);
         float4* q = reinterpret_cast<float4*>(img + L.l1_bq) + d * NB + 2 * p;
-        q[0] = make_float4(lo.x, hi.x, lo.y, hi.y);
+        q[0] = make_float4(bq_c1(P1, lo.x), bq_c1(P1, hi.x), lo.y, hi.y);
         q[1] = make_float4(lo.z, hi.z, lo.w, hi.w);
     }
     for (int o = tid; o < D; o += nt) {
@@ -93,7 +93,7 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
         for (int p = 0; p < NB / 2; ++p) {
             const float4 lo = branch_params(P2, h * NB + p), hi = branch_params(P2, h * NB + p + NB / 2);
             float4* q = reinterpret_cast<float4*>(rec + L.r_bq) + 2 * p;
-            q[0] = make_float4(lo.x, hi.x, lo.y, hi.y);
+            q[0] = make_float4(bq_c1(P2, lo.x), bq_c1(P2, hi.x), lo.y, hi.y);
             q[1] = make_float4(lo.z, hi.z, lo.w, hi.w);
         }
         for (int o = 0; o < D; ++o) {

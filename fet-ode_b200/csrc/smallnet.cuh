@@ -247,6 +247,17 @@ __device__ __forceinline__ void sn_rhs_scalar(const float* __restrict__ sm, int 
     }
 }
 
+// FERRO2D: crossed_neg_j = 1 / (1 + 2^(x gl + c1_j)) for the NB thresholds of one input shares its x-dependent factor,
+// 2^(x gl + c1_j) = 2^(x gl) * 2^(c1_j): the pair-ordered image stores C_j = 2^(c1_j) and the kernel spends ONE ex2 per
+// input instead of NB (the MUFU pipe is this kernel's busiest).  Both exponents are clamped to +-FETODE_EXP_SPLIT so each
+// factor is finite and non-zero: the product may overflow to inf (-> min(.., 2^30), exactly what the clamped sum gives)
+// or underflow to 0 (2^t ~ 0 there), never NaN.  min(2^t, 2^30) keeps rcp_batch2's operand range.
+#define FETODE_EXP_SPLIT 126.0f
+__device__ inline float bq_c1(const fetode_kanlayer_t& P, float c1) {
+    if (P.branch != FETODE_BRANCH_FERRO2D) return c1;
+    return exp2f(fminf(fmaxf(c1, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT));
+}
+
 // The NB branch factors of one input, two bases per lane pair: R[p] = (r_p, r_{p + NB/2}).  bq: the pair-ordered
 // constants (l1_bq / r_bq), two float4 per pair: (P_lo.x, P_hi.x, P_lo.y, P_hi.y), (P_lo.z, P_hi.z, P_lo.w, P_hi.w).
 template <int NB, int BR>
@@ -257,14 +268,14 @@ __device__ __forceinline__ void branch_eval2(float x, float omu, float gl, const
     f32x2 A[NP > 0 ? NP : 1];
     if constexpr (NB > 0 && BR == FETODE_BRANCH_FERRO2D) {
         f32x2 CN[NP];
-        const float xg = x * gl;
-        const f32x2 xg2 = pk2(xg, xg), omu2 = pk2(omu, omu);
+        const float ex = ex2_approx(fminf(fmaxf(x * gl, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT));
+        const f32x2 ex2v = pk2(ex, ex), omu2 = pk2(omu, omu);
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
             const float4 q0 = bq[2 * p];
             float t0, t1;
-            upk2(add2(xg2, pk2(q0.x, q0.y)), t0, t1);
-            A[p] = add2(pk2(ex2_approx(fminf(t0, FETODE_EXP_CLAMP)), ex2_approx(fminf(t1, FETODE_EXP_CLAMP))), one2);
+            upk2(mul2(ex2v, pk2(q0.x, q0.y)), t0, t1);          // 2^(x gl) * 2^(c1_j)
+            A[p] = add2(pk2(fminf(t0, 1073741824.0f), fminf(t1, 1073741824.0f)), one2);
         }
         rcp_batch2<NP>(A, CN);                                  // crossed_neg_Ec  ferro_class.py:563
 #pragma unroll
