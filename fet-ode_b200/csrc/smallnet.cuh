@@ -74,9 +74,10 @@ __host__ __device__ constexpr SNLayout sn_layout(int D, int H, int NB, int G) {
 // device: per-input features
 // ------------------------------------------------------------------------------------------
 // r[j] = 1/(1+2^t_j): the only input-dependent factor of branch basis j (see header comment)
+// cn_out (FERRO2D, optional): the crossed_neg factors, for a backward pass that would otherwise recompute them
 template <int NB, int BR>
 __device__ __forceinline__ void branch_eval(float x, float omu, float gl, const float4* __restrict__ bp,
-                                            float (&r)[NB > 0 ? NB : 1]) {
+                                            float (&r)[NB > 0 ? NB : 1], float* cn_out = nullptr) {
     if constexpr (NB > 0 && BR == FETODE_BRANCH_FERRO2D) {
         float a[NB], cn[NB];
         const float xg = x * gl;
@@ -84,6 +85,10 @@ __device__ __forceinline__ void branch_eval(float x, float omu, float gl, const 
         for (int j = 0; j < NB; ++j)
             a[j] = 1.0f + ex2_approx(fminf(xg + bp[j].x, FETODE_EXP_CLAMP));
         rcp_batch<NB>(a, cn);                                   // crossed_neg_Ec  ferro_class.py:563
+        if (cn_out) {
+#pragma unroll
+            for (int j = 0; j < NB; ++j) cn_out[j] = cn[j];
+        }
 #pragma unroll
         for (int j = 0; j < NB; ++j) {
             const float4 p = bp[j];

@@ -69,13 +69,15 @@ __device__ __forceinline__ float spl_at(int s, int m, const float (&v)[4]) {
 
 // d(loss)/d(branch inputs) for one (input, basis j): given G = d(loss)/d r_j returns d(loss)/dx and the two
 // raw-parameter contributions.  FERRO2D: SURVEY appendix A.4 with branch_sign == 1; LOGISTIC: A.3.
-template <int BR>
+// HAVE_CN: cn_in holds crossed_neg from the forward evaluation of the same point (branch_eval's cn_out); otherwise it is
+// recomputed from c1 (one ex2 + one rcp).
+template <int BR, bool HAVE_CN = false>
 __device__ __forceinline__ void branch_bwd(float x, float omu, float gl, float al2, float c1, float r, float G,
-                                           float p0, float p1, float& gx, float& g0, float& g1) {
+                                           float p0, float p1, float& gx, float& g0, float& g1, float cn_in = 0.f) {
     if constexpr (BR == FETODE_BRANCH_FERRO2D) {
         const float g = gl * (1.0f / FETODE_LOG2E);
         const float k = p0, Ec = p1;
-        const float cn = rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, gl, c1), FETODE_EXP_CLAMP)));
+        const float cn = HAVE_CN ? cn_in : rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, gl, c1), FETODE_EXP_CLAMP)));
         const float dcn = -g * cn * (1.0f - cn);                  // d/dx == d/dEc
         const float domu = -g * omu * (1.0f - omu);
         const float m = 1.0f - al2 * omu * cn;
@@ -181,8 +183,9 @@ __device__ __forceinline__ void sn_rhs_bwd(const float* __restrict__ sm, const f
         const float sl = x * sg;
         float omu = 0.f;
         if constexpr (BR == FETODE_BRANCH_FERRO2D) omu = rcp_approx(1.0f + ex2_approx(gl2 * (x - prev2[h * SN_THREADS])));
-        float r2[NBR];
-        branch_eval<NB, BR>(x, omu, gl2, reinterpret_cast<const float4*>(rec + L.r_bp), r2);
+        float r2[NBR], cn2[NBR];
+        branch_eval<NB, BR>(x, omu, gl2, reinterpret_cast<const float4*>(rec + L.r_bp), r2,
+                            BR == FETODE_BRANCH_FERRO2D ? cn2 : nullptr);
         const float* wu2 = rec + L.r_wu2;
         float G0 = 0.f;
 #pragma unroll
@@ -215,7 +218,8 @@ __device__ __forceinline__ void sn_rhs_bwd(const float* __restrict__ sm, const f
             for (int o = 0; o < DV; ++o) Gj = fmaf(go[o], wu2[(1 + j) * DV + o], Gj);
             const float4 bp = reinterpret_cast<const float4*>(rec + L.r_bp)[j];
             float gx;
-            branch_bwd<BR>(x, omu, gl2, al2, bp.x, r2[j], Gj, raw2[h * NB + j], raw2[(H + h) * NB + j], gx, c0[j], c1[j]);
+            branch_bwd<BR, true>(x, omu, gl2, al2, bp.x, r2[j], Gj, raw2[h * NB + j], raw2[(H + h) * NB + j], gx, c0[j],
+                                 c1[j], cn2[j]);
             gx2 += gx;
         }
         // ---- layer 1, output h: d(loss)/d(features of layer 1)
