@@ -62,7 +62,11 @@ __global__ void kl_pack_kernel(fetode_kanlayer_t P, KLLayout L, float* blob) {
         }
         pack_knots_row(P.grid + (size_t)i * L.NK, L.NK, L.NKP, t + L.t_kn, t + L.t_rd1, t + L.t_rd2, t + L.t_rd3,
                        t + L.t_gi);
-        for (int j = 0; j < NB; ++j) reinterpret_cast<float4*>(t + L.t_bp)[j] = branch_params(P, (int)i * NB + j);
+        for (int j = 0; j < NB; ++j) {
+            float4 q = branch_params(P, (int)i * NB + j);
+            q.x = bq_c1(P, q.x);                            // FERRO2D: 2^(c1) (smallnet.cuh, bq_c1)
+            reinterpret_cast<float4*>(t + L.t_bp)[j] = q;
+        }
     }
 }
 

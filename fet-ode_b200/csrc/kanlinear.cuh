@@ -67,9 +67,10 @@ __host__ __device__ inline KLLayout kl_layout(int I, int O, int G, int NB) {
 //   LOGISTIC: r_j = 1/(1+2^(-a(x-b) log2e))                 (phi = 2 r)
 //   FERRO2D : r_j = 1/(1+2^(2 log2e k (x + Ec*momentum)))   (tanh = 1 - 2 r)
 template <int BR>
-__device__ __forceinline__ float kl_branch_r(float x, float omu, float gl, const float4 p) {
+__device__ __forceinline__ float kl_branch_r(float x, float omu, float ex, const float4 p) {
     if constexpr (BR == FETODE_BRANCH_FERRO2D) {
-        const float cn = rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, gl, p.x), FETODE_EXP_CLAMP)));
+        // ex = ferro_ex(x, gl), p.x = 2^(c1_j): 1 + min(2^(x gl + c1_j), 2^30)   (smallnet.cuh, bq_c1)
+        const float cn = rcp_approx(1.0f + fminf(ex * p.x, 1073741824.0f));
         const float sl = omu * cn;
         const float t = fmaf(p.w, sl, fmaf(p.y, x, p.z));
         return rcp_approx(1.0f + ex2_approx(fminf(t, FETODE_EXP_CLAMP)));
@@ -102,7 +103,8 @@ __device__ __forceinline__ void kl_features(float x, float prev, float gl, const
         if constexpr (BR == FETODE_BRANCH_FERRO2D)
             omu = rcp_approx(1.0f + ex2_approx(gl * (x - prev)));                    // 1 - is_moving_up  ferro_class.py:560
         const float4* bp = reinterpret_cast<const float4*>(tab + L.t_bp);
-        for (int j = 0; j < L.NB; ++j) col[(1 + S + j) * stride] = kl_branch_r<BR>(x, omu, gl, bp[j]);
+        const float ex = BR == FETODE_BRANCH_FERRO2D ? ferro_ex(x, gl) : 0.f;
+        for (int j = 0; j < L.NB; ++j) col[(1 + S + j) * stride] = kl_branch_r<BR>(x, omu, ex, bp[j]);
     }
 }
 

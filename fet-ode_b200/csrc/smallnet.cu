@@ -53,7 +53,11 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
                        img + L.l1_rd1 + d * L.NKP, img + L.l1_rd2 + d * L.NKP, img + L.l1_rd3 + d * L.NKP,
                        img + L.l1_gi + d * 4);
     for (int idx = tid; idx < D * NB; idx += nt)
-        reinterpret_cast<float4*>(img + L.l1_bp)[idx] = branch_params(P1, idx);
+    {
+        float4 q = branch_params(P1, idx);
+        q.x = bq_c1(P1, q.x);                               // FERRO2D: 2^(c1) (see smallnet.cuh, bq_c1)
+        reinterpret_cast<float4*>(img + L.l1_bp)[idx] = q;
+    }
     for (int idx = tid; idx < D * (NB / 2); idx += nt) {                      // pair (p, p + NB/2) of input d
         const int d = idx / (NB / 2), p = idx % (NB / 2);
         const float4 lo = branch_params(P1, d * NB + p), hi = branch_params(P1, d * NB + p + NB / 2);
@@ -89,7 +93,11 @@ __global__ void smallnet_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2,
         rec[L.r_b1] = (float)b;
         pack_knots_row(P2.grid + (size_t)h * L.NK, L.NK, L.NKP, rec + L.r_kn, rec + L.r_rd1, rec + L.r_rd2,
                        rec + L.r_rd3, rec + L.r_gi);
-        for (int j = 0; j < NB; ++j) reinterpret_cast<float4*>(rec + L.r_bp)[j] = branch_params(P2, h * NB + j);
+        for (int j = 0; j < NB; ++j) {
+            float4 q = branch_params(P2, h * NB + j);
+            q.x = bq_c1(P2, q.x);
+            reinterpret_cast<float4*>(rec + L.r_bp)[j] = q;
+        }
         for (int p = 0; p < NB / 2; ++p) {
             const float4 lo = branch_params(P2, h * NB + p), hi = branch_params(P2, h * NB + p + NB / 2);
             float4* q = reinterpret_cast<float4*>(rec + L.r_bq) + 2 * p;

@@ -73,6 +73,20 @@ __host__ __device__ constexpr SNLayout sn_layout(int D, int H, int NB, int G) {
 // ------------------------------------------------------------------------------------------
 // device: per-input features
 // ------------------------------------------------------------------------------------------
+// FERRO2D: crossed_neg_j = 1 / (1 + 2^(x gl + c1_j)) for the NB thresholds of one input shares its x-dependent factor,
+// 2^(x gl + c1_j) = 2^(x gl) * 2^(c1_j): the pair-ordered image stores C_j = 2^(c1_j) and the kernel spends ONE ex2 per
+// input instead of NB (the MUFU pipe is this kernel's busiest).  Both exponents are clamped to +-FETODE_EXP_SPLIT so each
+// factor is finite and non-zero: the product may overflow to inf (-> min(.., 2^30), exactly what the clamped sum gives)
+// or underflow to 0 (2^t ~ 0 there), never NaN.  min(2^t, 2^30) keeps rcp_batch2's operand range.
+#define FETODE_EXP_SPLIT 126.0f
+__device__ __forceinline__ float ferro_ex(float x, float gl) {
+    return ex2_approx(fminf(fmaxf(x * gl, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT));
+}
+__device__ inline float bq_c1(const fetode_kanlayer_t& P, float c1) {
+    if (P.branch != FETODE_BRANCH_FERRO2D) return c1;
+    return exp2f(fminf(fmaxf(c1, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT));
+}
+
 // r[j] = 1/(1+2^t_j): the only input-dependent factor of branch basis j (see header comment)
 // cn_out (FERRO2D, optional): the crossed_neg factors, for a backward pass that would otherwise recompute them
 template <int NB, int BR>
@@ -80,10 +94,10 @@ __device__ __forceinline__ void branch_eval(float x, float omu, float gl, const 
                                             float (&r)[NB > 0 ? NB : 1], float* cn_out = nullptr) {
     if constexpr (NB > 0 && BR == FETODE_BRANCH_FERRO2D) {
         float a[NB], cn[NB];
-        const float xg = x * gl;
+        const float ex = ferro_ex(x, gl);
 #pragma unroll
         for (int j = 0; j < NB; ++j)
-            a[j] = 1.0f + ex2_approx(fminf(xg + bp[j].x, FETODE_EXP_CLAMP));
+            a[j] = 1.0f + fminf(ex * bp[j].x, 1073741824.0f);   // bp.x = 2^(c1_j): 1 + min(2^(x gl + c1_j), 2^30)
         rcp_batch<NB>(a, cn);                                   // crossed_neg_Ec  ferro_class.py:563
         if (cn_out) {
 #pragma unroll
@@ -252,17 +266,6 @@ __device__ __forceinline__ void sn_rhs_scalar(const float* __restrict__ sm, int 
     }
 }
 
-// FERRO2D: crossed_neg_j = 1 / (1 + 2^(x gl + c1_j)) for the NB thresholds of one input shares its x-dependent factor,
-// 2^(x gl + c1_j) = 2^(x gl) * 2^(c1_j): the pair-ordered image stores C_j = 2^(c1_j) and the kernel spends ONE ex2 per
-// input instead of NB (the MUFU pipe is this kernel's busiest).  Both exponents are clamped to +-FETODE_EXP_SPLIT so each
-// factor is finite and non-zero: the product may overflow to inf (-> min(.., 2^30), exactly what the clamped sum gives)
-// or underflow to 0 (2^t ~ 0 there), never NaN.  min(2^t, 2^30) keeps rcp_batch2's operand range.
-#define FETODE_EXP_SPLIT 126.0f
-__device__ inline float bq_c1(const fetode_kanlayer_t& P, float c1) {
-    if (P.branch != FETODE_BRANCH_FERRO2D) return c1;
-    return exp2f(fminf(fmaxf(c1, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT));
-}
-
 // The NB branch factors of one input, two bases per lane pair: R[p] = (r_p, r_{p + NB/2}).  bq: the pair-ordered
 // constants (l1_bq / r_bq), two float4 per pair: (P_lo.x, P_hi.x, P_lo.y, P_hi.y), (P_lo.z, P_hi.z, P_lo.w, P_hi.w).
 template <int NB, int BR>
@@ -273,7 +276,7 @@ __device__ __forceinline__ void branch_eval2(float x, float omu, float gl, const
     f32x2 A[NP > 0 ? NP : 1];
     if constexpr (NB > 0 && BR == FETODE_BRANCH_FERRO2D) {
         f32x2 CN[NP];
-        const float ex = ex2_approx(fminf(fmaxf(x * gl, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT));
+        const float ex = ferro_ex(x, gl);
         const f32x2 ex2v = pk2(ex, ex), omu2 = pk2(omu, omu);
 #pragma unroll
         for (int p = 0; p < NP; ++p) {

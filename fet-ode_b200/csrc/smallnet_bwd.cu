@@ -70,14 +70,14 @@ __device__ __forceinline__ float spl_at(int s, int m, const float (&v)[4]) {
 // d(loss)/d(branch inputs) for one (input, basis j): given G = d(loss)/d r_j returns d(loss)/dx and the two
 // raw-parameter contributions.  FERRO2D: SURVEY appendix A.4 with branch_sign == 1; LOGISTIC: A.3.
 // HAVE_CN: cn_in holds crossed_neg from the forward evaluation of the same point (branch_eval's cn_out); otherwise it is
-// recomputed from c1 (one ex2 + one rcp).
+// recomputed from et = 2^(x gl) * 2^(c1_j), the caller's ferro_ex(x, gl) times the packed constant (one rcp).
 template <int BR, bool HAVE_CN = false>
-__device__ __forceinline__ void branch_bwd(float x, float omu, float gl, float al2, float c1, float r, float G,
+__device__ __forceinline__ void branch_bwd(float x, float omu, float gl, float al2, float et, float r, float G,
                                            float p0, float p1, float& gx, float& g0, float& g1, float cn_in = 0.f) {
     if constexpr (BR == FETODE_BRANCH_FERRO2D) {
         const float g = gl * (1.0f / FETODE_LOG2E);
         const float k = p0, Ec = p1;
-        const float cn = HAVE_CN ? cn_in : rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, gl, c1), FETODE_EXP_CLAMP)));
+        const float cn = HAVE_CN ? cn_in : rcp_approx(1.0f + fminf(et, 1073741824.0f));
         const float dcn = -g * cn * (1.0f - cn);                  // d/dx == d/dEc
         const float domu = -g * omu * (1.0f - omu);
         const float m = 1.0f - al2 * omu * cn;
@@ -263,11 +263,12 @@ __device__ __forceinline__ void sn_rhs_bwd(const float* __restrict__ sm, const f
         for (int c = 0; c < 4; ++c) g = fmaf(U1s[d][c], dv1[d][c], g);
         if constexpr (NB > 0) {
             float c0[NBR], c1[NBR];
+            const float ex1 = BR == FETODE_BRANCH_FERRO2D ? ferro_ex(x, gl1) : 0.f;
 #pragma unroll
             for (int j = 0; j < NB; ++j) {
                 const float4 bp = reinterpret_cast<const float4*>(sm + L.l1_bp)[d * NB + j];
                 float gx;
-                branch_bwd<BR>(x, omu1[d], gl1, al1, bp.x, r1[d][j], U1u[d][1 + j], raw1[d * NB + j],
+                branch_bwd<BR>(x, omu1[d], gl1, al1, ex1 * bp.x, r1[d][j], U1u[d][1 + j], raw1[d * NB + j],
                                raw1[(D + d) * NB + j], gx, c0[j], c1[j]);
                 g += gx;
             }
