@@ -345,7 +345,8 @@ class LnTanhFn(torch.autograd.Function):
 
 def ln_tanh(x: torch.Tensor, ln: torch.nn.LayerNorm, h_bound: float) -> torch.Tensor:
     """Fused when the kernel has the case (CUDA fp32 [B, D], D <= 256, affine LayerNorm over the last axis); other
-    configurations keep the reference's two torch ops."""
+    configurations keep the reference's two torch ops (on the device: CPU tensors are refused like everywhere else)."""
+    _require_cuda(x, "input")
     if (x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and ln.elementwise_affine and ln.bias is not None
             and tuple(ln.normalized_shape) == (x.shape[1],) and x.shape[1] <= 256 and h_bound > 0):
         return LnTanhFn.apply(f32c(x), ln.weight, ln.bias, float(ln.eps), float(h_bound))
@@ -387,7 +388,9 @@ class LinearFn(torch.autograd.Function):
 
 
 def linear(x: torch.Tensor, lin: torch.nn.Linear) -> torch.Tensor:
-    """nn.Linear on a CUDA fp32 [B, in] input through csrc/linear.cu; anything else keeps the module's own call."""
+    """nn.Linear on a CUDA fp32 [B, in] input through csrc/linear.cu; other shapes / dtypes keep the module's own call
+    (on the device: CPU tensors are refused like everywhere else)."""
+    _require_cuda(x, "input")
     if x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and lin.weight.dtype == torch.float32:
         return LinearFn.apply(f32c(x), lin.weight, lin.bias)
     return lin(x)
