@@ -17,8 +17,10 @@ What makes the capture sound here:
   * all parameter versions are bumped before capture, so the packed weight images are rebuilt INSIDE the graph
     (a replayed step must repack after the optimiser changed the parameters).
 
-Not supported under capture (they synchronise with the host by construction): dopri5 (adaptive accept / reject),
-``update_grid``, the stateful ``ferro_class`` bases whose state changes shape after the first call.
+Not supported under capture (they synchronise with the host by construction): dopri5 (adaptive accept / reject) and
+``update_grid``.  The soft ferroelectric bases work when the step resets their state itself (the Lotka-Volterra loop calls
+``reset_state()`` every iteration, so no state crosses a replay boundary); state that must survive from one step to the
+next is only carried for the hard-gated ``ecg.LogisticBasis``.
 """
 from __future__ import annotations
 
