@@ -51,6 +51,44 @@ def uniform_knots(in_features: int, grid_size: int = 5, order: int = 3,
     return row.to(dtype).expand(in_features, -1).contiguous()
 
 
+def curve2coeff(x: Tensor, y: Tensor, knots: Tensor, order: int = 3) -> Tensor:
+    """Least-squares spline coefficients (efficientkan.py:133-143): x [B, I], y [B, I, O] -> [O, I, G+order]."""
+    A = bspline_basis(x, knots, order).transpose(0, 1)          # [I, B, S]
+    Bm = y.transpose(0, 1)                                       # [I, B, O]
+    return torch.linalg.lstsq(A, Bm).solution.permute(2, 0, 1).contiguous()
+
+
+def update_grid(x: Tensor, p: Params, *, grid_size: int = 5, order: int = 3, grid_eps: float = 0.02,
+                margin: float = 0.01):
+    """KANLinear.update_grid (efficientkan.py:184-221): returns (new knots [I, G+2k+1], new spline_weight [O, I, S]).
+    Sample-quantile knots blended with a uniform grid, `order` extrapolated knots either side, coefficients refitted so
+    that the spline part reproduces its old outputs on the batch."""
+    batch = x.size(0)
+    splines = bspline_basis(x, p["grid"], order).permute(1, 0, 2)                       # [I, B, S]
+    sw = p["spline_weight"] * p["spline_scaler"].unsqueeze(-1) if "spline_scaler" in p else p["spline_weight"]
+    unreduced = torch.bmm(splines, sw.permute(1, 2, 0)).permute(1, 0, 2)                # [B, I, O]
+    xs = torch.sort(x, dim=0)[0]
+    adaptive = xs[torch.linspace(0, batch - 1, grid_size + 1, dtype=torch.int64)]
+    step = (xs[-1] - xs[0] + 2 * margin) / grid_size
+    uniform = torch.arange(grid_size + 1, dtype=torch.float32).unsqueeze(1) * step + xs[0] - margin
+    grid = grid_eps * uniform + (1 - grid_eps) * adaptive
+    grid = torch.concatenate([grid[:1] - step * torch.arange(order, 0, -1).unsqueeze(1), grid,
+                              grid[-1:] + step * torch.arange(1, order + 1).unsqueeze(1)], dim=0)
+    knots = grid.T.contiguous()
+    return knots, curve2coeff(x, unreduced, knots, order)
+
+
+def regularization_loss(p: Params, regularize_activation=1.0, regularize_entropy=1.0, regularize_logistic_l1=0.0):
+    """efficientkan.py:223-237."""
+    l1 = p["spline_weight"].abs().mean(-1)
+    act = l1.sum()
+    q = l1 / (act + 1e-12)
+    reg = regularize_activation * act + regularize_entropy * (-torch.sum(q * (q + 1e-12).log()))
+    if regularize_logistic_l1 != 0.0 and "logistic_weight" in p:
+        reg = reg + regularize_logistic_l1 * p["logistic_weight"].abs().mean()
+    return reg
+
+
 # --------------------------------------------------------------------------------------
 # Logistic basis  (efficientkan.py:20-24)
 # --------------------------------------------------------------------------------------

@@ -93,3 +93,17 @@ def test_kuramoto_and_rk_loops_golden():
     assert max_rel(OS.rk2_midpoint(f, d["z0"]), d["rk2"]) < TOL
     assert max_rel(OS.rk4_classic(f, d["z0"]), d["rk4"]) < TOL
     assert max_rel(OS.rk4_substeps(f, d["z0"], torch.linspace(0, 1, 4), 3), d["rk4_sub"]) < TOL
+
+
+def test_update_grid_and_regularization_loss_against_reference_vectors():
+    """oracle.layers.update_grid / regularization_loss (efficientkan.py:184-237) against the vectors the live reference
+    produced (oracle/make_golden_grid.py).  The knots are exact fp32 arithmetic on sorted data; the refitted
+    coefficients come out of LAPACK's least squares, whose last bits depend on the thread count: 1e-5."""
+    from conftest import load_golden
+    from oracle import layers as OL
+    p, g = load_golden("update_grid_6x4")
+    assert torch.allclose(OL.regularization_loss(p), g["reg_default"], rtol=1e-6)
+    assert torch.allclose(OL.regularization_loss(p, 0.5, 2.0, 0.1), g["reg_custom"], rtol=1e-6)
+    knots, coef = OL.update_grid(g["x"], p, margin=0.01)
+    assert torch.equal(knots, g["grid_after"])
+    assert torch.allclose(coef, g["spline_weight_after"], rtol=1e-4, atol=1e-6)
