@@ -14,6 +14,7 @@ Step sizes are constants of the autograd graph.
 from __future__ import annotations
 
 import ctypes as C
+import math
 from typing import List
 
 import torch
@@ -84,6 +85,9 @@ def dopri5_integrate(func, y0, t, times: List[float], rtol, atol, options) -> to
     for tq in times[1:]:
         while tq > tb:
             t_new = tb + dt
+            # torchdiffeq's _adaptive_step asserts: a vanished or non-finite step must stop the solve, not spin
+            if not (math.isfinite(dt) and t_new > tb):
+                raise AssertionError(f"fetode.odeint(dopri5): underflow in dt {dt}")
             ks = [fy]
             yi = y
             for al, be in zip(_ALPHA, _BETA):
@@ -94,6 +98,10 @@ def dopri5_integrate(func, y0, t, times: List[float], rtol, atol, options) -> to
             y1 = yi
             err = combine(None, [k for k, c in zip(ks, _C_ERR) if c != 0.0], [c * dt for c in _C_ERR if c != 0.0])
             ratio = _sumsq(err, y, y1, atol, rtol, sync) ** 0.5
+            if not math.isfinite(ratio):
+                # min(10, max(nan, 0.2)) is 10 in Python: dt would GROW on every rejected attempt and the solve would
+                # never end.  torchdiffeq dies here too (dt becomes nan -> "underflow in dt" / non-finite state assert)
+                raise AssertionError("fetode.odeint(dopri5): non-finite values in the state / error estimate")
             if ratio <= 1.0:
                 dense = (y, y1, ks, dt)
                 ta, tb, y, fy = tb, t_new, y1, ks[-1]

@@ -47,6 +47,18 @@ class LogisticBasis(nn.Module):
         self.prev_x = torch.zeros(1, self.in_dim, self.num_basis, device=self.prev_x.device)
         self.branch_state = torch.ones(1, self.in_dim, self.num_basis, device=self.prev_x.device)
 
+    def _load_from_state_dict(self, state_dict, prefix, *args):
+        """prev_x is a stride-0 view of the compact row after any call: receive the checkpoint's buffers in real tensors
+        of the incoming shape (train_kan_fet_ett.py:353-358 restores the best state_dict), then re-read the row lazily."""
+        for name in ("prev_x", "branch_state"):
+            t = state_dict.get(prefix + name)
+            cur = self._buffers.get(name)
+            if t is not None and cur is not None:
+                self._buffers[name] = torch.empty(tuple(t.shape), dtype=t.dtype if name == "branch_state" else cur.dtype,
+                                                  device=cur.device)
+        super()._load_from_state_dict(state_dict, prefix, *args)
+        self._row = None                                                   # _prev_row() picks the loaded buffer up
+
     def _prev_row(self, device):
         if self._row is None:
             # honour a buffer written from outside (load_state_dict): first basis column carries the row
@@ -134,7 +146,15 @@ class MLPKANODEFunc(nn.Module):
             self._gain_val = None
             self._gain_val = self.scale * F.softplus(self.log_alpha)
             self._gain_key = key
+            if self._gain_val.requires_grad:
+                # once this node has been backpropagated its saved tensors are gone: a second forward + backward
+                # before any optimiser step (gradient accumulation) must build a new one
+                self._gain_val.register_hook(self._gain_used)
         return self._gain_val
+
+    def _gain_used(self, grad):
+        self._gain_key = None
+        return grad
 
     def forward(self, t, h):
         h = ops.ln_tanh(h, self.ln, self.h_bound)           # LayerNorm + h_bound * tanh(h / h_bound) :459-461, one kernel

@@ -157,7 +157,7 @@ class KANLinear(nn.Module):
             prev = self.logistic_basis._prev_rows(x2d.shape[0], x2d.device)
         y = ops.kanlinear_apply(self._pack, x2d, prev)
         if ferro:
-            self.logistic_basis._set_rows(x2d.detach())
+            self.logistic_basis._set_rows(x2d.detach().clone())   # own the state (reference: detach().clone())
         return y.reshape(*lead, self.out_features)
 
     # ---- grid adaptation / regulariser (PyTorch; efficientkan.py:184-237) ----------------------

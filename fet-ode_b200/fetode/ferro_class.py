@@ -31,7 +31,9 @@ class _FerroState:
         self._rows: Optional[torch.Tensor] = None       # [B, I]; None == reference's fresh [1,...] zeros
 
     def _set_rows(self, rows: torch.Tensor) -> None:
-        """Record x as the new previous input (ferro_class.py:409 / :584-590)."""
+        """Record x as the new previous input (ferro_class.py:409 / :584-590).  ``rows`` must be OWNED by the module
+        (the reference stores ``x.detach().clone()``): callers pass a copy of the user's input or a state tensor a
+        fused kernel wrote, never the input itself -- ``prev_x.zero_()`` from user code then cannot reach the data."""
         self._rows = rows
         view = rows
         for _ in range(len(self._tail) - 1):
@@ -67,6 +69,34 @@ class _FerroState:
             self._set_rows(fn(self._rows))
         return out
 
+    # ---- checkpoint restore (train_kan_fet_ett.py:353-358 reloads the best state_dict, buffers included) ----
+    # ``prev_x`` is a stride-0 view after any forward: copy_() into it is illegal, and the incoming buffer has the
+    # reference's expanded shape [B, *tail].  Receive it in a real tensor of the incoming shape, then fold it back
+    # into the compact rows (its first basis column).
+    def _load_from_state_dict(self, state_dict, prefix, *args):
+        for name in ("prev_x", "branch_sign"):
+            t = state_dict.get(prefix + name)
+            cur = self._buffers.get(name)
+            if t is not None and cur is not None:
+                self._buffers[name] = torch.empty(tuple(t.shape), dtype=cur.dtype, device=cur.device)
+        super()._load_from_state_dict(state_dict, prefix, *args)
+        self._adopt_loaded_buffers()
+
+    def _adopt_loaded_buffers(self):
+        p = self._buffers["prev_x"]
+        if p.dim() != len(self._tail) + 1 or tuple(p.shape[1:]) != self._tail:
+            return                                       # size mismatch: the base class has reported it
+        rows = p[(slice(None), slice(None)) + (0,) * (len(self._tail) - 1)]
+        if p.shape[0] == 1 and not bool((rows != 0).any()):
+            self._rows = None                            # the reference's fresh [1, ...] zeros
+            self.prev_x = torch.zeros(1, *self._tail, device=p.device)
+        else:
+            self._set_rows(rows.clone())
+        br = self._buffers["branch_sign"]
+        if hasattr(self, "_br_live"):
+            self._br_live = bool(getattr(self, "_update_branch", False) and br.dim() == len(self._tail) + 1
+                                 and (br.shape[0] > 1 or bool((br != 1).any())))
+
 
 class TwoDimensionFerroelectricBasis(_FerroState, nn.Module):
     """ferro_class.py:526-596.  Used in the ``logistic_basis`` slot of KANLinear to form KANFET;
@@ -93,7 +123,7 @@ class TwoDimensionFerroelectricBasis(_FerroState, nn.Module):
         out, _ = ops.ferro_apply(self, ops.FERRO_TWO_D, x2, prev)
         if self.use_noise:
             out = out + (torch.randn_like(out) * self.noise_std).detach() * self.coef
-        self._set_rows(x2.detach())
+        self._set_rows(x2.detach().clone())
         return out
 
 
@@ -164,7 +194,7 @@ class _FullFerro(_FerroState, nn.Module):
             noise = torch.randn_like(basis) * self.noise_std
             out = out + (noise * self.coef).sum(dim=(1, 3))
             basis = basis + noise
-        self._set_rows(x2.detach())
+        self._set_rows(x2.detach().clone())
         if self._update_branch:                          # :512-514
             self.branch_sign = side["br_out"]
             self._br_live = True
@@ -209,7 +239,7 @@ class BatchedFerroelectricBasis(_FullFerro):
             noise = torch.randn_like(basis) * self.noise_std
             out = out + (noise * self.coef).sum(dim=(1, 3))
             basis = basis + noise
-        self._set_rows(x2.detach()[-1:].contiguous())
+        self._set_rows(x2.detach()[-1:].clone())
         if return_activations:
             return out, basis, self.coef.detach()
         return out

@@ -57,6 +57,7 @@ class GraphedTrainStep:
         self.forward = forward if forward is not None else (lambda m, inp: m(inp))
         self.max_norm, self.allreduce = max_norm, bool(allreduce)
         self.x, self.y = x.clone(), y.clone()
+        self._params = [p for p in model.parameters()]
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):                       # eager steps: builds the flat buffers, warms every cache
@@ -100,4 +101,8 @@ class GraphedTrainStep:
         self.graph.replay()
         self.replays += 1
         self.opt.step_count += 1
+        # the replay changed the parameters behind autograd's back: bump their version counters (host only) so that
+        # every version-keyed cache (LayerPack.blob, SmallNetPlan.packed, MLPKANODEFunc._gain) is rebuilt by the next
+        # EAGER call, e.g. a validation pass between replays
+        torch.autograd.graph.increment_version(self._params)
         return self.loss

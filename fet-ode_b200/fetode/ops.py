@@ -99,7 +99,9 @@ class LayerView:
         for i in range(5):
             t = ts[f"bp{i}"]
             s.bp[i] = ptr(None if t is None else _keep(s, f32c(t.detach()))).value
-        s.scale_logistic = float(getattr(m, "scale_logistic", 1.0))
+        # mnist_kuramoto_kan.KANLinear (use_logistic_basis) never multiplies by scale_logistic in forward
+        # (mnist_kuramoto_kan.py:139-140); efficientkan.KANLinear does (efficientkan.py:149-158)
+        s.scale_logistic = 1.0 if "use_logistic_basis" in m.__dict__ else float(getattr(m, "scale_logistic", 1.0))
         lb = getattr(m, "logistic_basis", None)
         s.gate_slope = float(getattr(lb, "gate_slope", 10.0))
         s.alpha = float(getattr(lb, "alpha", 0.8))
