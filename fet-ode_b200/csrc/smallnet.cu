@@ -20,7 +20,9 @@
 //   (never written by TwoDimensionFerroelectricBasis) => momentum = 1 - 2(1-alpha)*to_lower.
 //   With r = 1/(1+2^t3):  coef*(Ps*tanh+bias)*W = W*coef*(Ps+bias) + (-2*W*coef*Ps)*r ; the first
 //   term is input independent and summed into a per-output bias at pack time.
+#include <cstdlib>
 #include "smallnet.cuh"
+#include "smallnet_v2.cuh"
 
 namespace fetode {
 
@@ -268,7 +270,18 @@ static int sn_launch_d(const fetode_smallnet_t* net, const SNArgs& a, cudaStream
     return FETODE_EUNSUPPORTED;
 }
 
+// FETODE_SN_V1=1 keeps the first-generation kernel for shapes the second one covers (A/B timing only; read once)
+static bool sn_force_v1() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("FETODE_SN_V1"); v = (e && e[0] == '1') ? 1 : 0; }
+    return v == 1;
+}
+
 static int sn_launch(const fetode_smallnet_t* net, const SNArgs& a, cudaStream_t st) {
+    if (sn2_has(net) && !sn_force_v1()) {
+        const int off = sn_layout(net->widths[0], net->widths[1], net->num_basis, net->grid_size).total_ext;
+        return sn2_launch(net, a, a.packed + off, st);
+    }
     switch (net->widths[0]) {
         case 1: return sn_launch_d<1>(net, a, st);
         case 2: return sn_launch_d<2>(net, a, st);
@@ -286,7 +299,7 @@ extern "C" int fetode_smallnet_supported(const fetode_smallnet_t* net) { return 
 
 extern "C" int64_t fetode_smallnet_packed_floats(const fetode_smallnet_t* net) {
     if (sn_check(net) != FETODE_OK) return -1;
-    return sn_layout(net->widths[0], net->widths[1], net->num_basis, net->grid_size).total_ext;
+    return sn_layout(net->widths[0], net->widths[1], net->num_basis, net->grid_size).total_ext + sn2_image_floats(net);
 }
 
 extern "C" int64_t fetode_smallnet_state_floats(const fetode_smallnet_t* net) {
@@ -313,7 +326,9 @@ extern "C" int fetode_smallnet_pack(const fetode_smallnet_t* net, const fetode_k
     }
     const SNLayout L = sn_layout(D, H, net->num_basis, net->grid_size);
     smallnet_pack_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(layers[0], layers[1], L, packed);
-    return FETODE_LAUNCH_RC();
+    rc = FETODE_LAUNCH_RC();
+    if (rc) return rc;
+    return sn2_pack(net, layers, packed + L.total_ext, (cudaStream_t)stream);    // second-generation image, appended
 }
 
 static int sn_run(const fetode_smallnet_t* net, const float* packed, int tab, const float* y0, float* y_out,

@@ -1,0 +1,662 @@
+// smallnet_v2.cu -- fused KAN / KANFET([2,10,2]) + Runge-Kutta loop, second generation (sm_100a).
+// Mapping and image: smallnet_v2.cuh.  Reference arithmetic replaced (file:line, reference checkout 704a0df4):
+//   KAN.forward / KANLinear.forward           efficient_kan/efficientkan.py:160-182, 274-279
+//   b_splines (Cox-de Boor)                   efficient_kan/efficientkan.py:117-131   (here: per-interval cubics)
+//   LogisticBasis.forward                     efficient_kan/efficientkan.py:20-24
+//   TwoDimensionFerroelectricBasis.forward    ferro_class.py:547-592                  (KANFET branch)
+//   integrate_euler / rk2 / rk4               train_ecg_kan_fet_nn_ode.py:670-705
+//   torchdiffeq fixed-grid euler/midpoint/rk4 (call sites train_kanfet_node_predprey.py:252)
+// Folding identities: smallnet.cu header.
+#include <cstdlib>
+#include "smallnet_v2.cuh"
+
+namespace fetode {
+
+// ------------------------------------------------------------------------------------------
+// pack
+// ------------------------------------------------------------------------------------------
+// Monomial coefficients (in s = x - t_m) of the cubic B-spline basis functions N^3_0..N^3_{NK-5} restricted to the
+// knot interval [t_m, t_{m+1}): the Cox-de Boor recursion of efficientkan.py:122-128 carried out on polynomials, in
+// double.  A zero knot difference drops its term (such an interval is empty under the reference's half-open test).
+__device__ inline void sn2_piece_polys(const float* t, int NK, int m, double (*P)[4]) {
+    for (int j = 0; j < NK - 1; ++j)
+        for (int k = 0; k < 4; ++k) P[j][k] = (j == m && k == 0) ? 1.0 : 0.0;
+    const double tm = (double)t[m];
+    for (int p = 1; p <= 3; ++p) {
+        for (int j = 0; j + p < NK - 1; ++j) {
+            const double d1 = (double)t[j + p] - (double)t[j], d2 = (double)t[j + p + 1] - (double)t[j + 1];
+            const double a = d1 != 0.0 ? 1.0 / d1 : 0.0, b = d2 != 0.0 ? 1.0 / d2 : 0.0;
+            const double l0 = tm - (double)t[j], r0 = (double)t[j + p + 1] - tm;
+            double o[4];
+            for (int k = 0; k < 4; ++k) {
+                const double pj1 = k > 0 ? P[j][k - 1] : 0.0, pn1 = k > 0 ? P[j + 1][k - 1] : 0.0;
+                o[k] = a * (pj1 + l0 * P[j][k]) + b * (r0 * P[j + 1][k] - pn1);
+            }
+            for (int k = 0; k < 4; ++k) P[j][k] = o[k];
+        }
+    }
+}
+
+__device__ inline void sn2_pack_input(const fetode_kanlayer_t& P, int i, const SN2Layout& L, float* gi, float* kn,
+                                      float* bc) {
+    const float* t = P.grid + (size_t)i * L.NK;
+    for (int j = 0; j < L.NKQ; ++j) kn[j] = t[j < 1 ? 0 : (j - 1 < L.NK ? j - 1 : L.NK - 1)];   // kn[1 + j] = t_j
+    gi[0] = t[0];
+    gi[1] = (float)(L.NK - 1) / (t[L.NK - 1] - t[0]);
+    gi[2] = t[L.NK - 1];
+    // gi[3] != 0: every knot lies within a quarter spacing of the uniform grid through t_0 and t_last, so the
+    // arithmetic interval guess is off by at most one (true for the constructor's grid, efficientkan.py:55-61;
+    // update_grid's quantile knots, :184-221, take the search loop)
+    const float hh = (t[L.NK - 1] - t[0]) / (float)(L.NK - 1);
+    bool uni = hh > 0.f;
+    for (int j = 0; j < L.NK; ++j) uni = uni && fabsf(t[j] - (t[0] + (float)j * hh)) <= 0.25f * hh;
+    gi[3] = uni ? 1.f : 0.f;
+    const int NB = L.NB;
+    if (P.branch == FETODE_BRANCH_FERRO2D) bc[6 * NB] = bc[6 * NB + 1] = -2.0f * (1.0f - P.alpha);
+    for (int j = 0; j < NB; ++j) {
+        const float4 q = branch_params(P, i * NB + j);
+        if (P.branch == FETODE_BRANCH_FERRO2D) {
+            bc[2 * j] = bc[2 * j + 1] = bq_c1(P, q.x);                     // C = 2^(c1)
+            bc[2 * NB + 4 * j] = bc[2 * NB + 4 * j + 1] = q.y;             // k'
+            bc[2 * NB + 4 * j + 2] = bc[2 * NB + 4 * j + 3] = q.z;         // c2'
+        } else {
+            bc[2 * NB + 4 * j] = bc[2 * NB + 4 * j + 1] = q.x;             // -a log2e
+            bc[2 * NB + 4 * j + 2] = bc[2 * NB + 4 * j + 3] = q.y;         // a b log2e
+        }
+    }
+}
+
+__global__ void sn2_pack_kernel(fetode_kanlayer_t P1, fetode_kanlayer_t P2, SN2Layout L, float* img) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int D = L.D, H = L.H, NB = L.NB, S = L.NK - 4, DO = D;
+    for (int i = tid; i < L.total; i += nt) img[i] = 0.f;
+    __syncthreads();
+    if (tid == 0) {
+        const float g1 = P1.gate_slope * FETODE_LOG2E, g2 = P2.gate_slope * FETODE_LOG2E;
+        img[L.hdr + 0] = img[L.hdr + 1] = g1;
+        img[L.hdr + 2] = img[L.hdr + 3] = g2;
+    }
+    for (int o = tid; o < DO; o += nt) {
+        double b = P2.branch_bias ? (double)P2.branch_bias[o] : 0.0;
+        for (int h = 0; h < H; ++h)
+            for (int j = 0; j < NB; ++j) { double wr, wc; branch_fold(P2, o, h, j, wr, wc); b += wc; }
+        img[L.b2 + 2 * o] = img[L.b2 + 2 * o + 1] = (float)b;
+    }
+    for (int h = tid; h < H; h += nt) {
+        double b = P1.branch_bias ? (double)P1.branch_bias[h] : 0.0;
+        for (int d = 0; d < D; ++d)
+            for (int j = 0; j < NB; ++j) { double wr, wc; branch_fold(P1, h, d, j, wr, wc); b += wc; }
+        img[L.b1 + 2 * h] = img[L.b1 + 2 * h + 1] = (float)b;
+    }
+    for (int d = tid; d < D; d += nt) {
+        float* blk = img + L.l1 + d * L.L1S;
+        sn2_pack_input(P1, d, L, blk + L.o_gi, blk + L.o_kn, blk + L.o_bc);
+        for (int h = 0; h < H; ++h) {
+            float* w = blk + L.o_w1 + h * L.W1Q;
+            w[0] = w[1] = P1.base_weight[h * D + d];
+            for (int j = 0; j < NB; ++j) {
+                double wr, wc;
+                branch_fold(P1, h, d, j, wr, wc);
+                w[2 + 2 * j] = w[3 + 2 * j] = (float)wr;
+            }
+        }
+    }
+    for (int h = tid; h < H; h += nt) {
+        float* rec = img + L.rec0 + h * L.REC;
+        sn2_pack_input(P2, h, L, rec + L.r_gi, rec + L.r_kn, rec + L.r_bc);
+        for (int o = 0; o < DO; ++o) {
+            float* w = rec + L.r_w2 + 2 * o;
+            w[0] = w[1] = P2.base_weight[o * H + h];
+            for (int j = 0; j < NB; ++j) {
+                double wr, wc;
+                branch_fold(P2, o, h, j, wr, wc);
+                w[(1 + j) * L.DOP * 2] = w[(1 + j) * L.DOP * 2 + 1] = (float)wr;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        bool uni = true;
+        for (int d = 0; d < D; ++d) uni = uni && img[L.l1 + d * L.L1S + L.o_gi + 3] != 0.f;
+        for (int h = 0; h < H; ++h) uni = uni && img[L.rec0 + h * L.REC + L.r_gi + 3] != 0.f;
+        img[L.hdr + 4] = uni ? 1.f : 0.f;
+    }
+    // piecewise-cubic spline tables: one task per (input, interval)
+    for (int task = tid; task < (D + H) * L.NI; task += nt) {
+        const bool first = task < D * L.NI;
+        const int i = first ? task / L.NI : (task - D * L.NI) / L.NI;
+        const int m = first ? task % L.NI : (task - D * L.NI) % L.NI;
+        const fetode_kanlayer_t& P = first ? P1 : P2;
+        double poly[16][4];
+        sn2_piece_polys(P.grid + (size_t)i * L.NK, L.NK, m, poly);
+        const int I = first ? D : H, O = first ? H : DO;
+        for (int o = 0; o < O; ++o) {
+            const double sc = P.spline_scaler ? (double)P.spline_scaler[o * I + i] : 1.0;
+            double c[4] = {0.0, 0.0, 0.0, 0.0};
+            for (int s = 0; s < S; ++s) {
+                const double w = (double)P.spline_weight[((size_t)o * I + i) * S + s] * sc;
+                for (int k = 0; k < 4; ++k) c[k] += w * poly[s][k];
+            }
+            float* dst = first ? img + L.l1tab + ((i * L.NI + m) * H + o) * 4
+                               : img + L.rec0 + i * L.REC + L.r_tab + (m * L.DOP + o) * 4;
+            for (int k = 0; k < 4; ++k) dst[k] = (float)c[k];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// device: features of one input for TP packed trajectory pairs
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ f32x2 ex2_pair(f32x2 t, float hi_clamp) {
+    float t0, t1;
+    upk2(t, t0, t1);
+    return pk2(ex2_approx(fminf(t0, hi_clamp)), ex2_approx(fminf(t1, hi_clamp)));
+}
+__device__ __forceinline__ f32x2 lds_pair(const float* p) {
+    const float2 v = *reinterpret_cast<const float2*>(p);
+    return pk2(v.x, v.y);
+}
+
+// x[p]: the input of TP pairs; prev[p]: the previous input (read; the caller advances it); bc: branch constants
+// out: silu[p] = x * sigmoid(x) (efficientkan.py:166), r[p][j] = 1 / (1 + 2^t_j) (smallnet.cu header)
+template <int NB, int BR, int TP>
+__device__ __forceinline__ void sn2_features(const f32x2 (&x)[TP], const f32x2 (&prev)[TP], f32x2 gl,
+                                             const float* __restrict__ bc, f32x2 (&silu)[TP], f32x2 (&r)[TP][NB]) {
+    const f32x2 one = pk2(1.0f, 1.0f), mone = pk2(-1.0f, -1.0f), nl2e = pk2(-FETODE_LOG2E, -FETODE_LOG2E);
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+        f32x2 den[TP][NB + 2], rec[TP][NB + 2], ex[TP];
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            den[p][0] = add2(ex2_pair(mul2(x[p], nl2e), FETODE_EXP_CLAMP), one);                    // 1 + e^-x
+            den[p][1] = add2(ex2_pair(mul2(fma2(prev[p], mone, x[p]), gl), FETODE_EXP_CLAMP), one);  // 1 + e^(g dx) :560
+            float u0, u1;
+            upk2(mul2(x[p], gl), u0, u1);
+            ex[p] = pk2(ex2_approx(fminf(fmaxf(u0, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT)),
+                        ex2_approx(fminf(fmaxf(u1, -FETODE_EXP_SPLIT), FETODE_EXP_SPLIT)));
+        }
+#pragma unroll
+        for (int j2 = 0; j2 < NB / 2; ++j2) {
+            const float4 c = reinterpret_cast<const float4*>(bc)[j2];                                 // C_j C_j C_j+1 C_j+1
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                float a0, a1, b0, b1;
+                upk2(fma2(ex[p], pk2(c.x, c.y), one), a0, a1);                                        // 1 + 2^(x gl) 2^(c1_j)
+                upk2(fma2(ex[p], pk2(c.z, c.w), one), b0, b1);
+                den[p][2 + 2 * j2] = pk2(fminf(a0, 1073741824.0f), fminf(a1, 1073741824.0f));
+                den[p][3 + 2 * j2] = pk2(fminf(b0, 1073741824.0f), fminf(b1, 1073741824.0f));
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            rcp_batch2<NB + 2>(den[p], rec[p]);                 // silu, 1 - moving_up, crossed_neg_j :563 in 3 MUFU pairs
+            silu[p] = mul2(x[p], rec[p][0]);
+        }
+        f32x2 a[TP][NB], nom[TP];
+#pragma unroll
+        for (int p = 0; p < TP; ++p) nom[p] = mul2(rec[p][1], pk2(bc[6 * NB], bc[6 * NB + 1]));      // -2(1-alpha) (1 - up)
+#pragma unroll
+        for (int j2 = 0; j2 < NB / 2; ++j2) {
+            const float4 k0 = reinterpret_cast<const float4*>(bc + 2 * NB)[2 * j2];                   // k' k' c2 c2
+            const float4 k1 = reinterpret_cast<const float4*>(bc + 2 * NB)[2 * j2 + 1];
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                // momentum = 1 - 2(1-alpha) switch_to_lower :567-571 ;  t = 2 log2e k (x + Ec momentum) :572-575
+                const f32x2 m0 = fma2(nom[p], rec[p][2 + 2 * j2], one);
+                const f32x2 m1 = fma2(nom[p], rec[p][3 + 2 * j2], one);
+                const f32x2 t0 = fma2(pk2(k0.z, k0.w), m0, mul2(pk2(k0.x, k0.y), x[p]));
+                const f32x2 t1 = fma2(pk2(k1.z, k1.w), m1, mul2(pk2(k1.x, k1.y), x[p]));
+                a[p][2 * j2] = add2(ex2_pair(t0, FETODE_EXP_CLAMP), one);
+                a[p][2 * j2 + 1] = add2(ex2_pair(t1, FETODE_EXP_CLAMP), one);
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < TP; ++p) rcp_batch2<NB>(a[p], r[p]);                                     // tanh = 1 - 2 r :578
+    } else {
+        f32x2 den[TP][NB + 1], rec[TP][NB + 1];
+#pragma unroll
+        for (int p = 0; p < TP; ++p) den[p][0] = add2(ex2_pair(mul2(x[p], nl2e), FETODE_EXP_CLAMP), one);
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+            const float4 ab = reinterpret_cast<const float4*>(bc + 2 * NB)[j];                        // A A B B
+#pragma unroll
+            for (int p = 0; p < TP; ++p)
+                den[p][1 + j] = add2(ex2_pair(fma2(x[p], pk2(ab.x, ab.y), pk2(ab.z, ab.w)), FETODE_EXP_CLAMP), one);
+        }
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            rcp_batch2<NB + 1>(den[p], rec[p]);                                                       // phi = 2 r  efficientkan.py:24
+            silu[p] = mul2(x[p], rec[p][0]);
+#pragma unroll
+            for (int j = 0; j < NB; ++j) r[p][j] = rec[p][1 + j];
+        }
+    }
+}
+
+// Knot interval of x, branch-free: m = largest j with t_j <= x (membership against the stored fp32 knots, i.e. the
+// reference's (x >= t_j) & (x < t_{j+1}) test, efficientkan.py:122), s = x - t_m, mask = 1 inside [t_0, t_last) else 0
+// (then s = 0, so the cubic stays finite and mask removes it).  kn is padded: kn[1 + j] = t_j, kn[0] = t_0.
+template <bool UNI>
+__device__ __forceinline__ void sn2_locate(float x, const float* kn, const float4 gi, int NK, int& m, float& s,
+                                           float& mask) {
+    const bool in = x >= gi.x && x < gi.z;
+    int g = (int)((x - gi.x) * gi.y);
+    g = min(max(g, 0), NK - 2);
+    float base;
+    if constexpr (UNI) {                                  // every input's grid is near-uniform (hdr[4], set by the pack kernel)
+        const float a = kn[g], b = kn[g + 1], c = kn[g + 2];
+        const bool dn = x < b, up = x >= c;
+        g = g - (dn ? 1 : 0) + (up ? 1 : 0);
+        base = dn ? a : (up ? c : b);
+        g = min(max(g, 0), NK - 2);
+    } else {
+        while (g > 0 && x < kn[g + 1]) --g;
+        while (g < NK - 2 && x >= kn[g + 2]) ++g;
+        base = kn[g + 1];
+    }
+    m = g;
+    s = in ? x - base : 0.f;
+    mask = in ? 1.f : 0.f;
+}
+
+__device__ __forceinline__ float sn2_horner(const float4 c, float s) {
+    return fmaf(fmaf(fmaf(c.w, s, c.z), s, c.y), s, c.x);
+}
+
+// ------------------------------------------------------------------------------------------
+// one right-hand-side evaluation for the TP pairs of this lane
+// ------------------------------------------------------------------------------------------
+template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool UNI>
+__device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x2 (&ys)[D][TP], f32x2 (&prev1)[D][TP],
+                                        f32x2* colcur, const f32x2* colprev, f32x2 (&out)[D][TP]) {
+    constexpr SN2Layout L = sn2_layout(D, H, NB, G);
+    constexpr int NK = L.NK;
+    const float4 hdr = *reinterpret_cast<const float4*>(sm + L.hdr);
+    // ---------------- layer 1: per input d, its features once, then a rolled loop over the H outputs; the partial
+    // sums of output h travel through this thread's column (colcur[h]) between the two inputs
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const float* blk = sm + L.l1 + d * L.L1S;
+        f32x2 silu[TP], r[TP][NB];
+        {
+            f32x2 xin[TP], pv[TP];
+#pragma unroll
+            for (int p = 0; p < TP; ++p) { xin[p] = ys[d][p]; pv[p] = prev1[d][p]; prev1[d][p] = ys[d][p]; }
+            sn2_features<NB, BR, TP>(xin, pv, pk2(hdr.x, hdr.y), blk + L.o_bc, silu, r);
+        }
+        // spline term: scalar per trajectory (the interval differs between the two halves of a pair)
+        const float4 gi = *reinterpret_cast<const float4*>(blk + L.o_gi);
+        float sp_s[2 * TP], sp_k[2 * TP];
+        int sp_m[2 * TP];
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            float xs[2];
+            upk2(ys[d][p], xs[0], xs[1]);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                int m;
+                sn2_locate<UNI>(xs[q], blk + L.o_kn, gi, NK, m, sp_s[2 * p + q], sp_k[2 * p + q]);
+                sp_m[2 * p + q] = (d * L.NI + m) * H;
+            }
+        }
+        const float4* tab = reinterpret_cast<const float4*>(sm + L.l1tab);
+#pragma unroll 2
+        for (int h = 0; h < H; ++h) {
+            f32x2 acc[TP];
+            if (d == 0) {
+                const f32x2 b = lds_pair(sm + L.b1 + 2 * h);
+#pragma unroll
+                for (int p = 0; p < TP; ++p) acc[p] = b;
+            } else {
+#pragma unroll
+                for (int p = 0; p < TP; ++p) acc[p] = colcur[(h * TP + p) * THREADS];
+            }
+            const float4* w4 = reinterpret_cast<const float4*>(blk + L.o_w1 + h * L.W1Q);
+#pragma unroll
+            for (int q = 0; q < (1 + NB + 1) / 2; ++q) {
+                const float4 w = w4[q];                              // features 2q, 2q+1 (0 = silu, 1+j = r_j)
+#pragma unroll
+                for (int p = 0; p < TP; ++p) {
+                    acc[p] = fma2(pk2(w.x, w.y), q == 0 ? silu[p] : r[p][2 * q - 1], acc[p]);
+                    if (2 * q + 1 <= NB) acc[p] = fma2(pk2(w.z, w.w), r[p][2 * q], acc[p]);
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                float lo, hi;
+                upk2(acc[p], lo, hi);
+                lo = fmaf(sn2_horner(tab[sp_m[2 * p] + h], sp_s[2 * p]), sp_k[2 * p], lo);
+                hi = fmaf(sn2_horner(tab[sp_m[2 * p + 1] + h], sp_s[2 * p + 1]), sp_k[2 * p + 1], hi);
+                colcur[(h * TP + p) * THREADS] = pk2(lo, hi);
+            }
+        }
+    }
+
+    // ---------------- layer 2: loop over its H inputs
+    {
+        const float4 b2 = *reinterpret_cast<const float4*>(sm + L.b2);
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            out[0][p] = pk2(b2.x, b2.y);
+            if constexpr (D > 1) out[1][p] = pk2(b2.z, b2.w);
+        }
+        static_assert(D <= 2, "v2 kernel: D <= 2");
+    }
+    const float* rec = sm + L.rec0;
+#pragma unroll 1
+    for (int h = 0; h < H; ++h, rec += L.REC) {
+        f32x2 xin[TP], pv[TP], silu[TP], r[TP][NB];
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            xin[p] = colcur[(h * TP + p) * THREADS];
+            pv[p] = colprev[(h * TP + p) * THREADS];
+        }
+        sn2_features<NB, BR, TP>(xin, pv, pk2(hdr.z, hdr.w), rec + L.r_bc, silu, r);
+        const float4* w4 = reinterpret_cast<const float4*>(rec + L.r_w2);
+#pragma unroll
+        for (int f = 0; f <= NB; ++f) {
+            const float4 w = w4[f];                                   // w[f][0] dup | w[f][1] dup
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                const f32x2 ft = f == 0 ? silu[p] : r[p][f - 1];
+                out[0][p] = fma2(pk2(w.x, w.y), ft, out[0][p]);
+                if constexpr (D > 1) out[1][p] = fma2(pk2(w.z, w.w), ft, out[1][p]);
+            }
+        }
+        const float4 gi = *reinterpret_cast<const float4*>(rec + L.r_gi);
+#pragma unroll
+        for (int p = 0; p < TP; ++p) {
+            float xs[2];
+            upk2(xin[p], xs[0], xs[1]);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                int m;
+                float s, mask;
+                sn2_locate<UNI>(xs[q], rec + L.r_kn, gi, NK, m, s, mask);
+                const float4* tab = reinterpret_cast<const float4*>(rec + L.r_tab) + m * L.DOP;
+#pragma unroll
+                for (int o = 0; o < D; ++o) {
+                    const float v = sn2_horner(tab[o], s);
+                    float lo, hi;
+                    upk2(out[o][p], lo, hi);
+                    if (q == 0) lo = fmaf(v, mask, lo); else hi = fmaf(v, mask, hi);
+                    out[o][p] = pk2(lo, hi);
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// kernel
+// ------------------------------------------------------------------------------------------
+// ALT: the 3/8-rule tableau (torchdiffeq "rk4") keeps k1, k2 across stages; it is a separate instantiation so the
+// other tableaus do not pay its registers
+template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool ALT, bool UNI>
+__device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restrict__ sm) {
+    constexpr SN2Layout L = sn2_layout(D, H, NB, G);
+    constexpr int TPL = 2 * TP;
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    constexpr int SF = FERRO ? D + H : 0;
+    const int tid = threadIdx.x;
+    f32x2* col0 = const_cast<f32x2*>(reinterpret_cast<const f32x2*>(sm + L.total)) + tid;   // [H][TP][THREADS] pairs
+    f32x2* col1 = col0 + H * TP * THREADS;
+
+    const long long base = (long long)blockIdx.x * (THREADS * TPL) + tid;   // trajectory of (pair p, half q): base + (2p+q) THREADS
+    if (base >= a.B) return;
+    bool live[TPL];
+#pragma unroll
+    for (int i = 0; i < TPL; ++i) live[i] = base + (long long)i * THREADS < a.B;
+
+    f32x2 y[D][TP], prev1[D][TP];
+#pragma unroll
+    for (int p = 0; p < TP; ++p) {
+        float v[2][D];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const long long b = base + (long long)(2 * p + q) * THREADS;
+#pragma unroll
+            for (int d = 0; d < D; ++d) v[q][d] = live[2 * p + q] ? a.y0[b * D + d] : 0.f;
+        }
+#pragma unroll
+        for (int d = 0; d < D; ++d) { y[d][p] = pk2(v[0][d], v[1][d]); prev1[d][p] = pk2(0.f, 0.f); }
+    }
+    f32x2* colprev = col0;      // previous layer-2 inputs (the reference's prev_x of layer 2, ferro_class.py:584-590)
+    f32x2* colcur = col1;
+    if constexpr (FERRO) {
+        if (!a.state_is_zero) {
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                const long long b0 = base + (long long)(2 * p) * THREADS, b1 = b0 + THREADS;
+                const bool l0 = live[2 * p], l1 = live[2 * p + 1];
+#pragma unroll
+                for (int d = 0; d < D; ++d)
+                    prev1[d][p] = pk2(l0 ? a.state[b0 * SF + d] : 0.f, l1 ? a.state[b1 * SF + d] : 0.f);
+#pragma unroll 1
+                for (int h = 0; h < H; ++h)
+                    colprev[(h * TP + p) * THREADS] = pk2(l0 ? a.state[b0 * SF + D + h] : 0.f,
+                                                          l1 ? a.state[b1 * SF + D + h] : 0.f);
+            }
+        } else {
+#pragma unroll 1
+            for (int i = 0; i < H * TP; ++i) colprev[i * THREADS] = pk2(0.f, 0.f);
+        }
+    }
+
+    const int tab = a.tab;
+    if (tab == TAB_RHS_ONLY) {
+        f32x2 o[D][TP];
+        sn2_rhs<D, H, NB, G, BR, TP, THREADS, UNI>(sm, y, prev1, colcur, colprev, o);
+        { f32x2* t = colcur; colcur = colprev; colprev = t; }
+#pragma unroll
+        for (int d = 0; d < D; ++d)
+#pragma unroll
+            for (int p = 0; p < TP; ++p) y[d][p] = o[d][p];
+    } else {
+        const int nst = tab == FETODE_TABLEAU_EULER ? 1 : (tab == FETODE_TABLEAU_MIDPOINT ? 2 : 4);
+        constexpr int NC = D + SF;
+        const f32x2 dt2 = pk2(a.dt, a.dt), hdt2 = pk2(a.hdt, a.hdt), dt62 = pk2(a.dt6, a.dt6);
+        [[maybe_unused]] const f32x2 third = pk2(1.0f / 3.0f, 1.0f / 3.0f), mthird = pk2(-1.0f / 3.0f, -1.0f / 3.0f);
+        [[maybe_unused]] const f32x2 mone = pk2(-1.0f, -1.0f), three = pk2(3.0f, 3.0f);
+        [[maybe_unused]] const f32x2 dt8 = pk2(a.dt * 0.125f, a.dt * 0.125f);
+        const f32x2 one = pk2(1.0f, 1.0f), two = pk2(2.0f, 2.0f);
+#pragma unroll 1
+        for (int step = 0; step < a.n_steps; ++step) {
+            if (a.ckpt) {
+#pragma unroll
+                for (int p = 0; p < TP; ++p) {
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        if (!live[2 * p + q]) continue;
+                        float* c = a.ckpt + ((size_t)step * NC) * a.B + (base + (long long)(2 * p + q) * THREADS);
+#pragma unroll
+                        for (int d = 0; d < D; ++d) {
+                            float lo, hi;
+                            upk2(y[d][p], lo, hi);
+                            c[(size_t)d * a.B] = q ? hi : lo;
+                        }
+                        if constexpr (FERRO) {
+#pragma unroll
+                            for (int d = 0; d < D; ++d) {
+                                float lo, hi;
+                                upk2(prev1[d][p], lo, hi);
+                                c[(size_t)(D + d) * a.B] = q ? hi : lo;
+                            }
+#pragma unroll 1
+                            for (int h = 0; h < H; ++h) {
+                                float lo, hi;
+                                upk2(colprev[(h * TP + p) * THREADS], lo, hi);
+                                c[(size_t)(2 * D + h) * a.B] = q ? hi : lo;
+                            }
+                        }
+                    }
+                }
+            }
+            f32x2 k1[ALT ? D : 1][TP], k2[ALT ? D : 1][TP], acc[D][TP], ys[D][TP], kn[D][TP];
+#pragma unroll
+            for (int d = 0; d < D; ++d)
+#pragma unroll
+                for (int p = 0; p < TP; ++p) {
+                    if constexpr (ALT) k1[d][p] = k2[d][p] = pk2(0.f, 0.f);
+                    acc[d][p] = pk2(0.f, 0.f);
+                    ys[d][p] = y[d][p];
+                }
+#pragma unroll 1
+            for (int s = 0; s < nst; ++s) {
+                sn2_rhs<D, H, NB, G, BR, TP, THREADS, UNI>(sm, ys, prev1, colcur, colprev, kn);
+                { f32x2* t = colcur; colcur = colprev; colprev = t; }
+                if (!ALT && tab == FETODE_TABLEAU_RK4) {
+                    // (k1 + 2 k2 + 2 k3 + k4), stage inputs h + c k_prev   train_ecg_kan_fet_nn_ode.py:698-703
+                    const f32x2 c = (s == 2) ? dt2 : hdt2;
+                    const f32x2 w = (s == 0 || s == 3) ? one : two;
+#pragma unroll
+                    for (int d = 0; d < D; ++d)
+#pragma unroll
+                        for (int p = 0; p < TP; ++p) {
+                            acc[d][p] = (s == 0) ? kn[d][p] : fma2(w, kn[d][p], acc[d][p]);
+                            ys[d][p] = fma2(c, kn[d][p], y[d][p]);
+                        }
+                } else if constexpr (ALT) {
+                    // torchdiffeq rk4_alt_step_func (3/8 rule); acc carries k3 after stage 2
+#pragma unroll
+                    for (int d = 0; d < D; ++d)
+#pragma unroll
+                        for (int p = 0; p < TP; ++p) {
+                            const f32x2 k = kn[d][p];
+                            if (s == 0) { k1[d][p] = k; ys[d][p] = add2(y[d][p], mul2(mul2(dt2, k), third)); }
+                            else if (s == 1) { k2[d][p] = k; ys[d][p] = add2(y[d][p], mul2(dt2, fma2(k1[d][p], mthird, k))); }
+                            else if (s == 2) { acc[d][p] = k; ys[d][p] = add2(y[d][p], mul2(dt2, add2(fma2(k2[d][p], mone, k1[d][p]), k))); }
+                            else acc[d][p] = mul2(add2(add2(k1[d][p], mul2(three, add2(k2[d][p], acc[d][p]))), k), dt8);
+                        }
+                } else {
+                    // euler: h + dt f(h) :676 ; midpoint: k2 = f(h + 0.5 dt k1), h + dt k2 :686-689
+#pragma unroll
+                    for (int d = 0; d < D; ++d)
+#pragma unroll
+                        for (int p = 0; p < TP; ++p) { ys[d][p] = fma2(hdt2, kn[d][p], y[d][p]); acc[d][p] = kn[d][p]; }
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < D; ++d)
+#pragma unroll
+                for (int p = 0; p < TP; ++p) {
+                    if constexpr (ALT) y[d][p] = add2(y[d][p], acc[d][p]);
+                    else if (tab == FETODE_TABLEAU_RK4) y[d][p] = fma2(dt62, acc[d][p], y[d][p]);
+                    else y[d][p] = fma2(dt2, acc[d][p], y[d][p]);
+                }
+            if (a.traj && (step + 1) % a.dump_every == 0) {
+                float* t = a.traj + (size_t)((step + 1) / a.dump_every - 1) * a.B * D;
+#pragma unroll
+                for (int p = 0; p < TP; ++p)
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        float lo, hi;
+                        upk2(y[d][p], lo, hi);
+                        if (live[2 * p]) t[(base + (long long)(2 * p) * THREADS) * D + d] = lo;
+                        if (live[2 * p + 1]) t[(base + (long long)(2 * p + 1) * THREADS) * D + d] = hi;
+                    }
+            }
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < TP; ++p) {
+        const long long b0 = base + (long long)(2 * p) * THREADS, b1 = b0 + THREADS;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            float lo, hi;
+            upk2(y[d][p], lo, hi);
+            if (live[2 * p]) a.y_out[b0 * D + d] = lo;
+            if (live[2 * p + 1]) a.y_out[b1 * D + d] = hi;
+        }
+        if constexpr (FERRO) {
+            if (a.state) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    float lo, hi;
+                    upk2(prev1[d][p], lo, hi);
+                    if (live[2 * p]) a.state[b0 * SF + d] = lo;
+                    if (live[2 * p + 1]) a.state[b1 * SF + d] = hi;
+                }
+#pragma unroll 1
+                for (int h = 0; h < H; ++h) {
+                    float lo, hi;
+                    upk2(colprev[(h * TP + p) * THREADS], lo, hi);
+                    if (live[2 * p]) a.state[b0 * SF + D + h] = lo;
+                    if (live[2 * p + 1]) a.state[b1 * SF + D + h] = hi;
+                }
+            }
+        }
+    }
+}
+
+template <int D, int H, int NB, int G, int BR, int TP, int THREADS, int MINB, bool ALT>
+__global__ void __launch_bounds__(THREADS, MINB) smallnet_rk2_kernel(const SNArgs a, const float* __restrict__ img2) {
+    extern __shared__ float4 sn2_smem4[];
+    float* sm = reinterpret_cast<float*>(sn2_smem4);
+    constexpr SN2Layout L = sn2_layout(D, H, NB, G);
+    for (int i = threadIdx.x; i < L.total / 4; i += THREADS) sn2_smem4[i] = reinterpret_cast<const float4*>(img2)[i];
+    __syncthreads();
+    // the constructor's grids are near-uniform: arithmetic interval guess + one correction, no search loop; adapted
+    // (update_grid) knots take the general body.  One block-uniform branch per launch.
+    if (sm[L.hdr + 4] != 0.f) sn2_body<D, H, NB, G, BR, TP, THREADS, ALT, true>(a, sm);
+    else sn2_body<D, H, NB, G, BR, TP, THREADS, ALT, false>(a, sm);
+}
+
+// ------------------------------------------------------------------------------------------
+// host
+// ------------------------------------------------------------------------------------------
+int64_t sn2_image_floats(const fetode_smallnet_t* net) {
+    if (!sn2_has(net)) return 0;
+    return sn2_layout(2, 10, 10, 5).total;
+}
+
+int sn2_pack(const fetode_smallnet_t* net, const fetode_kanlayer_t* layers, float* img2, cudaStream_t st) {
+    if (!sn2_has(net)) return FETODE_OK;
+    const SN2Layout L = sn2_layout(2, 10, 10, 5);
+    sn2_pack_kernel<<<1, 128, 0, st>>>(layers[0], layers[1], L, img2);
+    return FETODE_LAUNCH_RC();
+}
+
+template <int BR, int TP, int THREADS, int MINB, bool ALT>
+static int sn2_launch_k(const SNArgs& a, const float* img2, cudaStream_t st) {
+    constexpr int D = 2, H = 10, NB = 10, G = 5;
+    constexpr SN2Layout L = sn2_layout(D, H, NB, G);
+    const size_t smem = (size_t)L.total * 4 + (size_t)2 * H * TP * THREADS * 8;
+    const long long per_cta = (long long)THREADS * 2 * TP;
+    const unsigned grid = (unsigned)((a.B + per_cta - 1) / per_cta);
+    auto kern = smallnet_rk2_kernel<D, H, NB, G, BR, TP, THREADS, MINB, ALT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<grid, THREADS, smem, st>>>(a, img2);
+    return FETODE_LAUNCH_RC();
+}
+
+// Launch shape (measured on B200, profiles/r2_sn_sweep.jsonl).  The kernel is latency-bound (shared-memory operand loads
+// and MUFU chains), so resident warps matter more than spill-freedom: two trajectories per lane, 64 registers, four
+// 256-thread CTAs per SM (32 warps; shared memory = 4 x (15 KB image + 40 KB columns)) is the fastest shape from
+// ~10^5 rows up (2.6e9 traj-steps/s at 2^20 rows; 128 registers / 16 warps: 2.2e9; four trajectories per lane at
+// 168 registers / 12 warps: 2.4e9).  Small batches take 64-thread CTAs so that every SM gets work.
+// FETODE_SN2_SHAPE=12564|164 overrides (experiments only; read once).
+static int sn2_shape(long long B) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("FETODE_SN2_SHAPE");
+        forced = e ? atoi(e) : 0;
+    }
+    if (forced > 0) return forced;
+    return B >= 98304 ? 12564 : 164;
+}
+
+template <int BR>
+static int sn2_launch_b(const SNArgs& a, const float* img2, cudaStream_t st) {
+    const int shape = sn2_shape(a.B);
+    if (a.tab == FETODE_TABLEAU_RK4_38)
+        return shape == 164 ? sn2_launch_k<BR, 1, 64, 8, true>(a, img2, st) : sn2_launch_k<BR, 1, 256, 4, true>(a, img2, st);
+    return shape == 164 ? sn2_launch_k<BR, 1, 64, 8, false>(a, img2, st) : sn2_launch_k<BR, 1, 256, 4, false>(a, img2, st);
+}
+
+int sn2_launch(const fetode_smallnet_t* net, const SNArgs& a, const float* img2, cudaStream_t st) {
+    if (net->branch == FETODE_BRANCH_FERRO2D) return sn2_launch_b<FETODE_BRANCH_FERRO2D>(a, img2, st);
+    return sn2_launch_b<FETODE_BRANCH_LOGISTIC>(a, img2, st);
+}
+
+}  // namespace fetode

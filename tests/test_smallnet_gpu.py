@@ -123,3 +123,43 @@ def test_long_horizon_properties_full_size(cuda):
     assert torch.equal(full, big)
     assert torch.equal(st2, st)
     assert torch.isfinite(big).all()
+
+
+@pytest.mark.parametrize("branch", ["logistic", "ferro2d"])
+def test_rhs_on_adapted_non_uniform_grid(cuda, branch):
+    """update_grid (efficientkan.py:184-221) leaves per-feature NON-uniform knots: the fused kernel's interval search
+    and its per-interval cubic tables must follow the stored knots, not a closed-form spacing."""
+    layers, m = fetode_kan_random([2, 10, 2], branch, seed=17, device=cuda)
+    gen = torch.Generator().manual_seed(3)
+    for li, lay in enumerate(layers):
+        g = lay["grid"]
+        step = (torch.rand(g.shape, generator=gen) * 0.9 + 0.1) * 0.4            # spacings in [0.04, 0.4]
+        newg = (torch.cumsum(step, dim=1) - 2.3).float().contiguous()
+        lay["grid"] = newg
+        m.layers[li].grid.copy_(newg.to(cuda))
+        torch.autograd.graph.increment_version(m.layers[li].base_weight)          # repack
+    f, _ = _oracle_rhs(layers, branch)
+    x = torch.rand(777, 2, generator=gen) * 5.0 - 2.5
+    x[:12] = layers[0]["grid"][0, :12, None].expand(12, 2)                        # knot-exact inputs
+    with torch.no_grad():
+        for call in range(2):
+            xi = x + 0.05 * call
+            assert max_rel(m(xi.to(cuda)), f(None, xi)) < RHS_TOL, (branch, call)
+
+
+def test_benchmark_horizon_1000_steps_vs_oracle(cuda):
+    """BASELINE configs[1] horizon: 1000 classic-RK4 steps, dt = 0.014 -- trajectories within 1e-4 (max-norm relative)
+    of the fp32 oracle (the reference's arithmetic) for 256 rows, every dumped sample, and all states finite."""
+    layers, m = fetode_kan_random([2, 10, 2], "ferro2d", seed=8, device=cuda)
+    f, _ = _oracle_rhs(layers, "ferro2d")
+    x0 = lv_inputs(256, 1)
+    n, dt = 1000, 0.014
+    with torch.no_grad():
+        want = OS.rk4_classic(f, x0, 0.0, n * dt, n, trajectory=True)
+        t = torch.arange(n + 1, dtype=torch.float64) * dt
+        got = fetode.odeint(lambda tt, X: m(X), x0.to(cuda), t, method="rk4_classic")
+    assert torch.isfinite(got).all()
+    err_T = max_rel(got[-1], want[-1])
+    err_all = max_rel(got, want)
+    print(f"1000-step horizon: final-state rel err {err_T:.3e}, whole-trajectory rel err {err_all:.3e}")
+    assert err_T < TRAJ_TOL and err_all < TRAJ_TOL
