@@ -104,7 +104,8 @@ def norm_sync(pair: torch.Tensor) -> None:
 
 
 def hardgate_prev_sync(module) -> None:
-    """Make every rank's hard-gate state the last row of the GLOBAL batch (= the last rank's last row)."""
+    """Make every rank's hard-gate state the last row of the GLOBAL batch (= the last rank's last row), once, for
+    every hard-gated basis under ``module``.  (The per-call form is ``enable_hardgate_sync``.)"""
     rank, w = world()
     if w == 1:
         return
@@ -112,6 +113,36 @@ def hardgate_prev_sync(module) -> None:
         row = getattr(m, "_row", None)
         if row is not None and hasattr(m, "branch_breaking_point"):
             dist.broadcast(row, src=w - 1)
+
+
+def enable_hardgate_sync(module, on: bool = True) -> int:
+    """Option 2 of SURVEY section 8e: after EVERY call of a hard-gated ``ecg.LogisticBasis`` under ``module`` the new
+    ``prev_x`` row ([in_dim] floats) is broadcast from the last rank, so each rank gates its next call on the last
+    row of the GLOBAL batch exactly like the single-process reference (train_ecg_kan_fet_nn_ode.py:129-132).  The
+    broadcast is issued on the current stream (capturable).  Returns the number of modules switched."""
+    n = 0
+    for m in module.modules():
+        if hasattr(m, "branch_breaking_point") and hasattr(m, "_dist_sync"):
+            m._dist_sync = bool(on)
+            n += 1
+    return n
+
+
+def shard_rows_with_sentinel(x: torch.Tensor, rank: Optional[int] = None,
+                             world_size: Optional[int] = None) -> Tuple[torch.Tensor, int]:
+    """Option 1 of SURVEY section 8e (zero communication): this rank's contiguous rows of the global batch ``x``
+    followed -- on every rank but the last -- by the GLOBAL last row.  Rows never interact except through the
+    hard-gated basis, whose state is the last row of whatever batch it sees: with the sentinel appended that is the
+    global last row on every rank, so every rank computes the reference's function on its rows.  Returns
+    (rows [n_real (+1), ...], n_real); the caller drops output row n_real before the loss."""
+    r, w = world()
+    rank = r if rank is None else rank
+    world_size = w if world_size is None else world_size
+    lo, hi = shard_bounds(x.shape[0], rank, world_size)
+    rows = x[lo:hi]
+    if world_size > 1 and hi != x.shape[0]:
+        rows = torch.cat([rows, x[-1:]], dim=0)
+    return rows, hi - lo
 
 
 def clip_grad_norm_(params, max_norm: float) -> torch.Tensor:

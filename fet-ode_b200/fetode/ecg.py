@@ -41,6 +41,7 @@ class LogisticBasis(nn.Module):
         self.register_buffer("prev_x", torch.zeros(1, in_dim, num_basis))
         self.register_buffer("branch_state", torch.ones(1, in_dim, num_basis))
         self._row = None                                                   # compact [in_dim] previous last row
+        self._dist_sync = False                                            # fetode.dist.enable_hardgate_sync
 
     def reset_state(self, value: float = 0.0):
         self._row = None
@@ -87,6 +88,12 @@ class LogisticBasis(nn.Module):
                 out = torch.sigmoid(out)
             if int(apply_sigmoid) == 2:
                 out = torch.nan_to_num(out, nan=0.0, posinf=1e3, neginf=-1e3)
+        if self._dist_sync:
+            # batch-sharded run: the reference's prev_x is the last row of the GLOBAL batch (:131-132) = the last
+            # rank's last row
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                dist.broadcast(new_row, src=dist.get_world_size() - 1)
         self._row = new_row
         self.prev_x = new_row.view(1, -1, 1).expand(1, self.in_dim, self.num_basis)
         self.branch_state = side["gate"]                                   # uint8 [B,in,K]: 1 = up branch

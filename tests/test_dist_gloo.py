@@ -71,3 +71,34 @@ def test_shard_bounds_cover_everything():
             assert b[0][0] == 0 and b[-1][1] == n
             assert all(b[i][1] == b[i + 1][0] for i in range(w - 1))
             assert max(hi - lo for lo, hi in b) - min(hi - lo for lo, hi in b) <= 1
+
+
+def _sync_worker(rank, world, port, out_dir):
+    for p in (ROOT, os.path.join(ROOT, "fet-ode_b200")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from fetode import dist as fd
+    from fetode import ecg
+    # a hard-gated basis whose state row differs per rank: after the sync every rank holds the LAST rank's row
+    m = torch.nn.Sequential(ecg.LogisticBasis(5, 3))
+    m[0]._row = torch.full((5,), float(rank + 1))
+    fd.hardgate_prev_sync(m)
+    assert fd.enable_hardgate_sync(m) == 1 and m[0]._dist_sync
+    x = torch.arange(7 * 2, dtype=torch.float32).reshape(7, 2)
+    rows, n = fd.shard_rows_with_sentinel(x)
+    torch.save({"row": m[0]._row.clone(), "rows": rows.clone(), "n": n}, os.path.join(out_dir, f"s{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_hardgate_row_sync_and_sentinel_rows(tmp_path):
+    world = 2
+    mp.spawn(_sync_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    res = [torch.load(os.path.join(tmp_path, f"s{r}.pt")) for r in range(world)]
+    x = torch.arange(7 * 2, dtype=torch.float32).reshape(7, 2)
+    for r in range(world):
+        assert torch.equal(res[r]["row"], torch.full((5,), float(world)))        # the last rank's row everywhere
+    assert res[0]["n"] == 4 and res[1]["n"] == 3
+    assert torch.equal(res[0]["rows"], torch.cat([x[:4], x[-1:]]))                # rank 0: its rows + the global last row
+    assert torch.equal(res[1]["rows"], x[4:])                                     # the last rank already ends on it
