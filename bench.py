@@ -1,19 +1,27 @@
 #!/usr/bin/env python
-"""bench.py -- headline benchmark: Lotka-Volterra KAN-FET NODE inference ensemble.
+"""bench.py -- headline benchmark: Lotka-Volterra KAN-FET NODE inference ensemble (BASELINE.json configs[1]) plus the
+fwd+bwd training steps of configs[0] and configs[2] in the same JSON line.
 
-Workload (BASELINE.json configs[1]): KANFET([2,10,2], grid 5) right-hand side, classic RK4,
-2^20 synthetic initial conditions x 1000 steps (dt = 0.014) PER GPU (weak scaling: every rank
-integrates its own shard, no data-path collective).  One "step" of this script = one pass of the
-hot path over one batch = one launch of the fused kernel = 2^20 x 1000 trajectory-steps.
+Primary workload: KANFET([2,10,2], grid 5) right-hand side, classic RK4, 2^20 synthetic initial conditions x 1000 steps
+(dt = 0.014) IN TOTAL, batch-sharded over the N ranks (131 072 rows per GPU at N = 8; STRONG scaling, as the config
+states it; no data-path collective).  One "step" of this script = one pass of the hot path over the batch = one launch
+of the fused kernel per rank = 2^20 x 1000 trajectory-steps in total.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-train]
     torchrun ... bench.py --gpus N ...      (one rank per GPU)
 
-Prints ONE JSON line (rank 0).  `value` is device-timed with inputs resident in HBM; `e2e` is the same
-metric through the public API (fetode.integrate_rk4) with the initial conditions copied from pinned
-host memory and the final states copied back inside the timed region.
-`--impl reference` times the CPU oracle (the reference's PyTorch arithmetic restated in oracle/,
-bit-identical to the live reference) on the host cores on a bounded sample of the same workload.
+Prints ONE JSON line (rank 0).
+  value      device-timed, inputs resident in HBM (CUDA events around each launch, max over ranks)
+  e2e        the same metric through the public API (fetode.integrate_rk4) with the initial conditions copied from pinned
+             host memory and the final states copied back inside the timed region
+  weak       (N > 1) the same kernel with 2^20 rows PER GPU -- the round-1 figure, kept as a secondary key
+  fwd_bwd    BASELINE's "fwd+bwd step ms": LV training (config 1: 34 classic-RK4 steps, MSE, Adam; B = 1 as the script runs
+             it and B = 65 536 per GPU) and ECG training (config 3: B = 4096 per GPU, RK4 x 8, cross-entropy, clip 1.0,
+             AdamW), whole step replayed from a CUDA graph, the flat-gradient NCCL all-reduce inside the step at N > 1
+             (allreduce_ms = the collective alone), each with its roofline fraction and, at N = 1, its CPU leg
+  roofline   dominant kernel of the primary workload against the FP32 CUDA-core peak measured live (FFMA probe)
+  cpu_baseline (N = 1) the oracle port of the reference's PyTorch arithmetic on all host cores, bounded sample
+`--impl reference` times that CPU port alone (rank 0), same metric / config, 65 536 trajectories x 10 steps per step.
 """
 from __future__ import annotations
 
@@ -35,10 +43,13 @@ import torch  # noqa: E402
 WIDTHS = [2, 10, 2]
 RK_STEPS = 1000
 DT = 0.014
-TRAJ_PER_GPU = 1 << 20
+TRAJ_TOTAL = 1 << 20
 FLOP_PER_TRAJ_STEP = 22712          # KANFET([2,10,2]) ferro branch, classic RK4
+ECG_FLOP_PER_ROW_RHS = 4.49e6       # ECG right-hand side, logistic branch nb = 10
 METRIC = "lv_kanfet_node_traj_steps_per_s"
 UNIT = "traj-steps/s"
+WORKLOAD = "LV KANFET([2,10,2]) inference ensemble, 2^20 initial conditions x 1000 classic-RK4 steps, dt=0.014 (BASELINE configs[1])"
+CPU_SAMPLE = (65536, 10)            # the CPU slice of config 2
 
 
 def _dist_env():
@@ -55,11 +66,17 @@ def make_model(seed=0):
     return fetode.KANFET(layers_hidden=WIDTHS, grid_size=5)
 
 
-def oracle_layers(model):
+def oracle_layers(model, grad=False):
     sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()
           if not k.endswith("prev_x") and not k.endswith("branch_sign")}
-    return [{k[len(f"layers.{i}."):]: v for k, v in sd.items() if k.startswith(f"layers.{i}.")}
-            for i in range(len(WIDTHS) - 1)]
+    out = [{k[len(f"layers.{i}."):]: v for k, v in sd.items() if k.startswith(f"layers.{i}.")}
+           for i in range(len(WIDTHS) - 1)]
+    if grad:
+        for lay in out:
+            for k, v in lay.items():
+                if not k.endswith("grid"):
+                    v.requires_grad_(True)
+    return out
 
 
 def synth_x0(n, seed):
@@ -68,7 +85,7 @@ def synth_x0(n, seed):
 
 
 # ------------------------------------------------------------------------------------------
-# CPU leg (oracle port of the reference's PyTorch path)
+# CPU legs (oracle port of the reference's PyTorch path; test infrastructure used as the reported baseline)
 # ------------------------------------------------------------------------------------------
 def cpu_reference_run(layers, n_traj, n_steps, seed=0):
     """Seconds to integrate n_traj trajectories for n_steps classic-RK4 steps on the host cores."""
@@ -83,13 +100,40 @@ def cpu_reference_run(layers, n_traj, n_steps, seed=0):
         return time.perf_counter() - t0
 
 
-def cpu_sample_size(layers, budget_s):
-    """Pick (n_traj, n_steps) so one sample costs about budget_s seconds on this host."""
-    n_traj = 16384
-    t = cpu_reference_run(layers, n_traj, 1)            # also the warm-up
-    t = min(t, cpu_reference_run(layers, n_traj, 1))
-    n_steps = max(1, min(50, int(budget_s / max(t, 1e-4))))
-    return n_traj, n_steps
+def cpu_lv_train_ms(model, B, iters=2):
+    """fwd+bwd of one LV training iteration (34 classic-RK4 steps, MSE) on the host cores, B rows."""
+    from oracle import models as OM
+    lay = oracle_layers(model, grad=True)
+    params = [v for l in lay for v in l.values() if v.requires_grad]
+    gen = torch.Generator().manual_seed(1)
+    x0 = synth_x0(B, 1) if B > 1 else torch.ones(1, 2)
+    target = torch.randn(35, B, 2, generator=gen)
+
+    def step():
+        for p in params:
+            p.grad = None
+        OM.lv_train_loss(lay, x0, target, 3.5, 34).backward()
+    step()
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        step()
+    return 1e3 * (time.perf_counter() - t0) / iters
+
+
+def cpu_ecg_train_ms(model, B):
+    """fwd+bwd of one ECG training step (RK4 x 8, cross-entropy) on the host cores, B rows (bounded sample)."""
+    import torch.nn.functional as F
+
+    from oracle import models as OM
+    P = OM.ecg_params(model.state_dict(), torch.float32, requires_grad=True)
+    st = OM.EcgStates(P)
+    gen = torch.Generator().manual_seed(1)
+    x = torch.randn(B, 96, generator=gen)
+    x = (x - x.mean(1, keepdim=True)) / x.std(1, keepdim=True)
+    y = torch.randint(0, 2, (B,), generator=gen)
+    t0 = time.perf_counter()
+    F.cross_entropy(OM.kanfet_mlp_node_forward(x, P, st), y).backward()
+    return 1e3 * (time.perf_counter() - t0)
 
 
 def run_reference(args):
@@ -99,9 +143,7 @@ def run_reference(args):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     layers = oracle_layers(make_model())
-    total_budget = 100.0
-    per_step = total_budget / max(1, args.steps + args.warmup)
-    n_traj, n_steps = cpu_sample_size(layers, min(per_step, 20.0))
+    n_traj, n_steps = CPU_SAMPLE
     for _ in range(args.warmup):
         cpu_reference_run(layers, n_traj, n_steps)
     secs = [cpu_reference_run(layers, n_traj, n_steps, seed=i) for i in range(args.steps)]
@@ -111,9 +153,8 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "LV KANFET([2,10,2]) inference ensemble, classic RK4, dt=0.014 (BASELINE configs[1])",
-                   "sample": sample},
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -164,149 +205,371 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # GPU leg
 # ------------------------------------------------------------------------------------------
-def run_ours(args):
-    import torch.distributed as dist
+class Ctx:
+    """Rank / device / timing helpers shared by the sections of the GPU arm."""
 
-    import fetode
-    from fetode._lib import TABLEAU, lib
-
-    rank, world, local = _dist_env()
-    # libraries (NCCL's version banner) write to fd 1; keep stdout clean for the one JSON line
-    sys.stdout.flush()
-    saved_stdout = os.dup(1)
-    os.dup2(2, 1)
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
+    def __init__(self, args):
+        import torch.distributed as dist
+        self.dist = dist
+        self.rank, self.world, self.local = _dist_env()
+        if self.world != args.gpus and self.world == 1 and args.gpus > 1:
             raise SystemExit("launch with torchrun --nproc-per-node N for --gpus N > 1")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)     # > 126 MB L2
 
-    model = make_model().to(dev)
-    plan = model.small_plan()
-    assert plan is not None, "fused small-net kernel unavailable"
-    B = args.traj_per_gpu
-    n_rk = args.rk_steps
-    x0_host = synth_x0(B, seed=1000 + rank).pin_memory()
-    x0 = x0_host.to(dev)
-    y = torch.empty_like(x0)
-    state = torch.empty(B, plan.state_floats, device=dev)
-    out_host = torch.empty(B, 2).pin_memory()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
-    tab = TABLEAU["rk4_classic"]
-    plan.image()                                                       # pack once (weights are static)
-
-    def kernel_step():
-        plan.rk_fwd(tab, x0, DT, n_rk, state=state, state_is_zero=True, y_out=y)
-
-    func = fetode.as_rhs(model)
-
-    def e2e_step():
-        model.reset_state()
-        xd = x0_host.to(dev, non_blocking=True)
-        yT = fetode.integrate_rk4(func, xd, 0.0, n_rk * DT, n_rk)
-        out_host.copy_(yT, non_blocking=True)
-
-    def barrier():
+    def barrier(self):
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        if self.world > 1:
+            self.dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(step_fn, k, w):
-        with torch.no_grad():
+    def max_over_ranks(self, v: float) -> float:
+        if self.world == 1:
+            return v
+        t = torch.tensor([v], device=self.dev, dtype=torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(self, step_fn, k, w, flush=True, grad=False):
+        """W warm-up calls, then K calls each bracketed by CUDA events on the launching stream (L2 flushed before each
+        when flush); barrier + synchronize on both sides; returns total ms of the K calls, max over ranks."""
+        with torch.set_grad_enabled(grad):
             for _ in range(w):
                 step_fn()
-            barrier()
+            self.barrier()
             evs = []
-            t_wall0 = time.perf_counter()
             for _ in range(k):
-                flush.zero_()                                            # evict L2 between timed iterations
+                if flush:
+                    self.flush.zero_()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 step_fn()
                 e1.record()
                 evs.append((e0, e1))
-            barrier()
-            wall = time.perf_counter() - t_wall0
-        ms = sum(a.elapsed_time(b) for a, b in evs)
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, wall
+            self.barrier()
+        return self.max_over_ranks(sum(a.elapsed_time(b) for a, b in evs))
 
-    with ClockSampler(local) as clk:
-        ms_kernel, _ = timed(kernel_step, args.steps, args.warmup)
-    ms_e2e, _ = timed(e2e_step, args.steps, max(1, min(args.warmup, 2)))
 
-    units_per_step = B * n_rk * world
+def measure_peaks(ctx):
+    """FP32 CUDA-core peak (live FFMA probe in libfetode) and dense TF32 tensor peak (cuBLAS through torch.matmul,
+    the way MEASURED_PEAKS.json measured bf16) -- the two denominators MEASURED_PEAKS.json does not hold."""
+    import ctypes as C
+
+    from fetode._lib import lib
+    tf = C.c_double(0.0)
+    rc = lib().fetode_probe_fp32_peak(C.byref(tf), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    fp32 = tf.value if rc == 0 and tf.value > 0 else None
+    tf32 = None
+    try:
+        old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = True
+        n = 8192
+        a = torch.randn(n, n, device=ctx.dev)
+        b = torch.randn(n, n, device=ctx.dev)
+        for _ in range(2):
+            a @ b
+        best = 0.0
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            best = max(best, 2.0 * n ** 3 / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+        tf32 = best
+        torch.backends.cuda.matmul.allow_tf32 = old
+        del a, b
+    except Exception:
+        pass
+    return fp32, tf32
+
+
+def lv_train_section(ctx, B, fp32_peak, with_cpu):
+    """Config 1: LV KANFET([2,10,2]) NODE training iteration (train_kanfet_node_predprey.py:246-257), classic RK4 x 34,
+    MSE over all samples, Adam lr 2e-3, B rows per GPU; whole step replayed from a CUDA graph."""
+    import fetode
+    from fetode import dist as fdist
+    model = make_model().to(ctx.dev)
+    n, T = 34, 3.5
+    t = torch.linspace(0, T, n + 1, dtype=torch.float64)
+    gen = torch.Generator().manual_seed(100 + ctx.rank)
+    x0 = (torch.rand(B, 2, generator=gen) * 6.75 + 0.25) if B > 1 else torch.ones(1, 2)
+    x0d = x0.to(ctx.dev)
+    tgt = torch.randn(n + 1, B, 2, generator=gen).to(ctx.dev)
+    func = fetode.as_rhs(model)
+
+    def gfwd(m, x):
+        m.reset_state()
+        return fetode.odeint(func, x, t, method="rk4_classic")
+    mse = lambda pred, y: ((pred - y) ** 2).mean()
+    eopt = fetode.optim.Adam(model.parameters(), lr=2e-3)
+
+    def eager():
+        eopt.zero_grad()
+        mse(gfwd(model, x0d), tgt).backward()
+        if ctx.world > 1:
+            fdist.allreduce_gradients(eopt)
+        eopt.step()
+    k = 5
+    eager_ms = ctx.timed(eager, k, 3, flush=False, grad=True) / k
+    gopt = fetode.optim.Adam(model.parameters(), lr=2e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, mse, x0d, tgt, warmup=2, forward=gfwd, allreduce=ctx.world > 1)
+    k = 10
+    ms = ctx.timed(lambda: gstep(gstep.x, gstep.y), k, 3, flush=False, grad=True) / k
+    ar_ms = None
+    if ctx.world > 1:
+        ar_ms = ctx.timed(lambda: ctx.dist.all_reduce(gopt.flat_grad), 20, 5, flush=False) / 20
+    loss = float(gstep.loss)
+    units = B * n * ctx.world
+    ach = 3.0 * FLOP_PER_TRAJ_STEP * B * n / (ms * 1e-3) / 1e12
+    out = {"workload": f"config 1: LV KANFET([2,10,2]) NODE training, classic RK4 x {n}, MSE, fused Adam "
+                       "(train_kanfet_node_predprey.py:246-257)",
+           "rows_per_gpu": B, "ms_per_step": ms, "eager_ms_per_step": eager_ms, "graph_replayed": True,
+           "traj_steps_per_s": units / (ms * 1e-3), "loss_finite": loss == loss,
+           "allreduce_ms": ar_ms, "allreduce_bytes": int(gopt.flat_grad.numel()) * 4 if ctx.world > 1 else 0,
+           "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
+                        "frac": ach / fp32_peak if fp32_peak else None,
+                        "flop_per_traj_step": 3 * FLOP_PER_TRAJ_STEP, "convention": "fwd+bwd = 3 x the SURVEY 8(d) forward count"}}
+    if with_cpu:
+        Bc = min(B, 2048)
+        cms = cpu_lv_train_ms(make_model(), Bc)                          # same seed: the same weights on the host
+        out["cpu"] = {"ms_per_step": cms, "rows": Bc, "traj_steps_per_s": Bc * n / (cms * 1e-3), "cores": os.cpu_count(),
+                      "kind": "port", "sample": f"fwd+bwd of {Bc} rows x {n} classic-RK4 steps (oracle port, torch autograd)"}
+    del gstep, gopt
+    return out
+
+
+def ecg_train_section(ctx, B, tf32_peak, with_cpu):
+    """Config 3: KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128) training step (train_ecg_kan_fet_nn_ode.py:1100-1112),
+    classic RK4 x 8, cross-entropy, clip_grad_norm_(1.0), AdamW; B rows per GPU.  At N > 1 every rank but the last
+    appends the GLOBAL last row (sentinel) so the hard gate sees the reference's prev_x (:129-132) without communication."""
+    import torch.nn.functional as F
+
+    import fetode
+    from fetode import ecg
+    torch.manual_seed(0)
+    model = ecg.KanFet_MLP_NODE(T=96, num_classes=2, latent_dim=64, num_basis=12, ode_hidden=128, dropout=0.0)
+    model.ode_method = "rk4_classic"
+    cpu_sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    model = model.to(ctx.dev)
+
+    def rows_of(rank):
+        gen = torch.Generator().manual_seed(200 + rank)
+        x = torch.randn(B, 96, generator=gen)
+        x = (x - x.mean(1, keepdim=True)) / x.std(1, keepdim=True)               # per-row z-score :44
+        return x, torch.randint(0, 2, (B,), generator=gen)
+    x, y = rows_of(ctx.rank)
+    sentinel = ctx.world > 1 and ctx.rank != ctx.world - 1
+    if sentinel:
+        x = torch.cat([x, rows_of(ctx.world - 1)[0][-1:]], dim=0)
+    x, y = x.to(ctx.dev), y.to(ctx.dev)
+    fwd = (lambda m, inp: m(inp)[:B]) if sentinel else (lambda m, inp: m(inp))
+    gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, max_norm=1.0, warmup=2, forward=fwd,
+                                           allreduce=ctx.world > 1)
+    k = 5
+    ms = ctx.timed(lambda: gstep(gstep.x, gstep.y), k, 2, flush=False, grad=True) / k
+    ar_ms = None
+    if ctx.world > 1:
+        ar_ms = ctx.timed(lambda: ctx.dist.all_reduce(gopt.flat_grad), 20, 5, flush=False) / 20
+    loss = float(gstep.loss)
+    n_rk = 8
+    ach = 3.0 * 4 * n_rk * ECG_FLOP_PER_ROW_RHS * B / (ms * 1e-3) / 1e12
+    peak = tf32_peak / 3.0 if tf32_peak else None
+    out = {"workload": "config 3: ECG KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128), classic RK4 x 8, CE, clip 1.0, "
+                       "fused AdamW (train_ecg_kan_fet_nn_ode.py:1100-1112)",
+           "rows_per_gpu": B, "ms_per_step": ms, "graph_replayed": True, "sample_steps_per_s": B * n_rk * ctx.world / (ms * 1e-3),
+           "loss_finite": loss == loss, "hardgate_rule": "sentinel row (global last row on every rank)" if ctx.world > 1 else "single rank",
+           "allreduce_ms": ar_ms, "allreduce_bytes": int(gopt.flat_grad.numel()) * 4 if ctx.world > 1 else 0,
+           "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+                        "frac": ach / peak if peak else None,
+                        "peak_source": "cuBLAS TF32 8192^3 through torch.matmul, measured in this run, / 3 (3xTF32 split)",
+                        "tf32_dense_tflops": tf32_peak, "flop_per_row_rhs": ECG_FLOP_PER_ROW_RHS,
+                        "convention": "useful FLOP: fwd+bwd = 3 x 32 right-hand sides x SURVEY 8(d) count"}}
+    if with_cpu:
+        Bc = 128
+        model_cpu = ecg.KanFet_MLP_NODE(T=96, num_classes=2, latent_dim=64, num_basis=12, ode_hidden=128, dropout=0.0)
+        model_cpu.load_state_dict(cpu_sd)
+        cms = cpu_ecg_train_ms(model_cpu, Bc)
+        out["cpu"] = {"ms_per_step": cms, "rows": Bc, "sample_steps_per_s": Bc * n_rk / (cms * 1e-3), "cores": os.cpu_count(),
+                      "kind": "port", "sample": f"fwd+bwd of {Bc} rows, RK4 x 8 (oracle port, torch autograd); per-row cost is flat in B"}
+    del gstep, gopt
+    return out
+
+
+def inspan_fractions(x0, yT, state, D):
+    """Share of layer inputs inside the knot span [-2.2, 2.2) (where the spline term is non-zero): layer 1 = the ODE
+    state (at t = 0 and at the horizon), layer 2 = the hidden pre-activations of the last right-hand-side call (the
+    kernel's hysteresis state holds them).  The second-generation kernel evaluates the spline cubic unconditionally
+    (masked outside the span), so the timed work no longer depends on these fractions; they say how much of the
+    SURVEY 8(d) spline FLOP count is 'live'."""
+    f = lambda t: float(((t >= -2.2) & (t < 2.2)).float().mean())
+    out = {"layer1_t0": f(x0), "layer1_horizon": f(yT)}
+    if state is not None and state.shape[1] > D:
+        out["layer2_horizon"] = f(state[:, D:])
+    return out
+
+
+def run_ours(args):
+    import fetode
+    from fetode import dist as fdist
+    from fetode._lib import TABLEAU
+
+    # libraries (NCCL's version banner) write to fd 1; keep stdout clean for the one JSON line
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    ctx = Ctx(args)
+    rank, world, dev = ctx.rank, ctx.world, ctx.dev
+
+    # ---------------- primary: config 2, 2^20 trajectories in total, sharded
+    model = make_model().to(dev)
+    plan = model.small_plan()
+    assert plan is not None, "fused small-net kernel unavailable"
+    total = args.trajectories
+    lo, hi = fdist.shard_bounds(total, rank, world)
+    B = hi - lo
+    n_rk = args.rk_steps
+    tab = TABLEAU["rk4_classic"]
+    plan.image()                                                       # pack once (weights are static)
+    func = fetode.as_rhs(model)
+
+    def make_case(x_cpu):
+        rows = x_cpu.shape[0]
+        x0_host = x_cpu.contiguous().pin_memory()
+        x0 = x0_host.to(dev)
+        y = torch.empty_like(x0)
+        state = torch.empty(rows, plan.state_floats, device=dev)
+        out_host = torch.empty(rows, 2).pin_memory()
+
+        def kernel_step():
+            plan.rk_fwd(tab, x0, DT, n_rk, state=state, state_is_zero=True, y_out=y)
+
+        def e2e_step():
+            model.reset_state()
+            xd = x0_host.to(dev, non_blocking=True)
+            yT = fetode.integrate_rk4(func, xd, 0.0, n_rk * DT, n_rk)
+            out_host.copy_(yT, non_blocking=True)
+        return kernel_step, e2e_step, x0, y, state
+
+    # every rank draws the SAME global batch and takes its slice, so the union over ranks is the N = 1 workload
+    kernel_step, e2e_step, x0, y, state = make_case(synth_x0(total, seed=1000)[lo:hi])
+
+    with ClockSampler(ctx.local) as clk:
+        ms_kernel = ctx.timed(kernel_step, args.steps, args.warmup)
+    finite = bool(torch.isfinite(y).all())
+    inspan = inspan_fractions(x0, y, state, 2)
+    ms_e2e = ctx.timed(e2e_step, args.steps, max(1, min(args.warmup, 2)))
+    units_per_step = total * n_rk
     value = units_per_step * args.steps / (ms_kernel * 1e-3)
     e2e_value = units_per_step * args.steps / (ms_e2e * 1e-3)
 
+    # ---------------- secondary: weak scaling (2^20 rows per GPU), N > 1 only
+    weak = None
+    if world > 1 and not args.no_weak:
+        del kernel_step, e2e_step, x0, y, state
+        torch.cuda.empty_cache()
+        wk, _, wx0, wy, wstate = make_case(synth_x0(TRAJ_TOTAL, seed=1000 + rank))
+        wms = ctx.timed(wk, 2, 1)
+        weak = {"value": TRAJ_TOTAL * world * n_rk * 2 / (wms * 1e-3), "unit": UNIT, "trajectories_per_gpu": TRAJ_TOTAL,
+                "ms_per_step": wms / 2, "steps": 2, "warmup": 1}
+        del wk, wx0, wy, wstate
+        torch.cuda.empty_cache()
+
+    # ---------------- peaks + the training configurations (BASELINE metric: "fwd+bwd step ms")
+    fp32_peak, tf32_peak = measure_peaks(ctx)
+    fwd_bwd = None
+    if not args.no_train:
+        with_cpu = world == 1 and not args.no_cpu
+        if with_cpu:
+            torch.set_num_threads(os.cpu_count() or 1)
+        fwd_bwd = {}
+        for name, fn, a in (("lv_train_B1", lv_train_section, (1, fp32_peak, with_cpu)),
+                            ("lv_train_B65536", lv_train_section, (65536, fp32_peak, with_cpu)),
+                            ("ecg_train_B4096", ecg_train_section, (4096, tf32_peak, with_cpu))):
+            try:
+                fwd_bwd[name] = fn(ctx, *a)
+            except Exception as e:                                   # noqa: BLE001 -- the primary number must still print
+                fwd_bwd[name] = {"error": repr(e)[:300]}
+            torch.cuda.empty_cache()
+
     if rank == 0:
-        # roofline of the dominant (only) kernel: FP32 CUDA-core pipe, peak measured live by an FFMA probe
-        import ctypes as C
-        tf = C.c_double(0.0)
-        rc = lib().fetode_probe_fp32_peak(C.byref(tf), C.c_void_p(torch.cuda.current_stream().cuda_stream))
-        peak_tf = tf.value if rc == 0 and tf.value > 0 else 2 * 128 * 148 * 1.965e9 / 1e12
-        ach_tf = FLOP_PER_TRAJ_STEP * B * n_rk / (ms_kernel / args.steps * 1e-3) / 1e12
+        per_launch_ms = ms_kernel / args.steps
+        peak_tf = fp32_peak if fp32_peak else 2 * 128 * 148 * 1.965e9 / 1e12
+        ach_tf = FLOP_PER_TRAJ_STEP * B * n_rk / (per_launch_ms * 1e-3) / 1e12
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         hbm_bytes = B * (8 + 8 + 4 * plan.state_floats)              # y0 in, y out, hysteresis state out
-        # DRAM bytes per launch of the same kernel from the committed `ncu --set full` capture (profiles/)
         traffic, traffic_src = None, None
         try:
             import csv
-            prof = os.path.join(ROOT, "profiles", "r1_smallnet_rk_ncu_full.csv")
+            prof = os.path.join(ROOT, "profiles", "r2_smallnet_rk2_ncu_full.csv")
             vals = {r[0]: (r[1], float(r[2])) for r in csv.reader(open(prof)) if len(r) == 3 and r[0].startswith("dram__bytes")}
             scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
             traffic = sum(v * scale[u] for u, v in vals.values())
-            traffic_src = "profiles/r1_smallnet_rk_ncu_full.csv (dram read+write of one launch at this size; mostly register-spill lines)"
+            traffic_src = "profiles/r2_smallnet_rk2_ncu_full.csv (dram read+write of one launch at 2^20 rows)"
         except Exception:
             pass
         roofline = {
             "bound": "fp32", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
             "traffic": traffic, "traffic_source": traffic_src,
-            "peak_source": "live FFMA probe (fetode_probe_fp32_peak); MEASURED_PEAKS.json holds HBM/bf16 only" if rc == 0
+            "peak_source": "live FFMA probe (fetode_probe_fp32_peak); MEASURED_PEAKS.json holds HBM/bf16 only" if fp32_peak
                            else "fallback 2*128*148*1.965 GHz",
-            "kernel": "smallnet_rk_kernel<2,10,5,FERRO2D>",
+            "kernel": "smallnet_rk2_kernel<2,10,10,5,FERRO2D,...>", "rows_per_launch": B,
             "flop_per_traj_step": FLOP_PER_TRAJ_STEP,
-            "hbm": {"achieved_gbs": hbm_bytes / (ms_kernel / args.steps * 1e-3) / 1e9,
+            "convention": "MODEL FLOP of SURVEY 8(d) (30 per branch basis, dense 8-coefficient spline); the kernel "
+                          "executes fewer (factored exponentials, 4-term cubic): see profiles/ for executed-instruction rates",
+            "inspan_fraction": inspan,
+            "hbm": {"achieved_gbs": hbm_bytes / (per_launch_ms * 1e-3) / 1e9,
                     "peak_gbs": peaks.get("hbm_gbs"), "bytes_per_launch": hbm_bytes},
         }
-        # CPU baseline: oracle port on a bounded sample (about 10-20 s)
-        cores = os.cpu_count() or 1
-        torch.set_num_threads(cores)
-        layers = oracle_layers(model)
-        n_traj, n_steps = cpu_sample_size(layers, 6.0)
-        secs = min(cpu_reference_run(layers, n_traj, n_steps) for _ in range(2))
-        cpu_val = n_traj * n_steps / secs
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_kernel / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "LV KANFET([2,10,2]) inference ensemble, classic RK4, dt=0.014 (BASELINE configs[1])",
-                       "trajectories_per_gpu": B, "rk4_steps_per_step": n_rk, "l2": "flushed (256 MiB write) between timed iterations",
-                       "weights": "random init, torch.manual_seed(0)", "parallelism": f"dp{world} (batch-sharded, no collective)"},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * 8 * world, "d2h_bytes_per_step": B * 8 * world,
+            "warmup": args.warmup, "ms_per_step": per_launch_ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "trajectories_total": total, "trajectories_per_gpu": B,
+                       "rk4_steps_per_step": n_rk, "l2": "flushed (256 MiB write) between timed iterations",
+                       "weights": "random init, torch.manual_seed(0)",
+                       "parallelism": f"dp{world} (batch-sharded, no collective on this path)"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": total * 8, "d2h_bytes_per_step": total * 8,
                     "ms_per_step": ms_e2e / args.steps, "api": "fetode.integrate_rk4(as_rhs(KANFET), x0, 0, 14, 1000)"},
-            "gpu_launches": args.steps,
+            "gpu_launches": args.steps * world,
+            "outputs_finite": finite,
             "clocks": clk.summary(),
             "roofline": roofline,
-            "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{n_traj} trajectories x {n_steps} classic-RK4 steps (oracle port, torch CPU, no_grad)"},
+            "peaks_measured_here": {"fp32_tflops": fp32_peak, "tf32_dense_tflops": tf32_peak},
         }
+        if weak is not None:
+            line["weak"] = weak
+        if fwd_bwd is not None:
+            line["fwd_bwd"] = fwd_bwd
+        if world == 1 and not args.no_cpu:
+            cores = os.cpu_count() or 1
+            torch.set_num_threads(cores)
+            layers = oracle_layers(model)
+            n_traj, n_steps = CPU_SAMPLE
+            cpu_reference_run(layers, n_traj, 1)                     # warm-up
+            secs = min(cpu_reference_run(layers, n_traj, n_steps) for _ in range(2))
+            line["cpu_baseline"] = {"value": n_traj * n_steps / secs, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": f"{n_traj} trajectories x {n_steps} classic-RK4 steps (oracle port, torch CPU, no_grad)"}
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        import gc
+        import signal
+        gc.collect()
+        torch.cuda.synchronize()
+        signal.signal(signal.SIGALRM, lambda *_: os._exit(0))        # the line is printed: never hang in teardown
+        signal.alarm(60)
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
 
 
 def main():
@@ -315,8 +578,11 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--traj-per-gpu", type=int, default=TRAJ_PER_GPU)
+    ap.add_argument("--trajectories", type=int, default=TRAJ_TOTAL, help="total over all ranks")
     ap.add_argument("--rk-steps", type=int, default=RK_STEPS)
+    ap.add_argument("--no-train", action="store_true", help="skip the fwd_bwd block")
+    ap.add_argument("--no-weak", action="store_true", help="skip the weak-scaling secondary measurement (N > 1)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU legs (N = 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
