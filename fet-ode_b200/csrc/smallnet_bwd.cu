@@ -284,8 +284,11 @@ __device__ __forceinline__ void sn_rhs_bwd(const float* __restrict__ sm, const f
     }
 }
 
-template <int D, int NB, int G, int BR>
-__global__ void __launch_bounds__(SN_THREADS) smallnet_rk_bwd_kernel(const SNBwdArgs a) {
+// MINB = 4 caps the kernel at 128 registers (a few spills) so that four CTAs fit an SM: B = 65 536 rows is 512 CTAs, which
+// then run as ONE wave (3 CTAs per SM at 168 registers needed a second, nearly empty wave: 11.5 -> 10.1 ms per LV
+// training step).  Small batches are a single serial lane chain per warp: they take the spill-free build (MINB = 3).
+template <int D, int NB, int G, int BR, int MINB>
+__global__ void __launch_bounds__(SN_THREADS, MINB) smallnet_rk_bwd_kernel(const SNBwdArgs a) {
     extern __shared__ float4 sn_smem4[];
     float* sm = reinterpret_cast<float*>(sn_smem4);
     using A = SNAcc<D, NB, G, BR>;
@@ -420,11 +423,20 @@ static int snb_launch_k(const SNBwdArgs& a, cudaStream_t st) {
     const int total_ext = round_up(L0.total + a.H * L0.REC + 2 * D * NB + 2 * a.H * NB, 4);
     const size_t smem = (size_t)(total_ext + 4 * a.H * SN_THREADS + A::total(a.H)) * 4;
     if (smem > 227 * 1024) return FETODE_EUNSUPPORTED;
-    auto kern = smallnet_rk_bwd_kernel<D, NB, 5, BR>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
     const unsigned grid = (unsigned)((a.B + SN_THREADS - 1) / SN_THREADS);
-    kern<<<grid, SN_THREADS, smem, st>>>(a);
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (grid > (unsigned)(3 * sms)) {
+        auto kern = smallnet_rk_bwd_kernel<D, NB, 5, BR, 4>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        kern<<<grid, SN_THREADS, smem, st>>>(a);
+    } else {
+        auto kern = smallnet_rk_bwd_kernel<D, NB, 5, BR, 3>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        kern<<<grid, SN_THREADS, smem, st>>>(a);
+    }
     return FETODE_LAUNCH_RC();
 }
 
