@@ -6,17 +6,18 @@ Host-side mirror of the reference's module surface (sallywang147/FET-ODE @ 704a0
   fetode.ecg            hysteretic LogisticBasis, KANFeatureMixer, MLPKANODEFunc, KANFetODEFunc (ECG scripts)
   fetode.mnist_kuramoto_kan  KANLinear, Kuramoto2D, KuramotoKANClassifier             (mnist_kuramoto_kan.py)
   fetode.odeint         odeint, integrate_euler/rk2/rk4, odeint_rk4 (torchdiffeq call sites + in-repo loops)
+  fetode.compat         install(): sys.modules shims so the reference's own import lines resolve to the above
 All arithmetic runs in fetode/libfetode.so (C ABI: include/fetode.h); there is no CPU fallback.
 """
 from . import _lib  # noqa: F401
 from .efficientkan import KAN, KANFET, KANLinear, LogisticBasis  # noqa: F401
 from .ferro_class import (BatchedFerroelectricBasis, FerroelectricBasis, NoisyBatchedFerroelectricBasis,  # noqa: F401
                           NoisyFerroelectricBasis, TwoDimensionFerroelectricBasis)
-from . import ecg, graphs, mnist_kuramoto_kan, optim  # noqa: F401
+from . import compat, ecg, graphs, mnist_kuramoto_kan, optim  # noqa: F401
 from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odeint,  # noqa: F401
                      odeint_rk4)
 
 __all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "FerroelectricBasis",
            "NoisyFerroelectricBasis", "BatchedFerroelectricBasis", "NoisyBatchedFerroelectricBasis", "ecg",
-           "mnist_kuramoto_kan", "optim", "graphs", "odeint",
+           "mnist_kuramoto_kan", "optim", "graphs", "compat", "odeint",
            "integrate_euler", "integrate_rk2", "integrate_rk4", "odeint_rk4", "as_rhs"]
