@@ -72,7 +72,30 @@ struct FerroArgs {
     long long B;
     int I, O, K, prev_is_zero, apply_sigmoid;
     float g, alpha;
+    // fused right-hand-side glue of KANFetODEFunc.forward (train_ecg.py:997-1013), FULL variant only
+    float pre_bound;          // > 0: the neuron sees x_eff = pre_bound * tanh(x / pre_bound)            :1000
+    int post_op;              // 1: out = tanh(out) :1003 ; 2: nan_to_num(nan=0, +-inf=+-1e3) then clamp(+-50) :1008-1011
+    float* xeff_out;          // [B,I] <- x_eff (the next call's prev_x) or null
+    const float* yout;        // backward: the forward's (post-op) output, for d(post)/d(out)
 };
+
+__device__ __forceinline__ float ferro_post(float v, int op) {
+    if (op == 1) return tanh_fast(v);
+    if (op == 2) {
+        if (v != v) v = 0.f;
+        v = fminf(fmaxf(v, -1e3f), 1e3f);                 // +-inf -> +-1e3 (nan_to_num), then
+        return fminf(fmaxf(v, -50.0f), 50.0f);            // torch.clamp(dh, -50, 50)
+    }
+    return v;
+}
+// d(post)/d(out) from the post-op value y: tanh' = 1 - y^2; the clamp passes the gradient strictly inside (-50, 50)
+// (torch also passes it AT the bound: a measure-zero difference) -- a NaN that nan_to_num zeroed poisons the chain
+// in torch as well (0 * NaN upstream)
+__device__ __forceinline__ float ferro_post_grad(float y, int op) {
+    if (op == 1) return 1.0f - y * y;
+    if (op == 2) return fabsf(y) < 50.0f ? 1.0f : 0.f;
+    return 1.0f;
+}
 
 template <bool HAS_BR>
 __global__ void __launch_bounds__(FF_THREADS) ferro_full_fwd_kernel(const FerroArgs a) {
@@ -85,10 +108,12 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_fwd_kernel(const FerroA
     const int o = blockIdx.y * 32 + lane;
     const int I = a.I, O = a.O, K = a.K;
     for (int i = threadIdx.x; i < I; i += FF_THREADS) {
-        const float x = a.x[b * I + i];
-        const float p = a.prev_is_zero ? 0.f : a.prev[b * I + i];
+        float x = a.x[b * I + i];
+        if (a.pre_bound > 0.f) x = a.pre_bound * tanh_fast(x / a.pre_bound);
+        const float p = a.prev_is_zero == 1 ? 0.f : (a.prev_is_zero == 2 ? x : a.prev[b * I + i]);
         xs[i] = x;
         ups[i] = sigm(a.g * (x - p));
+        if (a.xeff_out && blockIdx.y == 0) a.xeff_out[b * I + i] = x;
     }
     __syncthreads();
     float acc = 0.f;
@@ -109,7 +134,8 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_fwd_kernel(const FerroA
     }
     part[w][lane] = acc;
     __syncthreads();
-    if (w == 0 && o < O) a.out[b * O + o] = part[0][lane] + part[1][lane] + part[2][lane] + part[3][lane];
+    if (w == 0 && o < O)
+        a.out[b * O + o] = ferro_post(part[0][lane] + part[1][lane] + part[2][lane] + part[3][lane], a.post_op);
 }
 
 // backward: one CTA per (input i, 32 outputs, tile of FB_BT rows); warps split the basis index j.
@@ -117,7 +143,7 @@ constexpr int FB_BT = 64;
 
 template <bool HAS_BR>
 __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroArgs a) {
-    __shared__ float xs[FB_BT], ups[FB_BT], dxs[FB_BT];
+    __shared__ float xs[FB_BT], ups[FB_BT], dxs[FB_BT], dpre[FB_BT];
     const int i = blockIdx.x;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int o = blockIdx.y * 32 + lane;
@@ -126,10 +152,20 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
     const int I = a.I, O = a.O, K = a.K;
     for (int t = threadIdx.x; t < FB_BT; t += FF_THREADS) {
         float x = 0.f, p = 0.f;
-        if (t < nb) { x = a.x[(b0 + t) * I + i]; p = a.prev_is_zero ? 0.f : a.prev[(b0 + t) * I + i]; }
+        float dp = 1.0f;
+        if (t < nb) {
+            x = a.x[(b0 + t) * I + i];
+            if (a.pre_bound > 0.f) {
+                const float th = tanh_fast(x / a.pre_bound);
+                x = a.pre_bound * th;
+                dp = 1.0f - th * th;
+            }
+            p = a.prev_is_zero == 1 ? 0.f : (a.prev_is_zero == 2 ? x : a.prev[(b0 + t) * I + i]);
+        }
         xs[t] = x;
         ups[t] = sigm(a.g * (x - p));
         dxs[t] = 0.f;
+        dpre[t] = dp;
     }
     __syncthreads();
     for (int j = w; j < K; j += 4) {
@@ -145,7 +181,8 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
                 const SoftBranch s = soft_branch(x, ups[t], k, Ec, br, a.g, a.alpha);
                 float dm_dx, dm_dEc;
                 soft_branch_grad(s, br, a.g, a.alpha, dm_dx, dm_dEc);
-                const float go = a.gout[(b0 + t) * O + o];
+                float go = a.gout[(b0 + t) * O + o];
+                if (a.post_op) go *= ferro_post_grad(a.yout[(b0 + t) * O + o], a.post_op);
                 ac = fmaf(go, fmaf(Ps, s.T, bias), ac);
                 const float gP = go * coef;
                 aPs = fmaf(gP, s.T, aPs);
@@ -170,7 +207,7 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
     }
     __syncthreads();
     if (a.gx)
-        for (int t = threadIdx.x; t < nb; t += FF_THREADS) atomicAdd(a.gx + (b0 + t) * I + i, dxs[t]);
+        for (int t = threadIdx.x; t < nb; t += FF_THREADS) atomicAdd(a.gx + (b0 + t) * I + i, dxs[t] * dpre[t]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -349,6 +386,8 @@ static FerroArgs ferro_args(const fetode_ferro_t* F, int64_t B) {
     a.k = F->k; a.Ec = F->Ec; a.Ps = F->Ps; a.bias = F->bias; a.coef = F->coef;
     a.B = B; a.I = F->in_dim; a.O = F->out_dim; a.K = F->num_basis;
     a.g = F->gate_slope; a.alpha = F->alpha; a.apply_sigmoid = F->apply_sigmoid;
+    a.pre_bound = F->variant == FETODE_FERRO_FULL ? F->pre_bound : 0.f;
+    a.post_op = F->variant == FETODE_FERRO_FULL ? F->post_op : 0;
     return a;
 }
 
@@ -364,10 +403,13 @@ extern "C" int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const f
     FETODE_CHECK_ARG(x && out && B >= 0);
     if (B == 0) return FETODE_OK;
     if (!prev_is_zero) FETODE_CHECK_ARG(prev != nullptr);
+    FETODE_CHECK_ARG(prev_is_zero >= 0 && prev_is_zero <= 2 && (prev_is_zero != 2 || F->variant == FETODE_FERRO_FULL));
+    FETODE_CHECK_ARG(F->post_op >= 0 && F->post_op <= 2);
     cudaStream_t st = (cudaStream_t)stream;
     FerroArgs a = ferro_args(F, B);
     a.x = x; a.prev = prev; a.prev_is_zero = prev_is_zero; a.br = br; a.out = out; a.basis_out = basis_out;
     a.br_out = br_out; a.gate_out = gate_out;
+    if (F->variant == FETODE_FERRO_FULL && a.pre_bound > 0.f) { a.xeff_out = prev_out; prev_out = nullptr; }
     if (F->variant == FETODE_FERRO_FULL) {
         FETODE_CHECK_SUPPORTED(B <= 0x7fffffffLL);
         const dim3 grid((unsigned)B, (unsigned)((a.O + 31) / 32));
@@ -400,12 +442,20 @@ extern "C" int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const f
 extern "C" int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
                                 const float* br, const float* gout, float* gx,
                                 const fetode_ferro_grads_t* grads, int64_t B, void* stream) {
+    return fetode_ferro_bwd_fused(F, x, prev, prev_is_zero, br, gout, nullptr, gx, grads, B, stream);
+}
+
+extern "C" int fetode_ferro_bwd_fused(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
+                                      const float* br, const float* gout, const float* yout, float* gx,
+                                      const fetode_ferro_grads_t* grads, int64_t B, void* stream) {
     int rc = ferro_check(F);
     if (rc) return rc;
     FETODE_CHECK_ARG(x && gout && B >= 0);
     if (!prev_is_zero) FETODE_CHECK_ARG(prev != nullptr);
+    if (F->variant == FETODE_FERRO_FULL && F->post_op) FETODE_CHECK_ARG(yout != nullptr);
     cudaStream_t st = (cudaStream_t)stream;
     FerroArgs a = ferro_args(F, B);
+    a.yout = yout;
     a.x = x; a.prev = prev; a.prev_is_zero = prev_is_zero; a.br = br; a.gout = gout; a.gx = gx;
     if (grads) { a.gk = grads->k; a.gEc = grads->Ec; a.gPs = grads->Ps; a.gbias = grads->bias; a.gcoef = grads->coef; }
     if (gx) {

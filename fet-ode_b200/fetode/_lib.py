@@ -56,6 +56,7 @@ class Ferro(C.Structure):
         ("variant", C.c_int32), ("in_dim", C.c_int32), ("out_dim", C.c_int32), ("num_basis", C.c_int32),
         ("k", C.c_void_p), ("Ec", C.c_void_p), ("Ps", C.c_void_p), ("bias", C.c_void_p), ("coef", C.c_void_p),
         ("gate_slope", C.c_float), ("alpha", C.c_float), ("apply_sigmoid", C.c_int32),
+        ("pre_bound", C.c_float), ("post_op", C.c_int32),
     ]
 
 

@@ -199,9 +199,39 @@ class KANFetODEFunc(nn.Module):
         self.act = nn.Tanh()
         self.fc2 = FerroelectricBasis(hidden_dim, latent_dim, num_basis)
 
+    def _fusable(self) -> bool:
+        return all(type(f) is FerroelectricBasis and not (f.use_noise and f.noise_std != 0.0) for f in (self.fc1, self.fc2)) \
+            and isinstance(self.act, nn.Tanh) and self.h_bound > 0
+
+    @staticmethod
+    def _mode(f, B):
+        """Hysteresis source of a FerroelectricBasis call: (prev rows or None, prev_mode) -- the reference's rule
+        (ferro_class.py:373-378): fresh [1,...] zeros match only B == 1, any other shape mismatch re-creates prev = x."""
+        r = f._rows
+        if r is None:
+            return None, (1 if B == 1 else 2)
+        if r.shape[0] != B:
+            return None, 2
+        return (r if r.is_contiguous() else r.contiguous()), 0
+
     def forward(self, t, h):
         if h.dim() == 1:
             h = h.unsqueeze(0)
+        if self._fusable() and h.is_cuda and h.dim() == 2:
+            # two launches: [tanh bound -> fc1 -> tanh] and [fc2 -> nan_to_num -> clamp]; the glue of :1000-1011 runs
+            # inside the neuron kernels (csrc/ferro.cu, pre_bound / post_op)
+            ops.abort_if_tracing()
+            x = ops.f32c(h)
+            B = x.shape[0]
+            p1, m1 = self._mode(self.fc1, B)
+            hb = torch.empty_like(x)                                   # the bounded state = fc1's next prev_x
+            z, _ = ops.ferro_apply(self.fc1, ops.FERRO_FULL, x, p1, prev_out=hb, pre_bound=self.h_bound, post_op=1,
+                                   prev_mode=m1)
+            self.fc1._set_rows(hb)
+            p2, m2 = self._mode(self.fc2, B)
+            dh, _ = ops.ferro_apply(self.fc2, ops.FERRO_FULL, z, p2, post_op=2, prev_mode=m2)
+            self.fc2._set_rows(z.detach().clone())                     # own the state (z is saved for backward)
+            return dh
         h = self.h_bound * torch.tanh(h / self.h_bound)
         z = self.act(self.fc1(h))
         dh = self.fc2(z)

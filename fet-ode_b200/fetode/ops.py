@@ -568,6 +568,7 @@ def _ferro_struct(cfg: dict, k, Ec, Ps, bias, coef) -> _lib.Ferro:
         setattr(s, name, ptr(None if t is None else _keep(s, f32c(t.detach()))).value)
     s.gate_slope, s.alpha = float(cfg["gate_slope"]), float(cfg["alpha"])
     s.apply_sigmoid = int(cfg.get("apply_sigmoid", 0))
+    s.pre_bound, s.post_op = float(cfg.get("pre_bound", 0.0)), int(cfg.get("post_op", 0))
     return s
 
 
@@ -591,23 +592,28 @@ class FerroFn(torch.autograd.Function):
         s = _ferro_struct(cfg, k, Ec, Ps, bias, coef)
         if br_out is not None and br is None:
             br = torch.ones(elem_shape, dtype=torch.float32, device=x.device)
+        # prev_mode: 0 read prev, 1 all zero, 2 (FULL) prev == effective input (first call with a batch, :373-378)
+        mode = int(cfg.get("prev_mode", 1 if prev is None else 0))
         if B > 0:
-            check(lib().fetode_ferro_fwd(C.byref(s), ptr(x), ptr(prev), C.c_int(1 if prev is None else 0), ptr(br),
+            check(lib().fetode_ferro_fwd(C.byref(s), ptr(x), ptr(prev if mode == 0 else None), C.c_int(mode), ptr(br),
                                          ptr(out), ptr(basis), ptr(br_out), ptr(gate), ptr(prev_out),
                                          C.c_int64(B), stream()), "ferro_fwd")
         side.update(basis=basis, br_out=br_out, gate=gate)
         cfg["side"] = side
-        ctx.cfg, ctx.prev, ctx.br = cfg, prev, br
-        ctx.save_for_backward(x, k, Ec, Ps, bias, coef if coef is not None else x.new_empty(0))
+        ctx.cfg, ctx.prev, ctx.br, ctx.mode = cfg, (prev if mode == 0 else None), br, mode
+        ctx.save_for_backward(x, k, Ec, Ps, bias, coef if coef is not None else x.new_empty(0),
+                              out if cfg.get("post_op", 0) else x.new_empty(0))
         ctx.has_coef = coef is not None
         return out
 
     @staticmethod
     def backward(ctx, gout):
-        x, k, Ec, Ps, bias, coef = ctx.saved_tensors
+        x, k, Ec, Ps, bias, coef, yout = ctx.saved_tensors
         if not ctx.has_coef:
             coef = None
         cfg = ctx.cfg
+        if not cfg.get("post_op", 0):
+            yout = None
         gout = f32c(gout)
         B = x.shape[0]
         s = _ferro_struct(cfg, k, Ec, Ps, bias, coef)
@@ -620,15 +626,14 @@ class FerroFn(torch.autograd.Function):
             setattr(g, name, ptr(gt).value)
             grads.append(gt)
         gx = torch.empty_like(x) if ctx.needs_input_grad[3] else None
-        check(lib().fetode_ferro_bwd(C.byref(s), ptr(x), ptr(ctx.prev), C.c_int(1 if ctx.prev is None else 0),
-                                     ptr(ctx.br), ptr(gout), ptr(gx), C.byref(g), C.c_int64(B), stream()),
-              "ferro_bwd")
+        check(lib().fetode_ferro_bwd_fused(C.byref(s), ptr(x), ptr(ctx.prev), C.c_int(ctx.mode), ptr(ctx.br), ptr(gout),
+                                           ptr(yout), ptr(gx), C.byref(g), C.c_int64(B), stream()), "ferro_bwd")
         return (None, None, None, gx, *grads)
 
 
 def ferro_apply(module, variant: int, x2: torch.Tensor, prev: Optional[torch.Tensor], *, br=None,
                 want_basis=False, want_br_out=False, want_gate=False, apply_sigmoid=False, prev_out=None,
-                gate_slope=None, alpha=None):
+                gate_slope=None, alpha=None, pre_bound=0.0, post_op=0, prev_mode=None):
     """Launch the neuron kernel for ``module`` (parameter names k, Ec, Ps, bias, coef | a, b).
     Returns (out, side) where side holds the optional basis / br_out / gate tensors."""
     if variant == FERRO_LOGISTIC:
@@ -644,7 +649,9 @@ def ferro_apply(module, variant: int, x2: torch.Tensor, prev: Optional[torch.Ten
                gate_slope=getattr(module, "gate_slope", 0.0) if gate_slope is None else gate_slope,
                alpha=getattr(module, "alpha", 0.5) if alpha is None else alpha,
                apply_sigmoid=int(apply_sigmoid), want_basis=want_basis, want_br_out=want_br_out,
-               want_gate=want_gate, prev_out=prev_out)
+               want_gate=want_gate, prev_out=prev_out, pre_bound=float(pre_bound), post_op=int(post_op))
+    if prev_mode is not None:
+        cfg["prev_mode"] = int(prev_mode)
     if variant == FERRO_LOGISTIC:
         cfg["gate_slope"], cfg["alpha"] = 0.0, 0.0
     out = FerroFn.apply(cfg, prev, br, x2, k, Ec, Ps, bias, coef)

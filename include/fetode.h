@@ -237,6 +237,9 @@ typedef struct fetode_ferro {
     float gate_slope, alpha;                   /* hard gate: gate_slope=5, alpha=breaking point 0.5 */
     int32_t apply_sigmoid;                     /* HARDGATE only: 1 = KANFeatureMixer's sigmoid :419 fused in;
                                                   2 = sigmoid then nan_to_num(nan=0) (MLPKANODEFunc.forward :464-465) */
+    /* FULL only: the glue of KANFetODEFunc.forward (train_ecg.py:997-1013) folded into the neuron kernel */
+    float pre_bound;                           /* > 0: input x_eff = pre_bound * tanh(x / pre_bound)  :1000; prev_out <- x_eff */
+    int32_t post_op;                           /* 1: tanh(out) :1003 ; 2: nan_to_num(0, +-1e3) then clamp(+-50) :1008-1011 */
 } fetode_ferro_t;
 
 typedef struct fetode_ferro_grads { float *k, *Ec, *Ps, *bias, *coef; } fetode_ferro_grads_t;
@@ -249,6 +252,12 @@ FETODE_API int fetode_ferro_fwd(const fetode_ferro_t* F, const float* x, const f
 FETODE_API int fetode_ferro_bwd(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
                      const float* br, const float* gout, float* gx /* [B,I] overwritten, or NULL */,
                      const fetode_ferro_grads_t* grads /* accumulated */, int64_t B, void* stream);
+/* prev_is_zero (both directions): 0 = read prev, 1 = prev is all zero, 2 (FULL) = prev IS the effective input (the
+ * reference's first call with a batch: buffers re-created as prev = x, ferro_class.py:373-378).
+ * _bwd_fused: as fetode_ferro_bwd for a forward that ran with post_op != 0; yout [B,O] is that forward's output. */
+FETODE_API int fetode_ferro_bwd_fused(const fetode_ferro_t* F, const float* x, const float* prev, int prev_is_zero,
+                     const float* br, const float* gout, const float* yout, float* gx,
+                     const fetode_ferro_grads_t* grads, int64_t B, void* stream);
 
 /* ---- Kuramoto lattice -----------------------------------------------------------------
  * Kuramoto2D.forward mnist_kuramoto_kan.py:175-204: x [B,H*W] in [0,1] -> feat [B, 2*H*W]

@@ -201,3 +201,46 @@ def test_empty_and_shape_errors(cuda):
     hg = ecg.LogisticBasis(8, 6).to(cuda)
     with pytest.raises(ValueError):
         hg(torch.randn(3, 7, device=cuda))
+
+
+@pytest.mark.parametrize("B", [1, 37])
+def test_kanfet_ode_func_fused_glue_values_and_gradients(cuda, B):
+    """KANFetODEFunc (train_ecg.py:986-1013) with its glue fused into the two neuron launches: two chained calls
+    (the second sees the hysteresis state of the first) against the oracle in fp32 (values) and fp64 autograd
+    (input and every parameter gradient); an out-of-range output exercises the clamp's zero gradient."""
+    gen = torch.Generator().manual_seed(100 + B)
+    p1 = OL.make_ferro_params((6, 9, 4), gen)
+    p2 = OL.make_ferro_params((9, 6, 4), gen)
+    p2["coef"] = p2["coef"] * 25.0                                      # push some outputs beyond +-50
+    m = ecg.KANFetODEFunc(6, 9, 4, h_bound=1.5)
+    m.fc1.load_state_dict(p1, strict=False)
+    m.fc2.load_state_dict(p2, strict=False)
+    m = m.to(cuda)
+    assert m._fusable()
+    hs = [torch.randn(B, 6, generator=gen) * 2.0, torch.randn(B, 6, generator=gen) * 2.0]
+    ws = [torch.randn(B, 6, generator=gen, dtype=torch.float64) for _ in hs]
+
+    def run_oracle(dtype):
+        q1 = {k: v.to(dtype).clone().requires_grad_(dtype == torch.float64) for k, v in p1.items()}
+        q2 = {k: v.to(dtype).clone().requires_grad_(dtype == torch.float64) for k, v in p2.items()}
+        s1, s2 = OL.FerroFullState(q1), OL.FerroFullState(q2)
+        xs = [h.to(dtype).clone().requires_grad_(dtype == torch.float64) for h in hs]
+        outs = [OL.kanfet_ode_rhs(x, q1, q2, s1, s2, h_bound=1.5) for x in xs]
+        return q1, q2, xs, outs
+    with torch.no_grad():
+        _, _, _, want32 = run_oracle(torch.float32)
+    q1, q2, x64, out64 = run_oracle(torch.float64)
+    sum((o * w).sum() for o, w in zip(out64, ws)).backward()
+    xg = [h.to(cuda).requires_grad_(True) for h in hs]
+    outs = [m(None, x) for x in xg]
+    for o, w32 in zip(outs, want32):
+        assert max_rel(o, w32) < RHS_TOL
+    assert float(torch.cat([o.detach().abs().flatten() for o in outs]).max()) == 50.0     # the clamp is active
+    sum((o * w.float().to(cuda)).sum() for o, w in zip(outs, ws)).backward()
+    for a, b in zip(xg, x64):
+        assert max_rel(a.grad, b.grad) < GRAD_TOL
+    for mod, q in ((m.fc1, q1), (m.fc2, q2)):
+        for name, t in mod.named_parameters():
+            assert max_rel(t.grad, q[name].grad) < GRAD_TOL, name
+    # state left behind: fc1 remembers the BOUNDED input, fc2 remembers tanh(fc1 out)
+    assert max_rel(m.fc1._rows, 1.5 * torch.tanh(hs[1] / 1.5)) < 1e-6
