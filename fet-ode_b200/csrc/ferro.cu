@@ -77,7 +77,24 @@ struct FerroArgs {
     int post_op;              // 1: out = tanh(out) :1003 ; 2: nan_to_num(nan=0, +-inf=+-1e3) then clamp(+-50) :1008-1011
     float* xeff_out;          // [B,I] <- x_eff (the next call's prev_x) or null
     const float* yout;        // backward: the forward's (post-op) output, for d(post)/d(out)
+    // implicit im2col (FerroelectricBasisConv2d, ferro_class.py:689-779): rows are (image b, patch l), input i is
+    // (channel, ky, kx); x / prev / gx are IMAGES [B,Cin,H,W], out / gout are [B,Cout,L] (+ out_bias)
+    fetode_conv2d_t cv;
+    int conv, br_momentum;    // br_momentum: br_out <- branch_momentum (:763-767) instead of target_sign
+    const float* out_bias;
+    float* g_out_bias;
 };
+
+// image offset of input i of patch row `row`, or -1 in the zero padding (F.unfold semantics, :699)
+__device__ __forceinline__ long long conv_index(const fetode_conv2d_t& g, long long row, int i) {
+    const int L = g.Hout * g.Wout;
+    const long long b = row / L;
+    const int l = (int)(row % L), oy = l / g.Wout, ox = l % g.Wout;
+    const int kk = g.kH * g.kW, c = i / kk, r = i % kk, ky = r / g.kW, kx = r % g.kW;
+    const int y = oy * g.stride - g.padding + ky, x = ox * g.stride - g.padding + kx;
+    if (y < 0 || y >= g.H || x < 0 || x >= g.W) return -1;
+    return ((b * g.Cin + c) * g.H + y) * (long long)g.W + x;
+}
 
 __device__ __forceinline__ float ferro_post(float v, int op) {
     if (op == 1) return tanh_fast(v);
@@ -108,9 +125,10 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_fwd_kernel(const FerroA
     const int o = blockIdx.y * 32 + lane;
     const int I = a.I, O = a.O, K = a.K;
     for (int i = threadIdx.x; i < I; i += FF_THREADS) {
-        float x = a.x[b * I + i];
+        const long long src = a.conv ? conv_index(a.cv, b, i) : b * I + i;
+        float x = src >= 0 ? a.x[src] : 0.f;
         if (a.pre_bound > 0.f) x = a.pre_bound * tanh_fast(x / a.pre_bound);
-        const float p = a.prev_is_zero == 1 ? 0.f : (a.prev_is_zero == 2 ? x : a.prev[b * I + i]);
+        const float p = a.prev_is_zero == 1 ? 0.f : (a.prev_is_zero == 2 ? x : (src >= 0 ? a.prev[src] : 0.f));
         xs[i] = x;
         ups[i] = sigm(a.g * (x - p));
         if (a.xeff_out && blockIdx.y == 0) a.xeff_out[b * I + i] = x;
@@ -128,14 +146,21 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_fwd_kernel(const FerroA
                 const float P = fmaf(a.Ps[base + j], s.T, a.bias[base + j]);
                 acc = fmaf(a.coef[base + j], P, acc);
                 if (a.basis_out) a.basis_out[sbase + j] = P;
-                if (HAS_BR && a.br_out) a.br_out[sbase + j] = s.tgt;          // ferro_class.py:512-514
+                if (HAS_BR && a.br_out) a.br_out[sbase + j] = a.br_momentum ? s.m : s.tgt;   // ferro_class.py:512-514 / :767
             }
         }
     }
     part[w][lane] = acc;
     __syncthreads();
-    if (w == 0 && o < O)
-        a.out[b * O + o] = ferro_post(part[0][lane] + part[1][lane] + part[2][lane] + part[3][lane], a.post_op);
+    if (w == 0 && o < O) {
+        const float v = part[0][lane] + part[1][lane] + part[2][lane] + part[3][lane];
+        if (a.conv) {
+            const int L = a.cv.Hout * a.cv.Wout;
+            a.out[((b / L) * O + o) * L + b % L] = v + (a.out_bias ? a.out_bias[o] : 0.f);     // (B, Cout, L) :770-773
+        } else {
+            a.out[b * O + o] = ferro_post(v, a.post_op);
+        }
+    }
 }
 
 // backward: one CTA per (input i, 32 outputs, tile of FB_BT rows); warps split the basis index j.
@@ -144,6 +169,7 @@ constexpr int FB_BT = 64;
 template <bool HAS_BR>
 __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroArgs a) {
     __shared__ float xs[FB_BT], ups[FB_BT], dxs[FB_BT], dpre[FB_BT];
+    __shared__ long long srcs[FB_BT];
     const int i = blockIdx.x;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int o = blockIdx.y * 32 + lane;
@@ -153,15 +179,18 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
     for (int t = threadIdx.x; t < FB_BT; t += FF_THREADS) {
         float x = 0.f, p = 0.f;
         float dp = 1.0f;
+        long long src = -1;
         if (t < nb) {
-            x = a.x[(b0 + t) * I + i];
+            src = a.conv ? conv_index(a.cv, b0 + t, i) : (b0 + t) * I + i;
+            x = src >= 0 ? a.x[src] : 0.f;
             if (a.pre_bound > 0.f) {
                 const float th = tanh_fast(x / a.pre_bound);
                 x = a.pre_bound * th;
                 dp = 1.0f - th * th;
             }
-            p = a.prev_is_zero == 1 ? 0.f : (a.prev_is_zero == 2 ? x : a.prev[(b0 + t) * I + i]);
+            p = a.prev_is_zero == 1 ? 0.f : (a.prev_is_zero == 2 ? x : (src >= 0 ? a.prev[src] : 0.f));
         }
+        srcs[t] = src;
         xs[t] = x;
         ups[t] = sigm(a.g * (x - p));
         dxs[t] = 0.f;
@@ -172,7 +201,7 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
         float k = 0.f, Ec = 0.f, Ps = 0.f, bias = 0.f, coef = 0.f;
         const size_t base = ((size_t)i * O + o) * K + j;
         if (o < O) { k = a.k[base]; Ec = a.Ec[base]; Ps = a.Ps[base]; bias = a.bias[base]; coef = a.coef[base]; }
-        float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f;
+        float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f, gob = 0.f;
         for (int t = 0; t < nb; ++t) {
             float dx = 0.f;
             if (o < O) {
@@ -181,7 +210,14 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
                 const SoftBranch s = soft_branch(x, ups[t], k, Ec, br, a.g, a.alpha);
                 float dm_dx, dm_dEc;
                 soft_branch_grad(s, br, a.g, a.alpha, dm_dx, dm_dEc);
-                float go = a.gout[(b0 + t) * O + o];
+                float go;
+                if (a.conv) {
+                    const int L = a.cv.Hout * a.cv.Wout;
+                    go = a.gout[(((b0 + t) / L) * O + o) * L + (b0 + t) % L];
+                    if (i == 0 && j == 0) gob += go;
+                } else {
+                    go = a.gout[(b0 + t) * O + o];
+                }
                 if (a.post_op) go *= ferro_post_grad(a.yout[(b0 + t) * O + o], a.post_op);
                 ac = fmaf(go, fmaf(Ps, s.T, bias), ac);
                 const float gP = go * coef;
@@ -203,11 +239,13 @@ __global__ void __launch_bounds__(FF_THREADS) ferro_full_bwd_kernel(const FerroA
             if (a.gPs) atomicAdd(a.gPs + base, aPs);
             if (a.gbias) atomicAdd(a.gbias + base, ab);
             if (a.gcoef) atomicAdd(a.gcoef + base, ac);
+            if (a.conv && a.g_out_bias && i == 0 && j == 0) atomicAdd(a.g_out_bias + o, gob);
         }
     }
     __syncthreads();
     if (a.gx)
-        for (int t = threadIdx.x; t < nb; t += FF_THREADS) atomicAdd(a.gx + (b0 + t) * I + i, dxs[t] * dpre[t]);
+        for (int t = threadIdx.x; t < nb; t += FF_THREADS)
+            if (srcs[t] >= 0) atomicAdd(a.gx + srcs[t], dxs[t] * dpre[t]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -476,5 +514,71 @@ extern "C" int fetode_ferro_bwd_fused(const fetode_ferro_t* F, const float* x, c
         else if (F->variant == FETODE_FERRO_LOGISTIC) ferro_elem_bwd_kernel<FETODE_FERRO_LOGISTIC><<<grid, 128, 0, st>>>(a);
         else ferro_elem_bwd_kernel<FETODE_FERRO_HARDGATE><<<grid, 128, 0, st>>>(a);
     }
+    return FETODE_LAUNCH_RC();
+}
+
+// ---- FerroelectricBasisConv2d / MemEfficient_FerroelectricBasisConv2d (ferro_class.py:601-944) -------------------
+static int conv_check(const fetode_ferro_t* F, const fetode_conv2d_t* G) {
+    if (!G) return FETODE_EINVAL;
+    if (F->variant != FETODE_FERRO_FULL) return FETODE_EINVAL;
+    if (G->Cin < 1 || G->H < 1 || G->W < 1 || G->kH < 1 || G->kW < 1 || G->stride < 1 || G->padding < 0) return FETODE_EINVAL;
+    if (G->Hout != (G->H + 2 * G->padding - G->kH) / G->stride + 1) return FETODE_ESHAPE;
+    if (G->Wout != (G->W + 2 * G->padding - G->kW) / G->stride + 1) return FETODE_ESHAPE;
+    if (G->Hout < 1 || G->Wout < 1) return FETODE_ESHAPE;
+    if (F->in_dim != G->Cin * G->kH * G->kW) return FETODE_ESHAPE;
+    return FETODE_OK;
+}
+
+extern "C" int fetode_ferro_conv2d_fwd(const fetode_ferro_t* F, const fetode_conv2d_t* G, const float* x,
+                                       const float* prev, int prev_mode, const float* br, const float* out_bias,
+                                       float* out, float* basis_out, float* br_out, int br_momentum, int64_t B,
+                                       void* stream) {
+    int rc = ferro_check(F);
+    if (rc) return rc;
+    rc = conv_check(F, G);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(x && out && B >= 0 && prev_mode >= 0 && prev_mode <= 2 && (prev_mode != 0 || prev));
+    if (B == 0) return FETODE_OK;
+    const long long rows = (long long)B * G->Hout * G->Wout;
+    FETODE_CHECK_SUPPORTED(rows <= 0x7fffffffLL);
+    FerroArgs a = ferro_args(F, rows);
+    a.pre_bound = 0.f; a.post_op = 0;
+    a.x = x; a.prev = prev; a.prev_is_zero = prev_mode; a.br = br; a.out = out; a.basis_out = basis_out;
+    a.br_out = br_out; a.br_momentum = br_momentum; a.cv = *G; a.conv = 1; a.out_bias = out_bias;
+    const dim3 grid((unsigned)rows, (unsigned)((a.O + 31) / 32));
+    const size_t smem = (size_t)2 * a.I * sizeof(float);
+    FETODE_CHECK_SUPPORTED(smem <= 48 * 1024);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (br) ferro_full_fwd_kernel<true><<<grid, FF_THREADS, smem, st>>>(a);
+    else ferro_full_fwd_kernel<false><<<grid, FF_THREADS, smem, st>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_ferro_conv2d_bwd(const fetode_ferro_t* F, const fetode_conv2d_t* G, const float* x,
+                                       const float* prev, int prev_mode, const float* br, const float* gout,
+                                       float* gx, const fetode_ferro_grads_t* grads, float* g_out_bias, int64_t B,
+                                       void* stream) {
+    int rc = ferro_check(F);
+    if (rc) return rc;
+    rc = conv_check(F, G);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(x && gout && B >= 0 && prev_mode >= 0 && prev_mode <= 2 && (prev_mode != 0 || prev));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (gx) {
+        cudaError_t e = cudaMemsetAsync(gx, 0, (size_t)B * G->Cin * G->H * G->W * sizeof(float), st);
+        if (e) return (int)e;
+    }
+    if (B == 0) return FETODE_OK;
+    const long long rows = (long long)B * G->Hout * G->Wout;
+    FerroArgs a = ferro_args(F, rows);
+    a.pre_bound = 0.f; a.post_op = 0;
+    a.x = x; a.prev = prev; a.prev_is_zero = prev_mode; a.br = br; a.gout = gout; a.gx = gx;
+    a.cv = *G; a.conv = 1; a.g_out_bias = g_out_bias;
+    if (grads) { a.gk = grads->k; a.gEc = grads->Ec; a.gPs = grads->Ps; a.gbias = grads->bias; a.gcoef = grads->coef; }
+    const long long bz = (rows + FB_BT - 1) / FB_BT;
+    FETODE_CHECK_SUPPORTED(bz <= 65535 && (a.O + 31) / 32 <= 65535);
+    const dim3 grid((unsigned)a.I, (unsigned)((a.O + 31) / 32), (unsigned)bz);
+    if (br) ferro_full_bwd_kernel<true><<<grid, FF_THREADS, 0, st>>>(a);
+    else ferro_full_bwd_kernel<false><<<grid, FF_THREADS, 0, st>>>(a);
     return FETODE_LAUNCH_RC();
 }

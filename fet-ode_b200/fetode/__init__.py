@@ -11,13 +11,15 @@ All arithmetic runs in fetode/libfetode.so (C ABI: include/fetode.h); there is n
 """
 from . import _lib  # noqa: F401
 from .efficientkan import KAN, KANFET, KANLinear, LogisticBasis  # noqa: F401
-from .ferro_class import (BatchedFerroelectricBasis, FerroelectricBasis, NoisyBatchedFerroelectricBasis,  # noqa: F401
+from .ferro_class import (BatchedFerroelectricBasis, FerroelectricBasis, FerroelectricBasisConv2d,  # noqa: F401
+                          MemEfficient_FerroelectricBasisConv2d, NoisyBatchedFerroelectricBasis,
                           NoisyFerroelectricBasis, TwoDimensionFerroelectricBasis)
 from . import compat, ecg, graphs, mnist_kuramoto_kan, optim  # noqa: F401
 from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odeint,  # noqa: F401
                      odeint_rk4)
 
 __all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "FerroelectricBasis",
-           "NoisyFerroelectricBasis", "BatchedFerroelectricBasis", "NoisyBatchedFerroelectricBasis", "ecg",
+           "NoisyFerroelectricBasis", "BatchedFerroelectricBasis", "NoisyBatchedFerroelectricBasis",
+           "FerroelectricBasisConv2d", "MemEfficient_FerroelectricBasisConv2d", "ecg",
            "mnist_kuramoto_kan", "optim", "graphs", "compat", "odeint",
            "integrate_euler", "integrate_rk2", "integrate_rk4", "odeint_rk4", "as_rhs"]

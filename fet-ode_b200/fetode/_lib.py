@@ -114,3 +114,7 @@ def f32c(t: torch.Tensor) -> torch.Tensor:
     if t.dtype != torch.float32:
         t = t.float()
     return t.contiguous()
+
+
+class Conv2d(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("Cin", "H", "W", "kH", "kW", "stride", "padding", "Hout", "Wout")]

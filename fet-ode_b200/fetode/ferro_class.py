@@ -251,3 +251,107 @@ class NoisyBatchedFerroelectricBasis(BatchedFerroelectricBasis):
 
     def __init__(self, in_dim, out_dim, num_basis, use_noise=True, gate_slope=10.0, alpha=0.8, noise_std=0.2):
         super().__init__(in_dim, out_dim, num_basis, use_noise, gate_slope, alpha, noise_std)
+
+
+class FerroelectricBasisConv2d(nn.Module):
+    """ferro_class.py:601-779: the ferroelectric neuron over the kH x kW patches of an image.
+
+    Same constructor arguments and parameter names / shapes ([Cout, Cin, K, kH, kW], ``out_bias`` [Cout]) as the
+    reference.  One kernel launch gathers the patches from the image (implicit im2col, zero padding) -- neither
+    ``F.unfold``'s (B, Cin*kH*kW, L) matrix nor the (B,Cout,Cin,K,kH,kW,L) broadcast exists in HBM.
+    State: stateless by default (prev = x, branch = +1 on every call, :724-727).  ``stateful=True`` keeps the previous
+    IMAGE (the reference keeps its unfolded expansion) and, for this class, the branch momentum; as in the reference
+    (whose branch buffer has no Cout axis, :686 vs :767) that only works for ``out_channels == 1`` and raises
+    RuntimeError otherwise."""
+
+    _mem_efficient = False
+
+    def __init__(self, in_channels, out_channels, kernel_size, num_basis=3, stride=1, padding=0, use_noise=False,
+                 noise_std=0.2, gate_slope=10.0, alpha=0.8, stateful=False):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.kernel_size = kernel_size if isinstance(kernel_size, tuple) else (kernel_size, kernel_size)
+        self.num_basis, self.stride, self.padding = num_basis, stride, padding
+        self.use_noise, self.noise_std = use_noise, noise_std
+        self.gate_slope, self.alpha, self.stateful = gate_slope, alpha, stateful
+        kH, kW = self.kernel_size
+        shape = (out_channels, in_channels, num_basis, kH, kW)
+        self.k = nn.Parameter(torch.rand(*shape) * 2.0 + 0.5)
+        self.Ec = nn.Parameter(torch.rand(*shape) * 2.0 + 0.5)
+        self.Ps = nn.Parameter(torch.rand(*shape) * 1.5 + 0.5)
+        self.bias = nn.Parameter(torch.randn(*shape) * 0.1)
+        self.coef = nn.Parameter(torch.randn(*shape))
+        self.out_bias = nn.Parameter(torch.zeros(out_channels))
+        self.register_buffer("_prev_x", torch.zeros(1))          # compact: the previous image once stateful
+        self.register_buffer("_branch_sign", torch.ones(1))      # [B*L, Cin*kH*kW, Cout, K] once stateful (plain class)
+        self._state_ready = False
+
+    def reset_state(self):
+        self._state_ready = False
+
+    def _kernel_params(self):
+        """[Cout, Cin, K, kH, kW] -> [(Cin, kH, kW), Cout, K]: layout only, autograd carries the gradients back."""
+        I = self.in_channels * self.kernel_size[0] * self.kernel_size[1]
+        return [p.permute(1, 3, 4, 0, 2).reshape(I, self.out_channels, self.num_basis).contiguous()
+                for p in (self.k, self.Ec, self.Ps, self.bias, self.coef)]
+
+    def forward(self, x, return_activations=False):
+        from ._lib import Conv2d
+        ops.abort_if_tracing()
+        B, Cin, H, W = x.shape
+        assert Cin == self.in_channels
+        kH, kW = self.kernel_size
+        x = ops.f32c(x)
+        g = Conv2d(Cin, H, W, kH, kW, self.stride, self.padding,
+                   (H + 2 * self.padding - kH) // self.stride + 1, (W + 2 * self.padding - kW) // self.stride + 1)
+        L = g.Hout * g.Wout
+        I, O, K = Cin * kH * kW, self.out_channels, self.num_basis
+        prev, br, mode = None, None, 2
+        track_br = self.stateful and not self._mem_efficient
+        if self.stateful:
+            if track_br and O != 1:
+                raise RuntimeError(f"output with shape {[B, 1, Cin, K, kH, kW, L]} doesn't match the broadcast shape "
+                                   f"{[B, O, Cin, K, kH, kW, L]} (the reference's stateful branch buffer has no Cout axis)")
+            ready = self._state_ready and tuple(self._prev_x.shape) == tuple(x.shape) and self._prev_x.device == x.device
+            if ready:
+                prev, mode = self._prev_x, 0
+                br = self._branch_sign if track_br else None
+        noisy = self.use_noise and self.noise_std != 0.0
+        want_basis = (return_activations and not self._mem_efficient) or noisy
+        cfg = dict(geom=g, I=I, O=O, K=K, gate_slope=float(self.gate_slope), alpha=float(self.alpha), prev_mode=mode,
+                   want_basis=want_basis, want_br_out=track_br, br_momentum=True)
+        out = ops.FerroConvFn.apply(cfg, prev, br, x, *self._kernel_params(), self.out_bias)
+        side = cfg["side"]
+        basis = side["basis"]
+        if noisy:
+            # basis + noise.detach() (:753-755): the noise reaches the output through coef only
+            noise = torch.randn_like(basis) * self.noise_std
+            coef_k = self._kernel_params()[4]
+            out = out + (noise * coef_k).sum(dim=(1, 3)).view(B, L, O).permute(0, 2, 1).reshape(B, O, g.Hout, g.Wout)
+            basis = basis + noise
+        if self.stateful:
+            self._prev_x = x.detach().clone()
+            if track_br:
+                self._branch_sign = side["br_out"]
+            self._state_ready = True
+        if return_activations:
+            if self._mem_efficient:
+                return out, None, None
+            # [B*L, (Cin,kH,kW), Cout, K] -> the reference's (B, Cout, Cin, K, kH, kW, L)
+            b7 = basis.detach().view(B, L, Cin, kH, kW, O, K).permute(0, 5, 2, 6, 3, 4, 1)
+            return out, b7, self.coef.detach().unsqueeze(0).unsqueeze(-1)
+        return out
+
+
+class MemEfficient_FerroelectricBasisConv2d(FerroelectricBasisConv2d):
+    """ferro_class.py:783-944: the same function evaluated in Cout chunks by the reference; here it IS the same
+    kernel (nothing is materialised to begin with, so ``out_chunk`` is accepted and ignored).  Stateful mode keeps the
+    previous image only: the reference's Cout-free branch buffer stays +1 (:927-931)."""
+
+    _mem_efficient = True
+
+    def __init__(self, in_channels, out_channels, kernel_size, num_basis=3, stride=1, padding=0, use_noise=False,
+                 noise_std=0.05, gate_slope=10.0, alpha=0.8, stateful=False, out_chunk=8):
+        super().__init__(in_channels, out_channels, kernel_size, num_basis, stride, padding, use_noise, noise_std,
+                         gate_slope, alpha, stateful)
+        self.out_chunk = out_chunk

@@ -714,3 +714,60 @@ class KuramotoFn(torch.autograd.Function):
 
 def kuramoto_apply(x, K, omega, H, W, steps, dt):
     return KuramotoFn.apply(x, K, omega, int(H), int(W), int(steps), float(dt))
+
+
+# --------------------------------------------------------------------------------------
+# FerroelectricBasisConv2d (csrc/ferro.cu, implicit im2col around the FULL neuron kernel)
+# --------------------------------------------------------------------------------------
+class FerroConvFn(torch.autograd.Function):
+    """One call of the convolutional ferroelectric neuron.  Parameters arrive in the kernel layout [Cin*kH*kW, Cout, K]
+    (the module permutes the reference's [Cout, Cin, K, kH, kW] with torch views: layout only).  ``prev`` (previous
+    image) and ``br`` are constants of the graph (ferro_class.py:719-722 detaches the snapshots)."""
+
+    @staticmethod
+    def forward(ctx, cfg, prev, br, x, k, Ec, Ps, bias, coef, out_bias):
+        _require_cuda(x, "input")
+        B = x.shape[0]
+        g = cfg["geom"]
+        L = g.Hout * g.Wout
+        I, O, K = cfg["I"], cfg["O"], cfg["K"]
+        out = torch.empty(B, O, g.Hout, g.Wout, dtype=torch.float32, device=x.device)
+        rows = B * L
+        basis = torch.empty(rows, I, O, K, dtype=torch.float32, device=x.device) if cfg.get("want_basis") else None
+        br_out = torch.empty(rows, I, O, K, dtype=torch.float32, device=x.device) if cfg.get("want_br_out") else None
+        if br_out is not None and br is None:
+            br = torch.ones(rows, I, O, K, dtype=torch.float32, device=x.device)
+        s = _ferro_struct(dict(variant=FERRO_FULL, I=I, O=O, K=K, gate_slope=cfg["gate_slope"], alpha=cfg["alpha"]),
+                          k, Ec, Ps, bias, coef)
+        ob = None if out_bias is None else f32c(out_bias.detach())
+        if B > 0:
+            check(lib().fetode_ferro_conv2d_fwd(C.byref(s), C.byref(g), ptr(x), ptr(prev), C.c_int(cfg["prev_mode"]),
+                                                ptr(br), ptr(ob), ptr(out), ptr(basis), ptr(br_out),
+                                                C.c_int(1 if cfg.get("br_momentum") else 0), C.c_int64(B), stream()),
+                  "ferro_conv2d_fwd")
+        cfg["side"] = dict(basis=basis, br_out=br_out)
+        ctx.cfg, ctx.prev, ctx.br = cfg, prev, br
+        ctx.has_bias = out_bias is not None
+        ctx.save_for_backward(x, k, Ec, Ps, bias, coef)
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, k, Ec, Ps, bias, coef = ctx.saved_tensors
+        cfg = ctx.cfg
+        gout = f32c(gout)
+        B = x.shape[0]
+        s = _ferro_struct(dict(variant=FERRO_FULL, I=cfg["I"], O=cfg["O"], K=cfg["K"], gate_slope=cfg["gate_slope"],
+                               alpha=cfg["alpha"]), k, Ec, Ps, bias, coef)
+        g = _lib.FerroGrads()
+        grads = []
+        for idx, (name, t) in enumerate((("k", k), ("Ec", Ec), ("Ps", Ps), ("bias", bias), ("coef", coef))):
+            gt = torch.zeros(t.shape, dtype=torch.float32, device=x.device) if ctx.needs_input_grad[4 + idx] else None
+            setattr(g, name, ptr(gt).value)
+            grads.append(gt)
+        gob = torch.zeros(cfg["O"], dtype=torch.float32, device=x.device) if (ctx.has_bias and ctx.needs_input_grad[9]) else None
+        gx = torch.empty_like(x) if ctx.needs_input_grad[3] else None
+        check(lib().fetode_ferro_conv2d_bwd(C.byref(s), C.byref(cfg["geom"]), ptr(x), ptr(ctx.prev),
+                                            C.c_int(cfg["prev_mode"]), ptr(ctx.br), ptr(gout), ptr(gx), C.byref(g),
+                                            ptr(gob), C.c_int64(B), stream()), "ferro_conv2d_bwd")
+        return (None, None, None, gx, *grads, gob)

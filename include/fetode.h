@@ -259,6 +259,28 @@ FETODE_API int fetode_ferro_bwd_fused(const fetode_ferro_t* F, const float* x, c
                      const float* br, const float* gout, const float* yout, float* gx,
                      const fetode_ferro_grads_t* grads, int64_t B, void* stream);
 
+/* ---- FerroelectricBasisConv2d / MemEfficient_FerroelectricBasisConv2d (ferro_class.py:601-779, :783-944) ----------
+ * The same neuron applied to the kH x kW patches of an image, WITHOUT materialising F.unfold's (B, Cin*kH*kW, L)
+ * matrix (:699-703) or the (B,Cout,Cin,K,kH,kW,L) broadcast (:712-722): the kernel gathers each patch element from the
+ * image (zero padding) -- an implicit im2col around fetode_ferro_fwd's FULL variant.
+ * F: variant FULL, in_dim = Cin*kH*kW ordered (channel, ky, kx), out_dim = Cout, parameters laid out [in_dim, Cout, K]
+ *    (the reference's [Cout, Cin, K, kH, kW] permuted by the caller).
+ * x, prev, gx: images [B, Cin, H, W]; out, gout: [B, Cout, Hout*Wout]; out_bias [Cout] or NULL (:773).
+ * prev_mode: 2 = stateless call, prev == x (:724-727, the default); 0 = stateful, prev = the previous image; 1 = zeros.
+ * br / br_out: [B*L, in_dim, Cout, K] branch state of the stateful plain class (NULL = +1 everywhere);
+ * br_momentum != 0 stores branch_momentum (:763-767) rather than target_sign. */
+typedef struct fetode_conv2d {
+    int32_t Cin, H, W, kH, kW, stride, padding, Hout, Wout;
+} fetode_conv2d_t;
+FETODE_API int fetode_ferro_conv2d_fwd(const fetode_ferro_t* F, const fetode_conv2d_t* G, const float* x,
+                     const float* prev, int prev_mode, const float* br, const float* out_bias, float* out,
+                     float* basis_out /* [B*L, in_dim, Cout, K] or NULL */, float* br_out, int br_momentum,
+                     int64_t B, void* stream);
+FETODE_API int fetode_ferro_conv2d_bwd(const fetode_ferro_t* F, const fetode_conv2d_t* G, const float* x,
+                     const float* prev, int prev_mode, const float* br, const float* gout,
+                     float* gx /* image, overwritten, or NULL */, const fetode_ferro_grads_t* grads /* accumulated */,
+                     float* g_out_bias /* [Cout] accumulated, or NULL */, int64_t B, void* stream);
+
 /* ---- Kuramoto lattice -----------------------------------------------------------------
  * Kuramoto2D.forward mnist_kuramoto_kan.py:175-204: x [B,H*W] in [0,1] -> feat [B, 2*H*W]
  * = [cos(theta), sin(theta)] after `steps` Euler steps.  K: device scalar, omega: [H*W].

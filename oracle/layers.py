@@ -161,6 +161,67 @@ def ferro_full_forward(x: Tensor, p: Params, st: FerroFullState, *, gate_slope=1
     return out
 
 
+class FerroConvState:
+    """_prev_x / _branch_sign / _state_ready of FerroelectricBasisConv2d (ferro_class.py:666-687) and of
+    MemEfficient_FerroelectricBasisConv2d (:826-838): shape-checked, re-created as prev = x_exp, br = 1."""
+
+    def __init__(self):
+        self.prev = None
+        self.br = None
+
+    def reset(self):
+        self.prev = self.br = None
+
+
+def ferro_conv2d_forward(x: Tensor, p: Params, st: Optional[FerroConvState] = None, *, stride=1, padding=0,
+                         gate_slope=10.0, alpha=0.8, stateful=False, mem_efficient=False, return_basis=False):
+    """FerroelectricBasisConv2d.forward (ferro_class.py:689-779) / MemEfficient_...forward (:840-944).
+
+    x: [B, Cin, H, W]; params k, Ec, Ps, bias, coef: [Cout, Cin, K, kH, kW]; out_bias [Cout] -> [B, Cout, Hout, Wout].
+    Stateless (default, :724-727): prev = x_exp (dx = 0), branch = +1.  Stateful: prev <- x_exp after the call; the plain
+    class also stores branch <- branch_momentum (:763-767) over the full (B,Cout,Cin,K,kH,kW,L) shape, the
+    memory-efficient class keeps its Cout-free branch buffer at +1 (:927-931).  The plain class's stateful mode
+    only runs for Cout == 1 (its branch buffer has no Cout axis; see the raise below)."""
+    B, Cin, H, W = x.shape
+    Cout, _, K, kH, kW = p["k"].shape
+    xu = F.unfold(x, kernel_size=(kH, kW), padding=padding, stride=stride)
+    L = xu.shape[-1]
+    x_exp = xu.view(B, Cin, kH, kW, L).unsqueeze(2).expand(-1, -1, K, -1, -1, -1).unsqueeze(1)   # (B,1,Cin,K,kH,kW,L)
+    q = {n: p[n].unsqueeze(0).unsqueeze(-1) for n in ("k", "Ec", "Ps", "bias", "coef")}
+    if stateful:
+        assert st is not None
+        if st.prev is None or st.prev.shape != x_exp.shape or st.prev.dtype != x_exp.dtype:
+            st.prev = x_exp.detach().clone()
+            st.br = torch.ones_like(x_exp).detach()           # (B,1,...): no Cout axis in either class (:686, :837)
+        prev, br = st.prev.detach().clone(), st.br.detach().clone()
+    else:
+        prev, br = x_exp.detach().clone(), torch.ones_like(x_exp).detach()
+    dx = x_exp - prev
+    up = torch.sigmoid(gate_slope * dx)
+    cpos = torch.sigmoid(gate_slope * (x_exp - q["Ec"]))
+    cneg = torch.sigmoid(gate_slope * (-x_exp - q["Ec"]))
+    to_upper = up * cpos
+    to_lower = (1.0 - up) * cneg
+    tgt = to_upper * 1.0 + to_lower * (-1.0) + (1.0 - to_upper - to_lower) * br
+    mom = alpha * br + (1.0 - alpha) * tgt
+    basis = q["Ps"] * torch.tanh(q["k"] * (x_exp + q["Ec"] * mom)) + q["bias"]
+    out = (basis * q["coef"]).sum(dim=(2, 3, 4, 5))
+    if stateful:
+        st.prev = x_exp.detach().clone()
+        if not mem_efficient:
+            # the reference does _branch_sign.copy_(branch_momentum) (:767) into the Cout-free buffer: this only
+            # broadcasts for Cout == 1 and raises RuntimeError otherwise -- restated as is
+            if mom.shape != st.br.shape:
+                raise RuntimeError(f"output with shape {list(st.br.shape)} doesn't match the broadcast shape {list(mom.shape)}")
+            st.br = mom.detach().clone()
+    Hout = (H + 2 * padding - kH) // stride + 1
+    Wout = (W + 2 * padding - kW) // stride + 1
+    out = out.view(B, Cout, Hout, Wout) + p["out_bias"].view(1, -1, 1, 1)
+    if return_basis:
+        return out, basis.detach()
+    return out
+
+
 class Ferro2DState:
     """TwoDimensionFerroelectricBasis buffers (ferro_class.py:544-545): prev [1,I,K] zeros
     which *broadcast* on the first call (prev=0) and are re-created as [B,I,K] afterwards

@@ -107,3 +107,26 @@ def test_update_grid_and_regularization_loss_against_reference_vectors():
     knots, coef = OL.update_grid(g["x"], p, margin=0.01)
     assert torch.equal(knots, g["grid_after"])
     assert torch.allclose(coef, g["spline_weight_after"], rtol=1e-4, atol=1e-6)
+
+
+def test_ferro_conv2d_against_reference_vectors():
+    """oracle.layers.ferro_conv2d_forward (ferro_class.py:689-779, :840-944) against the vectors the live reference
+    classes produced (oracle/make_golden_conv.py): stateless calls, true-hysteresis sequences, and the plain class's
+    stateful failure for Cout > 1."""
+    import pytest
+    from conftest import load_golden, max_rel
+    from oracle import layers as OL
+    for tag, kw, me in (("plain_s1p1", dict(stride=1, padding=1), False),
+                        ("plain_s2p0_c1", dict(stride=2, padding=0), False),
+                        ("memeff_s1p1", dict(stride=1, padding=1), True)):
+        p, d = load_golden("ferroconv_" + tag)
+        for i in (0, 1):
+            assert max_rel(OL.ferro_conv2d_forward(d[f"x{i}"], p, mem_efficient=me, **kw), d[f"stateless{i}"]) < 1e-6
+        st = OL.FerroConvState()
+        if "stateful0" in d:
+            for i in range(3):
+                got = OL.ferro_conv2d_forward(d[f"x{i}"], p, st, stateful=True, mem_efficient=me, **kw)
+                assert max_rel(got, d[f"stateful{i}"]) < 1e-6, (tag, i)
+        else:
+            with pytest.raises(RuntimeError):
+                OL.ferro_conv2d_forward(d["x0"], p, st, stateful=True, **kw)
