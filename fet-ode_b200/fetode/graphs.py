@@ -106,3 +106,75 @@ class GraphedTrainStep:
         # EAGER call, e.g. a validation pass between replays
         torch.autograd.graph.increment_version(self._params)
         return self.loss
+
+
+def _ferro_holders(modules):
+    """(module, attribute) pairs that hold hysteresis state tensors: ferro_class neurons (``_rows``) and the hard-gated
+    basis (``_row``)."""
+    out = []
+    for root in modules:
+        for m in root.modules():
+            if hasattr(m, "_rows") and hasattr(m, "_set_rows"):
+                out.append((m, "_rows"))
+            elif hasattr(m, "_row") and hasattr(m, "branch_breaking_point"):
+                out.append((m, "_row"))
+    return out
+
+
+class GraphedCall:
+    """``out = fn(*inputs)`` under ``torch.no_grad()``, captured ONCE into a CUDA graph and replayed: the launch-bound
+    loops around the hot path (the 250 reverse-diffusion steps of ``p_sample_loop`` over the KANFET stack,
+    kan_diffusion_ett.py:565-609, ~40 launches each) cost one graph launch per iteration.
+
+    The hysteresis state of every stateful neuron under ``modules`` is carried from replay to replay exactly as the
+    eager sequence carries it: the captured call reads the state tensors that exist after the warm-up calls, and their
+    new values are copied back into those tensors inside the graph.  ``reset_state()`` zero-fills them (== the modules'
+    own reset: a zero previous input is what a fresh buffer means)."""
+
+    def __init__(self, fn: Callable, inputs, modules=(), warmup: int = 2):
+        self.inputs = [t.clone() for t in inputs]
+        if not all(t.is_cuda for t in self.inputs):
+            raise RuntimeError("GraphedCall: inputs must live on a CUDA device (there is no CPU path)")
+        self.fn = fn
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):
+                fn(*self.inputs)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.holders = _ferro_holders(modules)
+        start = []
+        for m, attr in self.holders:
+            t = getattr(m, attr)
+            if t is None:
+                raise RuntimeError("GraphedCall: a stateful neuron under `modules` was not called by fn during warm-up")
+            start.append(t)
+        self.state = start
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.out = fn(*self.inputs)
+            for (m, attr), r0 in zip(self.holders, start):
+                r0.copy_(getattr(m, attr))
+        self._rebind()
+        self.replays = 0
+
+    def _rebind(self):
+        for (m, attr), r0 in zip(self.holders, self.state):
+            if attr == "_rows":
+                m._set_rows(r0)
+            else:
+                m._row = r0
+                m.prev_x = r0.view(1, -1, 1).expand(1, m.in_dim, m.num_basis)
+
+    def reset_state(self):
+        for r0 in self.state:
+            r0.zero_()
+
+    def __call__(self, *inputs):
+        for dst, src in zip(self.inputs, inputs):
+            if src is not dst:
+                dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        self.replays += 1
+        return self.out

@@ -281,6 +281,21 @@ FETODE_API int fetode_ferro_conv2d_bwd(const fetode_ferro_t* F, const fetode_con
                      float* gx /* image, overwritten, or NULL */, const fetode_ferro_grads_t* grads /* accumulated */,
                      float* g_out_bias /* [Cout] accumulated, or NULL */, int64_t B, void* stream);
 
+/* ---- logistic-KAN recurrent encoder ------------------------------------------------------------------------------
+ * FullyNonlinearKANCell.forward (train_kan_fet_ett.py:791-796; same cell train_ecg.py:203-217) applied T times
+ * (KANRNNEncoder.forward :810-815; T = 1 is the bare cell): h_t = sigmoid([LogisticBasis_in(x_t) | LogisticBasis_h(h_{t-1})])[:, :H].
+ * x [B,T,F]; h0 [B,H] or NULL (zeros); a_in,b_in [F,nb]; a_h,b_h [H,nb]; h_out [B,H] = h_T.
+ * hist [T+1,B,H] (h_0..h_T) is needed by the backward only when H > F*nb (some kept column reads h_{t-1}); otherwise
+ * h_T depends on x[:, T-1] alone and one step is evaluated.  bwd: g_x [B,T,F] must be zero-filled by the caller;
+ * g_h0 (or NULL) overwritten; parameter gradients accumulated. */
+FETODE_API int fetode_kanrnn_fwd(const float* x, const float* h0, const float* a_in, const float* b_in,
+                     const float* a_h, const float* b_h, float* h_out, float* hist /* or NULL */, int64_t B,
+                     int32_t T, int32_t F, int32_t H, int32_t nb, void* stream);
+FETODE_API int fetode_kanrnn_bwd(const float* x, const float* a_in, const float* b_in, const float* a_h,
+                     const float* b_h, const float* hist, const float* g_h, float* g_x /* or NULL */,
+                     float* g_h0 /* or NULL */, float* g_a_in, float* g_b_in, float* g_a_h, float* g_b_h, int64_t B,
+                     int32_t T, int32_t F, int32_t H, int32_t nb, void* stream);
+
 /* ---- Kuramoto lattice -----------------------------------------------------------------
  * Kuramoto2D.forward mnist_kuramoto_kan.py:175-204: x [B,H*W] in [0,1] -> feat [B, 2*H*W]
  * = [cos(theta), sin(theta)] after `steps` Euler steps.  K: device scalar, omega: [H*W].

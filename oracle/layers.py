@@ -369,6 +369,27 @@ def kanfet_ode_rhs(h: Tensor, p1: Params, p2: Params, s1: FerroFullState, s2: Fe
 
 
 # --------------------------------------------------------------------------------------
+# Logistic-KAN recurrent encoder  (train_kan_fet_ett.py:741-818)
+# --------------------------------------------------------------------------------------
+def kan_rnn_cell(x_t: Tensor, h_prev: Tensor, p: Params) -> Tensor:
+    """FullyNonlinearKANCell.forward (train_kan_fet_ett.py:791-796).  p: input_basis.a/.b [F,nb], hidden_basis.a/.b [H,nb]."""
+    H = p["hidden_basis.a"].shape[0]
+    x_phi = logistic_basis(x_t, p["input_basis.a"], p["input_basis.b"]).view(x_t.size(0), -1)
+    h_phi = logistic_basis(h_prev, p["hidden_basis.a"], p["hidden_basis.b"]).view(h_prev.size(0), -1)
+    return torch.sigmoid(torch.cat([x_phi, h_phi], dim=1))[:, :H]
+
+
+def kan_rnn_encoder(x_ctx: Tensor, p: Params) -> Tensor:
+    """KANRNNEncoder.forward (train_kan_fet_ett.py:808-818).  p: rnn_cell.* (as kan_rnn_cell), to_latent.weight/.bias."""
+    cell = {k[len("rnn_cell."):]: v for k, v in p.items() if k.startswith("rnn_cell.")}
+    B, T, _ = x_ctx.shape
+    h = torch.zeros(B, cell["hidden_basis.a"].shape[0], dtype=x_ctx.dtype)
+    for t in range(T):
+        h = kan_rnn_cell(x_ctx[:, t, :], h, cell)
+    return F.linear(h, p["to_latent.weight"], p["to_latent.bias"])
+
+
+# --------------------------------------------------------------------------------------
 # Kuramoto lattice  (mnist_kuramoto_kan.py:175-204)
 # --------------------------------------------------------------------------------------
 def kuramoto_forward(x_img: Tensor, K: Tensor, omega: Tensor, steps: int = 10, dt: float = 0.15) -> Tensor:

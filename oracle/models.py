@@ -74,3 +74,27 @@ def lv_train_loss(layers, x0: torch.Tensor, target: torch.Tensor, t1: float, n_s
     f = lambda t, h: OL.kan_forward(h, layers, branch=branch, states=states)
     pred = OS.rk4_classic(f, x0, 0.0, t1, n_steps, trajectory=True)
     return ((pred - target) ** 2).mean()
+
+
+def p_sample_loop(model, past, schedule_tensors, pred_len, d_in, noise):
+    """kan_diffusion_ett.py:565-609 restated with the noise made explicit: noise[0] is the initial y (:576), noise[1 + k]
+    the z drawn at the k-th iteration (ti = T-1-k, :602-603)."""
+    betas, alphas, abar, _sa, _s1 = schedule_tensors
+    T = betas.shape[0]
+    B = past.shape[0]
+    y = noise[0].clone()
+    for k, ti in enumerate(reversed(range(T))):
+        t = torch.full((B,), ti, dtype=torch.long)
+        eps_hat = model(y, past, t)
+        a_bar = abar[ti]
+        sqrt_a_bar = torch.sqrt(a_bar)
+        sqrt_1m_a_bar = torch.sqrt(1.0 - a_bar)
+        y0_hat = (y - sqrt_1m_a_bar * eps_hat) / (sqrt_a_bar + 1e-8)
+        beta_t, alpha_t = betas[ti], alphas[ti]
+        a_bar_prev = abar[ti - 1] if ti > 0 else torch.tensor(1.0)
+        beta_tilde = beta_t * (1.0 - a_bar_prev) / (1.0 - a_bar + 1e-8)
+        coef1 = (torch.sqrt(a_bar_prev) * beta_t) / (1.0 - a_bar + 1e-8)
+        coef2 = (torch.sqrt(alpha_t) * (1.0 - a_bar_prev)) / (1.0 - a_bar + 1e-8)
+        mean = coef1 * y0_hat + coef2 * y
+        y = mean + torch.sqrt(beta_tilde + 1e-8) * noise[1 + k] if ti > 0 else mean
+    return y

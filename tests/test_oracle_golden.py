@@ -130,3 +130,15 @@ def test_ferro_conv2d_against_reference_vectors():
         else:
             with pytest.raises(RuntimeError):
                 OL.ferro_conv2d_forward(d["x0"], p, st, stateful=True, **kw)
+
+
+def test_kan_rnn_encoder_against_reference_vectors():
+    """oracle.layers.kan_rnn_cell / kan_rnn_encoder (train_kan_fet_ett.py:780-818) against the live reference's
+    outputs (oracle/make_golden_rnn.py), including the recurrent regime H > F*nb."""
+    from conftest import load_golden, max_rel
+    from oracle import layers as OL
+    for tag in ("script_7_10_64", "recurrent_3_4_20"):
+        p, d = load_golden("kanrnn_" + tag)
+        assert max_rel(OL.kan_rnn_encoder(d["x"], p), d["z0"]) < 1e-6
+        cell = {k[len("rnn_cell."):]: v for k, v in p.items() if k.startswith("rnn_cell.")}
+        assert max_rel(OL.kan_rnn_cell(d["x"][:, 0, :], d["h_prev"], cell), d["cell"]) < 1e-6
