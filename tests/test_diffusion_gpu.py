@@ -20,8 +20,13 @@ def _schedule(T, device=None):
     return tuple(t.to(device) for t in ts) if device is not None else ts
 
 
+_FREQ = {}
+
+
 def _temb(t):
-    f = torch.tensor([0.1, 0.37, 0.9, 1.7], device=t.device)
+    f = _FREQ.get(t.device)                                  # built once per device: no H2D copy inside a captured step
+    if f is None:
+        f = _FREQ[t.device] = torch.tensor([0.1, 0.37, 0.9, 1.7], device=t.device)
     return torch.sin(t.float().unsqueeze(1) * f)
 
 
@@ -56,6 +61,7 @@ def test_graphed_sampler_equals_eager_and_oracle(cuda):
     with torch.no_grad():
         want = OM.p_sample_loop(model_cpu, past, _schedule(T), pred_len, d_in, noise)
     sched = _schedule(T, cuda)
+    _temb(torch.zeros(1, dtype=torch.long, device=cuda))
     for n in nets:
         n.reset_state()
     eager = fetode.diffusion.p_sample_loop(model, past.to(cuda), sched, pred_len, d_in, graphed=False,
