@@ -205,15 +205,91 @@ def mnist_train(B, skip_cpu):
             "image_steps_per_s": B / ms * 1e3, "gpu_fwd_bwd_graph_ms": gl, "graph_image_steps_per_s": B / gl * 1e3}
 
 
+def ett_rnn_encoder(B, skip_cpu):
+    """Config 4, "KAN-FET" variant: KANRNNEncoder(7 features, hidden 64, latent 64, nb 10) over a 336-step context
+    (train_kan_fet_ett.py:799-818) -- one launch per direction instead of 336 cell calls."""
+    from fetode import ett
+    from oracle import layers as OL
+    torch.manual_seed(0)
+    enc = ett.KANRNNEncoder(7, 64, 64, 10)
+    p = {k: v.detach().clone() for k, v in enc.state_dict().items()}
+    enc = enc.to(DEV)
+    x = torch.randn(B, 336, 7, device=DEV)
+
+    def step():
+        enc.zero_grad(set_to_none=True)
+        enc(x).square().mean().backward()
+
+    def fwd():
+        with torch.no_grad():
+            enc(x)
+    out = {"config": f"4: ETT KANRNNEncoder(F=7, hidden 64, latent 64, nb 10), context 336 (train_kan_fet_ett.py:799-818), B={B}",
+           "gpu_fwd_ms": gpu_ms(fwd), "gpu_fwd_bwd_ms": gpu_ms(step)}
+    if not skip_cpu:
+        Bc = min(B, 64)
+        xc = x[:Bc].cpu()
+
+        def cfwd():
+            with torch.no_grad():
+                OL.kan_rnn_encoder(xc, p)
+        ms = cpu_ms(cfwd)
+        out.update(cpu_fwd_ms=ms, cpu_rows=Bc, cpu_cores=os.cpu_count())
+    return out
+
+
+def kanfet_stack_sampler(B, skip_cpu):
+    """Config 4: the 250-step reverse-diffusion loop over KANFET([928,256]) -> ([256,256]) -> ([256,672])
+    (kan_diffusion_ett.py:421-425, 565-609; pred_len 96 x 7 channels, cond 128 + time 128 = 928 inputs), one CUDA-graph
+    replay per step against the eager loop."""
+    torch.manual_seed(0)
+    pred_len, d_in, T = 96, 7, 250
+    nets = torch.nn.ModuleList([fetode.KANFET([928, 256]), fetode.KANFET([256, 256]), fetode.KANFET([256, 672])]).to(DEV)
+    cond = torch.randn(B, 128, device=DEV)
+    freq = torch.exp(torch.arange(64, device=DEV) * (-9.21 / 64))
+
+    def model(y, past, t):
+        ang = t.float().unsqueeze(1) * freq
+        h = torch.cat([y.reshape(B, -1), cond, torch.sin(ang), torch.cos(ang)], dim=1)
+        for n in nets:
+            h = n(h)
+        return h.reshape(B, pred_len, d_in)
+    betas = torch.linspace(1e-4, 0.02, T, device=DEV)
+    alphas = 1.0 - betas
+    abar = torch.cumprod(alphas, 0)
+    sched = (betas, alphas, abar, abar.sqrt(), (1 - abar).sqrt())
+    past = torch.randn(B, 336, d_in, device=DEV)
+
+    def run(graphed):
+        for n in nets:
+            n.reset_state()
+        return fetode.diffusion.p_sample_loop(model, past, sched, pred_len, d_in, graphed=graphed, modules=[nets])
+    out = {"config": f"4: DDPM p_sample_loop x {T} over the KANFET 928->256->256->672 stack (kan_diffusion_ett.py:421-425, 565-609), B={B}"}
+    out["gpu_eager_ms"] = gpu_ms(lambda: run(False), iters=2, warm=1)
+    out["gpu_graphed_ms"] = gpu_ms(lambda: run(True), iters=2, warm=1)        # includes the one-off capture
+    out["gpu_graphed_ms_per_step"] = out["gpu_graphed_ms"] / T
+    out["finite"] = bool(torch.isfinite(run(True)).all())
+    return out
+
+
+def _commit():
+    import subprocess
+    try:
+        return subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip() or None
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-cpu", action="store_true")
     a = ap.parse_args()
     torch.set_num_threads(os.cpu_count() or 1)
+    commit = os.environ.get("FETODE_COMMIT") or _commit()
     for fn, args in ((lv_train, (1,)), (lv_train, (65536,)), (ecg_train, (4096,)), (ett_encoder, (4096,)),
-                     (ett_encoder, (64,)), (mnist_train, (128,)), (mnist_train, (1024,))):
+                     (ett_encoder, (64,)), (ett_rnn_encoder, (64,)), (ett_rnn_encoder, (4096,)),
+                     (kanfet_stack_sampler, (64,)), (mnist_train, (128,)), (mnist_train, (1024,))):
         try:
-            print(json.dumps(fn(*args, a.skip_cpu)), flush=True)
+            print(json.dumps({"commit": commit, **fn(*args, a.skip_cpu)}), flush=True)
         except Exception as e:                      # keep going: this is a survey, not the contract bench
             print(json.dumps({"config": f"{fn.__name__}{args}", "error": repr(e)[:300]}), flush=True)
 
