@@ -13,6 +13,7 @@ for _p in (ROOT, os.path.join(ROOT, "fet-ode_b200")):
 import torch  # noqa: E402
 
 import fetode  # noqa: E402
+from fetode._lib import lib  # noqa: E402
 
 SHAPES = [("ecg_kan1", 4096, 768, 128, 10), ("ecg_kan2", 4096, 128, 128, 10), ("ett_enc1", 4096, 2352, 128, 10),
           ("ett_enc1_b64", 64, 2352, 128, 10), ("kanfet_928_256", 4096, 928, 256, 10)]
@@ -44,7 +45,7 @@ def main():
         out = {}
         with torch.no_grad():
             for mode in ("0", "1"):
-                os.environ["FETODE_TC"] = mode
+                lib().fetode_set_tc_mode(int(mode))
                 layer(x)
                 out["cuda_core_ms" if mode == "0" else "tcgen05_ms"] = timeit(lambda: layer(x))
         F = 1 + 8 + nb

@@ -190,12 +190,22 @@ static int kl_fwd_launch(const KLFwdArgs& a, cudaStream_t st) {
     return FETODE_LAUNCH_RC();
 }
 
-// rows from which the tensor-core kernel is used; FETODE_TC=0 disables it, FETODE_TC=1 forces it for any batch
+// rows from which the tensor-core kernel is used.  Mode: -1 auto (>= 64 rows), 0 never, 1 always; set with
+// fetode_set_tc_mode(), initialised ONCE from FETODE_TC (no getenv on the per-call path).
+static int g_tc_mode = -2;
 long long kl_tc_min_rows() {
-    const char* e = getenv("FETODE_TC");
-    if (e && e[0] == '0') return (1LL << 62);
-    if (e && e[0] == '1') return 1;
+    if (g_tc_mode == -2) {
+        const char* e = getenv("FETODE_TC");
+        g_tc_mode = (e && e[0] == '0') ? 0 : ((e && e[0] == '1') ? 1 : -1);
+    }
+    if (g_tc_mode == 0) return (1LL << 62);
+    if (g_tc_mode == 1) return 1;
     return 64;
+}
+int kl_set_tc_mode(int mode) {
+    if (mode < -1 || mode > 1) return FETODE_EINVAL;
+    g_tc_mode = mode;
+    return FETODE_OK;
 }
 
 int kl_check(const fetode_kanlayer_t* P) {
@@ -332,3 +342,5 @@ extern "C" int fetode_bspline_basis(const float* grid, const float* x, float* ou
     fetode::bspline_basis_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(grid, x, out, n, I, grid_size);
     return FETODE_LAUNCH_RC();
 }
+
+extern "C" int fetode_set_tc_mode(int mode) { return fetode::kl_set_tc_mode(mode); }

@@ -402,9 +402,10 @@ int kl_tc_fwd(const fetode_kanlayer_t* P, const KLLayout& L, const float* blob, 
     splits = std::min<long long>(splits, L.tc_units);
     a.units_per_split = (int)((L.tc_units + splits - 1) / splits);
     a.units_per_split = std::min(a.units_per_split, 6);        // bounds the accumulation chains (see the MMA loop)
-    if (const char* e = getenv("FETODE_TC_UPS")) {         // tuning / diagnostics: 32-input units per K split
-        const int v = atoi(e);
-        if (v >= 1) a.units_per_split = std::min(v, L.tc_units);
+    {
+        static int ups = -2;                                // tuning / diagnostics: 32-input units per K split; read once
+        if (ups == -2) { const char* e = getenv("FETODE_TC_UPS"); ups = e ? atoi(e) : -1; }
+        if (ups >= 1) a.units_per_split = std::min(ups, L.tc_units);
     }
     splits = (L.tc_units + a.units_per_split - 1) / a.units_per_split;
     if (splits > 1) {

@@ -94,6 +94,9 @@ typedef struct fetode_kanlayer_grads {
  * reset_state, ferro_class.py:544,594-596).  prev_out (NULL, or a buffer that does NOT alias prev)
  * receives x, the next call's prev (ferro_class.py:584-590).
  */
+/* Kernel selection for the wide path: -1 = automatic (tcgen05 from 64 rows up; the default, or FETODE_TC=0|1 read once at
+ * first use), 0 = CUDA-core kernels only, 1 = tcgen05 for any batch.  Process-wide; for tests and A/B timing. */
+FETODE_API int fetode_set_tc_mode(int mode);
 FETODE_API int64_t fetode_kanlinear_wcat_floats(const fetode_kanlayer_t* L);
 FETODE_API int fetode_kanlinear_pack(const fetode_kanlayer_t* L, float* wcat, void* stream);
 FETODE_API int fetode_kanlinear_fwd(const fetode_kanlayer_t* L, const float* wcat, const float* x,

@@ -24,14 +24,16 @@ def _layer(I, O, nb, branch, cuda, seed):
     return p, layer.to(cuda), gen
 
 
+def _tc_mode(mode):
+    from fetode._lib import check, lib
+    check(lib().fetode_set_tc_mode(int(mode)), "set_tc_mode")
+
+
 @pytest.fixture
 def force_tc():
-    old = os.environ.get("FETODE_TC")
-    os.environ["FETODE_TC"] = "1"
+    _tc_mode(1)
     yield
-    os.environ.pop("FETODE_TC", None)
-    if old is not None:
-        os.environ["FETODE_TC"] = old
+    _tc_mode(-1)
 
 
 @pytest.mark.parametrize("I,O,nb,branch,B", [
@@ -66,18 +68,15 @@ def test_tc_backward_equals_cuda_core_backward_at_ecg_size(cuda):
     x = (torch.randn(4096, 768, generator=gen) * 0.9).to(cuda)
     g = torch.randn(4096, 128, generator=gen).to(cuda)
     res = {}
-    old = os.environ.get("FETODE_TC")
     try:
         for mode in ("0", "1"):
-            os.environ["FETODE_TC"] = mode
+            _tc_mode(int(mode))
             layer.zero_grad()
             xs = x.clone().requires_grad_(True)
             (layer(xs) * g).sum().backward()
             res[mode] = (xs.grad.clone(), {n: t.grad.clone() for n, t in layer.named_parameters()})
     finally:
-        os.environ.pop("FETODE_TC", None)
-        if old is not None:
-            os.environ["FETODE_TC"] = old
+        _tc_mode(-1)
     assert max_rel(res["1"][0], res["0"][0]) < 5e-5
     for n in res["0"][1]:
         assert max_rel(res["1"][1][n], res["0"][1][n]) < 5e-5, n

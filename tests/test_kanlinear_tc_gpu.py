@@ -25,15 +25,16 @@ def _layer(I, O, nb, branch, cuda, seed):
     return p, layer.to(cuda), gen
 
 
+def _tc_mode(mode):
+    from fetode._lib import check, lib
+    check(lib().fetode_set_tc_mode(int(mode)), "set_tc_mode")
+
+
 @pytest.fixture
 def force_tc():
-    old = os.environ.get("FETODE_TC")
-    os.environ["FETODE_TC"] = "1"
+    _tc_mode(1)
     yield
-    if old is None:
-        os.environ.pop("FETODE_TC", None)
-    else:
-        os.environ["FETODE_TC"] = old
+    _tc_mode(-1)
 
 
 @pytest.mark.parametrize("I,O,nb,branch,B", [
@@ -66,17 +67,14 @@ def test_tc_equals_cuda_core_path_at_full_ecg_size(cuda):
     """B = 4096, 768 -> 128 (BASELINE configs[2] kan1): the two kernels agree to fp32 rounding, split-K included."""
     p, layer, gen = _layer(768, 128, 10, "logistic", cuda, 3)
     x = (torch.randn(4096, 768, generator=gen) * 0.9).to(cuda)
-    old = os.environ.get("FETODE_TC")
     try:
         with torch.no_grad():
-            os.environ["FETODE_TC"] = "0"
+            _tc_mode(0)
             ref = layer(x)
-            os.environ["FETODE_TC"] = "1"
+            _tc_mode(1)
             got = layer(x)
     finally:
-        os.environ.pop("FETODE_TC", None)
-        if old is not None:
-            os.environ["FETODE_TC"] = old
+        _tc_mode(-1)
     assert max_rel(got, ref) < 1e-5          # each path is within ~5e-6 of an fp64 evaluation
     # linearity in the rows: any row subset gives the same rows (tiles are independent)
     with torch.no_grad():
