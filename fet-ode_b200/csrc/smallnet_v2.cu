@@ -265,11 +265,18 @@ __device__ __forceinline__ float sn2_horner(const float4 c, float s) {
 // ------------------------------------------------------------------------------------------
 // one right-hand-side evaluation for the TP pairs of this lane
 // ------------------------------------------------------------------------------------------
-template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool UNI>
+// SPLIT = 2: two adjacent lanes share a pair of trajectories -- both evaluate the layer-1 features (2 of the 12 inputs of
+// a right-hand side), each owns H/2 hidden units (their layer-1 sums, layer-2 features and partial outputs), and the
+// partial outputs meet in one shuffle.  1.19x the instructions for twice the warps and a chain of 7 instead of 12
+// inputs per lane: the shape for batches too small to fill the SMs with one lane per pair (latency-bound regime).
+template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool UNI, int SPLIT>
 __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x2 (&ys)[D][TP], f32x2 (&prev1)[D][TP],
-                                        f32x2* colcur, const f32x2* colprev, f32x2 (&out)[D][TP]) {
+                                        f32x2* colcur, const f32x2* colprev, f32x2 (&out)[D][TP], const int sub) {
     constexpr SN2Layout L = sn2_layout(D, H, NB, G);
     constexpr int NK = L.NK;
+    constexpr int HS = H / SPLIT;
+    static_assert(H % SPLIT == 0, "hidden units must divide over the split lanes");
+    const int h0 = SPLIT > 1 ? sub * HS : 0;
     const float4 hdr = *reinterpret_cast<const float4*>(sm + L.hdr);
     // ---------------- layer 1: per input d, its features once, then a rolled loop over the H outputs; the partial
     // sums of output h travel through this thread's column (colcur[h]) between the two inputs
@@ -300,7 +307,8 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
         }
         const float4* tab = reinterpret_cast<const float4*>(sm + L.l1tab);
 #pragma unroll 2
-        for (int h = 0; h < H; ++h) {
+        for (int hh = 0; hh < HS; ++hh) {
+            const int h = h0 + hh;
             f32x2 acc[TP];
             if (d == 0) {
                 const f32x2 b = lds_pair(sm + L.b1 + 2 * h);
@@ -308,7 +316,7 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
                 for (int p = 0; p < TP; ++p) acc[p] = b;
             } else {
 #pragma unroll
-                for (int p = 0; p < TP; ++p) acc[p] = colcur[(h * TP + p) * THREADS];
+                for (int p = 0; p < TP; ++p) acc[p] = colcur[(hh * TP + p) * THREADS];
             }
             const float4* w4 = reinterpret_cast<const float4*>(blk + L.o_w1 + h * L.W1Q);
 #pragma unroll
@@ -326,7 +334,7 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
                 upk2(acc[p], lo, hi);
                 lo = fmaf(sn2_horner(tab[sp_m[2 * p] + h], sp_s[2 * p]), sp_k[2 * p], lo);
                 hi = fmaf(sn2_horner(tab[sp_m[2 * p + 1] + h], sp_s[2 * p + 1]), sp_k[2 * p + 1], hi);
-                colcur[(h * TP + p) * THREADS] = pk2(lo, hi);
+                colcur[(hh * TP + p) * THREADS] = pk2(lo, hi);
             }
         }
     }
@@ -336,19 +344,20 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
         const float4 b2 = *reinterpret_cast<const float4*>(sm + L.b2);
 #pragma unroll
         for (int p = 0; p < TP; ++p) {
-            out[0][p] = pk2(b2.x, b2.y);
-            if constexpr (D > 1) out[1][p] = pk2(b2.z, b2.w);
+            const bool first = SPLIT == 1 || sub == 0;               // the bias enters once
+            out[0][p] = first ? pk2(b2.x, b2.y) : pk2(0.f, 0.f);
+            if constexpr (D > 1) out[1][p] = first ? pk2(b2.z, b2.w) : pk2(0.f, 0.f);
         }
         static_assert(D <= 2, "v2 kernel: D <= 2");
     }
-    const float* rec = sm + L.rec0;
+    const float* rec = sm + L.rec0 + h0 * L.REC;
 #pragma unroll 1
-    for (int h = 0; h < H; ++h, rec += L.REC) {
+    for (int hh = 0; hh < HS; ++hh, rec += L.REC) {
         f32x2 xin[TP], pv[TP], silu[TP], r[TP][NB];
 #pragma unroll
         for (int p = 0; p < TP; ++p) {
-            xin[p] = colcur[(h * TP + p) * THREADS];
-            pv[p] = colprev[(h * TP + p) * THREADS];
+            xin[p] = colcur[(hh * TP + p) * THREADS];
+            pv[p] = colprev[(hh * TP + p) * THREADS];
         }
         sn2_features<NB, BR, TP>(xin, pv, pk2(hdr.z, hdr.w), rec + L.r_bc, silu, r);
         const float4* w4 = reinterpret_cast<const float4*>(rec + L.r_w2);
@@ -384,6 +393,18 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
             }
         }
     }
+    if constexpr (SPLIT > 1) {
+#pragma unroll
+        for (int o = 0; o < D; ++o)
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                float lo, hi;
+                upk2(out[o][p], lo, hi);
+                lo += __shfl_xor_sync(0xffffffffu, lo, 1);
+                hi += __shfl_xor_sync(0xffffffffu, hi, 1);
+                out[o][p] = pk2(lo, hi);
+            }
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -391,21 +412,25 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
 // ------------------------------------------------------------------------------------------
 // ALT: the 3/8-rule tableau (torchdiffeq "rk4") keeps k1, k2 across stages; it is a separate instantiation so the
 // other tableaus do not pay its registers
-template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool ALT, bool UNI>
+template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool ALT, bool UNI, int SPLIT>
 __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restrict__ sm) {
     constexpr SN2Layout L = sn2_layout(D, H, NB, G);
     constexpr int TPL = 2 * TP;
     constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
     constexpr int SF = FERRO ? D + H : 0;
+    constexpr int HS = H / SPLIT, SLOTS = THREADS / SPLIT;          // hidden units per lane, trajectory slots per CTA
     const int tid = threadIdx.x;
-    f32x2* col0 = const_cast<f32x2*>(reinterpret_cast<const f32x2*>(sm + L.total)) + tid;   // [H][TP][THREADS] pairs
-    f32x2* col1 = col0 + H * TP * THREADS;
+    const int sub = SPLIT > 1 ? tid % SPLIT : 0, slot = tid / SPLIT;
+    const int hbase = sub * HS;
+    const bool writer = sub == 0;                                    // the lane of a split group that stores y / prev1
+    f32x2* col0 = const_cast<f32x2*>(reinterpret_cast<const f32x2*>(sm + L.total)) + tid;   // [HS][TP][THREADS] pairs
+    f32x2* col1 = col0 + HS * TP * THREADS;
 
-    const long long base = (long long)blockIdx.x * (THREADS * TPL) + tid;   // trajectory of (pair p, half q): base + (2p+q) THREADS
-    if (base >= a.B) return;
+    const long long base = (long long)blockIdx.x * (SLOTS * TPL) + slot;    // trajectory of (pair p, half q): base + (2p+q) SLOTS
+    if (SPLIT == 1 && base >= a.B) return;       // split groups stay for their partner's shuffles (nothing is stored for dead rows)
     bool live[TPL];
 #pragma unroll
-    for (int i = 0; i < TPL; ++i) live[i] = base + (long long)i * THREADS < a.B;
+    for (int i = 0; i < TPL; ++i) live[i] = base + (long long)i * SLOTS < a.B;
 
     f32x2 y[D][TP], prev1[D][TP];
 #pragma unroll
@@ -413,7 +438,7 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
         float v[2][D];
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
-            const long long b = base + (long long)(2 * p + q) * THREADS;
+            const long long b = base + (long long)(2 * p + q) * SLOTS;
 #pragma unroll
             for (int d = 0; d < D; ++d) v[q][d] = live[2 * p + q] ? a.y0[b * D + d] : 0.f;
         }
@@ -426,26 +451,26 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
         if (!a.state_is_zero) {
 #pragma unroll
             for (int p = 0; p < TP; ++p) {
-                const long long b0 = base + (long long)(2 * p) * THREADS, b1 = b0 + THREADS;
+                const long long b0 = base + (long long)(2 * p) * SLOTS, b1 = b0 + SLOTS;
                 const bool l0 = live[2 * p], l1 = live[2 * p + 1];
 #pragma unroll
                 for (int d = 0; d < D; ++d)
                     prev1[d][p] = pk2(l0 ? a.state[b0 * SF + d] : 0.f, l1 ? a.state[b1 * SF + d] : 0.f);
 #pragma unroll 1
-                for (int h = 0; h < H; ++h)
-                    colprev[(h * TP + p) * THREADS] = pk2(l0 ? a.state[b0 * SF + D + h] : 0.f,
-                                                          l1 ? a.state[b1 * SF + D + h] : 0.f);
+                for (int hh = 0; hh < HS; ++hh)
+                    colprev[(hh * TP + p) * THREADS] = pk2(l0 ? a.state[b0 * SF + D + hbase + hh] : 0.f,
+                                                           l1 ? a.state[b1 * SF + D + hbase + hh] : 0.f);
             }
         } else {
 #pragma unroll 1
-            for (int i = 0; i < H * TP; ++i) colprev[i * THREADS] = pk2(0.f, 0.f);
+            for (int i = 0; i < HS * TP; ++i) colprev[i * THREADS] = pk2(0.f, 0.f);
         }
     }
 
     const int tab = a.tab;
     if (tab == TAB_RHS_ONLY) {
         f32x2 o[D][TP];
-        sn2_rhs<D, H, NB, G, BR, TP, THREADS, UNI>(sm, y, prev1, colcur, colprev, o);
+        sn2_rhs<D, H, NB, G, BR, TP, THREADS, UNI, SPLIT>(sm, y, prev1, colcur, colprev, o, sub);
         { f32x2* t = colcur; colcur = colprev; colprev = t; }
 #pragma unroll
         for (int d = 0; d < D; ++d)
@@ -467,25 +492,29 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
 #pragma unroll
                     for (int q = 0; q < 2; ++q) {
                         if (!live[2 * p + q]) continue;
-                        float* c = a.ckpt + ((size_t)step * NC) * a.B + (base + (long long)(2 * p + q) * THREADS);
-#pragma unroll
-                        for (int d = 0; d < D; ++d) {
-                            float lo, hi;
-                            upk2(y[d][p], lo, hi);
-                            c[(size_t)d * a.B] = q ? hi : lo;
-                        }
-                        if constexpr (FERRO) {
+                        float* c = a.ckpt + ((size_t)step * NC) * a.B + (base + (long long)(2 * p + q) * SLOTS);
+                        if (writer) {
 #pragma unroll
                             for (int d = 0; d < D; ++d) {
                                 float lo, hi;
-                                upk2(prev1[d][p], lo, hi);
-                                c[(size_t)(D + d) * a.B] = q ? hi : lo;
+                                upk2(y[d][p], lo, hi);
+                                c[(size_t)d * a.B] = q ? hi : lo;
+                            }
+                        }
+                        if constexpr (FERRO) {
+                            if (writer) {
+#pragma unroll
+                                for (int d = 0; d < D; ++d) {
+                                    float lo, hi;
+                                    upk2(prev1[d][p], lo, hi);
+                                    c[(size_t)(D + d) * a.B] = q ? hi : lo;
+                                }
                             }
 #pragma unroll 1
-                            for (int h = 0; h < H; ++h) {
+                            for (int hh = 0; hh < HS; ++hh) {
                                 float lo, hi;
-                                upk2(colprev[(h * TP + p) * THREADS], lo, hi);
-                                c[(size_t)(2 * D + h) * a.B] = q ? hi : lo;
+                                upk2(colprev[(hh * TP + p) * THREADS], lo, hi);
+                                c[(size_t)(2 * D + hbase + hh) * a.B] = q ? hi : lo;
                             }
                         }
                     }
@@ -502,7 +531,7 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
                 }
 #pragma unroll 1
             for (int s = 0; s < nst; ++s) {
-                sn2_rhs<D, H, NB, G, BR, TP, THREADS, UNI>(sm, ys, prev1, colcur, colprev, kn);
+                sn2_rhs<D, H, NB, G, BR, TP, THREADS, UNI, SPLIT>(sm, ys, prev1, colcur, colprev, kn, sub);
                 { f32x2* t = colcur; colcur = colprev; colprev = t; }
                 if (!ALT && tab == FETODE_TABLEAU_RK4) {
                     // (k1 + 2 k2 + 2 k3 + k4), stage inputs h + c k_prev   train_ecg_kan_fet_nn_ode.py:698-703
@@ -543,7 +572,7 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
                     else if (tab == FETODE_TABLEAU_RK4) y[d][p] = fma2(dt62, acc[d][p], y[d][p]);
                     else y[d][p] = fma2(dt2, acc[d][p], y[d][p]);
                 }
-            if (a.traj && (step + 1) % a.dump_every == 0) {
+            if (writer && a.traj && (step + 1) % a.dump_every == 0) {
                 float* t = a.traj + (size_t)((step + 1) / a.dump_every - 1) * a.B * D;
 #pragma unroll
                 for (int p = 0; p < TP; ++p)
@@ -551,21 +580,21 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
                     for (int d = 0; d < D; ++d) {
                         float lo, hi;
                         upk2(y[d][p], lo, hi);
-                        if (live[2 * p]) t[(base + (long long)(2 * p) * THREADS) * D + d] = lo;
-                        if (live[2 * p + 1]) t[(base + (long long)(2 * p + 1) * THREADS) * D + d] = hi;
+                        if (live[2 * p]) t[(base + (long long)(2 * p) * SLOTS) * D + d] = lo;
+                        if (live[2 * p + 1]) t[(base + (long long)(2 * p + 1) * SLOTS) * D + d] = hi;
                     }
             }
         }
     }
 #pragma unroll
     for (int p = 0; p < TP; ++p) {
-        const long long b0 = base + (long long)(2 * p) * THREADS, b1 = b0 + THREADS;
+        const long long b0 = base + (long long)(2 * p) * SLOTS, b1 = b0 + SLOTS;
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             float lo, hi;
             upk2(y[d][p], lo, hi);
-            if (live[2 * p]) a.y_out[b0 * D + d] = lo;
-            if (live[2 * p + 1]) a.y_out[b1 * D + d] = hi;
+            if (writer && live[2 * p]) a.y_out[b0 * D + d] = lo;
+            if (writer && live[2 * p + 1]) a.y_out[b1 * D + d] = hi;
         }
         if constexpr (FERRO) {
             if (a.state) {
@@ -573,22 +602,22 @@ __device__ __forceinline__ void sn2_body(const SNArgs& a, const float* __restric
                 for (int d = 0; d < D; ++d) {
                     float lo, hi;
                     upk2(prev1[d][p], lo, hi);
-                    if (live[2 * p]) a.state[b0 * SF + d] = lo;
-                    if (live[2 * p + 1]) a.state[b1 * SF + d] = hi;
+                    if (writer && live[2 * p]) a.state[b0 * SF + d] = lo;
+                    if (writer && live[2 * p + 1]) a.state[b1 * SF + d] = hi;
                 }
 #pragma unroll 1
-                for (int h = 0; h < H; ++h) {
+                for (int hh = 0; hh < HS; ++hh) {
                     float lo, hi;
-                    upk2(colprev[(h * TP + p) * THREADS], lo, hi);
-                    if (live[2 * p]) a.state[b0 * SF + D + h] = lo;
-                    if (live[2 * p + 1]) a.state[b1 * SF + D + h] = hi;
+                    upk2(colprev[(hh * TP + p) * THREADS], lo, hi);
+                    if (live[2 * p]) a.state[b0 * SF + D + hbase + hh] = lo;
+                    if (live[2 * p + 1]) a.state[b1 * SF + D + hbase + hh] = hi;
                 }
             }
         }
     }
 }
 
-template <int D, int H, int NB, int G, int BR, int TP, int THREADS, int MINB, bool ALT>
+template <int D, int H, int NB, int G, int BR, int TP, int THREADS, int MINB, bool ALT, int SPLIT>
 __global__ void __launch_bounds__(THREADS, MINB) smallnet_rk2_kernel(const SNArgs a, const float* __restrict__ img2) {
     extern __shared__ float4 sn2_smem4[];
     float* sm = reinterpret_cast<float*>(sn2_smem4);
@@ -597,8 +626,8 @@ __global__ void __launch_bounds__(THREADS, MINB) smallnet_rk2_kernel(const SNArg
     __syncthreads();
     // the constructor's grids are near-uniform: arithmetic interval guess + one correction, no search loop; adapted
     // (update_grid) knots take the general body.  One block-uniform branch per launch.
-    if (sm[L.hdr + 4] != 0.f) sn2_body<D, H, NB, G, BR, TP, THREADS, ALT, true>(a, sm);
-    else sn2_body<D, H, NB, G, BR, TP, THREADS, ALT, false>(a, sm);
+    if (sm[L.hdr + 4] != 0.f) sn2_body<D, H, NB, G, BR, TP, THREADS, ALT, true, SPLIT>(a, sm);
+    else sn2_body<D, H, NB, G, BR, TP, THREADS, ALT, false, SPLIT>(a, sm);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -616,14 +645,14 @@ int sn2_pack(const fetode_smallnet_t* net, const fetode_kanlayer_t* layers, floa
     return FETODE_LAUNCH_RC();
 }
 
-template <int BR, int TP, int THREADS, int MINB, bool ALT>
+template <int BR, int TP, int THREADS, int MINB, bool ALT, int SPLIT = 1>
 static int sn2_launch_k(const SNArgs& a, const float* img2, cudaStream_t st) {
     constexpr int D = 2, H = 10, NB = 10, G = 5;
     constexpr SN2Layout L = sn2_layout(D, H, NB, G);
-    const size_t smem = (size_t)L.total * 4 + (size_t)2 * H * TP * THREADS * 8;
-    const long long per_cta = (long long)THREADS * 2 * TP;
+    const size_t smem = (size_t)L.total * 4 + (size_t)2 * (H / SPLIT) * TP * THREADS * 8;
+    const long long per_cta = (long long)(THREADS / SPLIT) * 2 * TP;
     const unsigned grid = (unsigned)((a.B + per_cta - 1) / per_cta);
-    auto kern = smallnet_rk2_kernel<D, H, NB, G, BR, TP, THREADS, MINB, ALT>;
+    auto kern = smallnet_rk2_kernel<D, H, NB, G, BR, TP, THREADS, MINB, ALT, SPLIT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     kern<<<grid, THREADS, smem, st>>>(a, img2);
@@ -631,11 +660,14 @@ static int sn2_launch_k(const SNArgs& a, const float* img2, cudaStream_t st) {
 }
 
 // Launch shape (measured on B200, profiles/r2_sn_sweep.jsonl).  The kernel is latency-bound (shared-memory operand loads
-// and MUFU chains), so resident warps matter more than spill-freedom: two trajectories per lane, 64 registers, four
-// 256-thread CTAs per SM (32 warps; shared memory = 4 x (15 KB image + 40 KB columns)) is the fastest shape from
-// ~10^5 rows up (2.6e9 traj-steps/s at 2^20 rows; 128 registers / 16 warps: 2.2e9; four trajectories per lane at
-// 168 registers / 12 warps: 2.4e9).  Small batches take 64-thread CTAs so that every SM gets work.
-// FETODE_SN2_SHAPE=12564|164 overrides (experiments only; read once).
+// and MUFU chains), so resident warps matter more than spill-freedom:
+//   * from ~2*10^5 rows: two trajectories per lane, 64 registers, four 256-thread CTAs per SM (32 warps; shared memory =
+//     4 x (15 KB image + 40 KB columns)): 2.6e9 traj-steps/s at 2^20 rows (128 registers / 16 warps: 2.2e9; four
+//     trajectories per lane at 168 registers / 12 warps: 2.4e9);
+//   * below that the rows no longer fill the SMs with warps: SPLIT = 2 (two lanes per trajectory pair, half the
+//     hidden units each) doubles the warps and shortens every lane's dependency chain: 65 536 rows 1.26e9 -> 1.60e9,
+//     131 072 rows (the 8-GPU shard of the 2^20 ensemble) 1.90e9 -> 1.95e9.
+// FETODE_SN2_SHAPE=12564|164|2064|2128|2256 overrides (experiments only; read once).
 static int sn2_shape(long long B) {
     static int forced = -1;
     if (forced < 0) {
@@ -643,7 +675,8 @@ static int sn2_shape(long long B) {
         forced = e ? atoi(e) : 0;
     }
     if (forced > 0) return forced;
-    return B >= 98304 ? 12564 : 164;
+    if (B >= 196608) return 12564;
+    return B >= 98304 ? 2128 : 2064;
 }
 
 template <int BR>
@@ -651,7 +684,13 @@ static int sn2_launch_b(const SNArgs& a, const float* img2, cudaStream_t st) {
     const int shape = sn2_shape(a.B);
     if (a.tab == FETODE_TABLEAU_RK4_38)
         return shape == 164 ? sn2_launch_k<BR, 1, 64, 8, true>(a, img2, st) : sn2_launch_k<BR, 1, 256, 4, true>(a, img2, st);
-    return shape == 164 ? sn2_launch_k<BR, 1, 64, 8, false>(a, img2, st) : sn2_launch_k<BR, 1, 256, 4, false>(a, img2, st);
+    switch (shape) {
+        case 164: return sn2_launch_k<BR, 1, 64, 8, false>(a, img2, st);
+        case 2064: return sn2_launch_k<BR, 1, 64, 8, false, 2>(a, img2, st);      // split pairs, 128 registers
+        case 2128: return sn2_launch_k<BR, 1, 128, 8, false, 2>(a, img2, st);     // split pairs, 64 registers
+        case 2256: return sn2_launch_k<BR, 1, 256, 4, false, 2>(a, img2, st);
+        default: return sn2_launch_k<BR, 1, 256, 4, false>(a, img2, st);
+    }
 }
 
 int sn2_launch(const fetode_smallnet_t* net, const SNArgs& a, const float* img2, cudaStream_t st) {
