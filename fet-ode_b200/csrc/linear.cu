@@ -13,7 +13,7 @@
 
 namespace fetode {
 
-constexpr int LG_BM = 32, LG_BN = 64, LG_BK = 32, LG_THREADS = 256;
+constexpr int LG_BM = 32, LG_BN = 64, LG_BK = 32, LG_THREADS = 128;
 
 struct GemmArgs {
     const float* A; const float* B; const float* bias; float* C;
@@ -21,24 +21,33 @@ struct GemmArgs {
     int N, K, k_per_split;
 };
 
-// C[m,n] (+)= sum_k A[m*sAm + k*sAk] * B[k*sBk + n*sBn] (+ bias[n]);  C row-major [M, N]
+// C[m,n] (+)= sum_k A[m*sAm + k*sAk] * B[k*sBk + n*sBn] (+ bias[n]);  C row-major [M, N].
+// 32 x 64 tile, 128 threads, 4 x 4 outputs per thread: per k one 128-bit load of four A rows (two addresses per warp:
+// broadcast), one of four B columns, 16 FMA -- 8 FMA per shared-memory instruction (the first version's 2 x 4 tile did
+// 8 per 3 and ran at 3.5 TFLOP/s: 19 us per product under ncu, 7 % of the ECG step).
 __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a) {
-    __shared__ float As[LG_BK][LG_BM + 1];
+    __shared__ __align__(16) float As[LG_BK][LG_BM + 4];
     __shared__ __align__(16) float Bs[LG_BK][LG_BN];
     const int tid = threadIdx.x;
     const long long m0 = (long long)blockIdx.x * LG_BM;
     const int n0 = blockIdx.y * LG_BN;
     const int k_begin = blockIdx.z * a.k_per_split, k_end = min(a.K, k_begin + a.k_per_split);
-    const int ty = tid / 16, tx = tid % 16;                 // thread -> rows 2 ty, 2 ty + 1 ; columns 4 tx .. 4 tx + 3
-    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    const int ty = tid / 16, tx = tid % 16;                 // thread -> rows 4 ty .. 4 ty + 3 ; columns 4 tx .. 4 tx + 3
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
     const bool a_k_fast = a.sAk == 1, b_n_fast = a.sBn == 1;
     for (int k0 = k_begin; k0 < k_end; k0 += LG_BK) {
+#pragma unroll 4
         for (int q = tid; q < LG_BM * LG_BK; q += LG_THREADS) {
             const int kk = a_k_fast ? q % LG_BK : q / LG_BM, mm = a_k_fast ? q / LG_BK : q % LG_BM;
             const long long m = m0 + mm;
             const int k = k0 + kk;
             As[kk][mm] = (m < a.M && k < k_end) ? a.A[m * a.sAm + k * a.sAk] : 0.f;
         }
+#pragma unroll 4
         for (int q = tid; q < LG_BK * LG_BN; q += LG_THREADS) {
             const int nn = b_n_fast ? q % LG_BN : q / LG_BK, kk = b_n_fast ? q / LG_BN : q % LG_BK;
             const int n = n0 + nn, k = k0 + kk;
@@ -48,17 +57,19 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
 #pragma unroll
         for (int kk = 0; kk < LG_BK; ++kk) {
             const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][4 * tx]);
-            const float a0 = As[kk][2 * ty], a1 = As[kk][2 * ty + 1];
-            acc[0][0] = fmaf(a0, b.x, acc[0][0]); acc[0][1] = fmaf(a0, b.y, acc[0][1]);
-            acc[0][2] = fmaf(a0, b.z, acc[0][2]); acc[0][3] = fmaf(a0, b.w, acc[0][3]);
-            acc[1][0] = fmaf(a1, b.x, acc[1][0]); acc[1][1] = fmaf(a1, b.y, acc[1][1]);
-            acc[1][2] = fmaf(a1, b.z, acc[1][2]); acc[1][3] = fmaf(a1, b.w, acc[1][3]);
+            const float4 av = *reinterpret_cast<const float4*>(&As[kk][4 * ty]);
+            const float ar[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                acc[i][0] = fmaf(ar[i], b.x, acc[i][0]); acc[i][1] = fmaf(ar[i], b.y, acc[i][1]);
+                acc[i][2] = fmaf(ar[i], b.z, acc[i][2]); acc[i][3] = fmaf(ar[i], b.w, acc[i][3]);
+            }
         }
         __syncthreads();
     }
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const long long m = m0 + 2 * ty + i;
+    for (int i = 0; i < 4; ++i) {
+        const long long m = m0 + 4 * ty + i;
         if (m >= a.M) continue;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {

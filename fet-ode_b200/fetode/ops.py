@@ -314,13 +314,105 @@ def kanlinear_apply(pack: LayerPack, x2d: torch.Tensor, prev: Optional[torch.Ten
 
 
 # --------------------------------------------------------------------------------------
+# one gradient accumulator per (module, parameter version) for parameters applied many times per step
+# --------------------------------------------------------------------------------------
+class ParamGroupFn(torch.autograd.Function):
+    """(parameters...) -> data-less handle.  A module that is applied once per Runge-Kutta stage (32 times per ECG
+    step: the hard-gated basis, the LayerNorm, the dense head) routes its parameter gradients through ONE such node:
+    every call's backward kernel accumulates (+=) into one shared buffer, zero-filled once per backward pass, and this
+    node hands the buffer's views to the parameters -- instead of a zero-fill per parameter and call plus an
+    AccumulateGrad add per parameter and call (~1 200 adds and ~700 fills per ECG step)."""
+
+    @staticmethod
+    def forward(ctx, shared, *params):
+        ctx.shared = shared
+        ctx.shapes = [tuple(p.shape) for p in params]
+        ctx.set_materialize_grads(False)
+        return torch.empty(max(_group_floats(ctx.shapes), 4), dtype=torch.float32, device=params[0].device)
+
+    @staticmethod
+    def backward(ctx, g):
+        acc = ctx.shared["acc"]
+        n = 1 + len(ctx.shapes)
+        if g is None or acc is None:
+            return (None,) * n
+        outs, off = [], 0
+        for i, shp in enumerate(ctx.shapes):
+            numel = 1
+            for d in shp:
+                numel *= d
+            outs.append(acc[off:off + numel].view(shp) if ctx.needs_input_grad[1 + i] else None)
+            off += (numel + 3) // 4 * 4
+        return (None, *outs)
+
+
+def _group_floats(shapes) -> int:
+    tot = 0
+    for shp in shapes:
+        numel = 1
+        for d in shp:
+            numel *= d
+        tot += (numel + 3) // 4 * 4
+    return tot
+
+
+class ParamGroup:
+    """Cache of the ParamGroupFn handle of one module (rebuilt when a parameter's version / storage changes)."""
+
+    def __init__(self):
+        self._key, self._handle = None, None
+
+    def __deepcopy__(self, memo):
+        return ParamGroup()                                   # the handle is a non-leaf tensor: never copied
+
+    def __reduce__(self):
+        return (ParamGroup, ())
+
+    def handle(self, params) -> Optional[torch.Tensor]:
+        """Handle for ``params`` (list of Parameters), or None when autograd is off / nothing requires a gradient."""
+        if not torch.is_grad_enabled() or not any(p.requires_grad for p in params):
+            return None
+        key = tuple((p.data_ptr(), p._version, p.requires_grad) for p in params)
+        h = self._handle
+        if h is None or key != self._key or h.grad_fn is None:
+            h = self._handle = None
+            shared = {"acc": None}
+            h = self._handle = ParamGroupFn.apply(shared, *params)
+            h._fetode_shared = shared
+            h._fetode_shapes = [tuple(p.shape) for p in params]
+            self._key = key
+        return h
+
+
+def group_grad_views(handle, device):
+    """Inside a consumer's backward: (views of the shared accumulator, one per parameter of the group; first) where
+    ``first`` says this call created (zero-filled) the buffer and must return it as the handle's gradient."""
+    shared, shapes = handle._fetode_shared, handle._fetode_shapes
+    first = shared["acc"] is None
+    if first:
+        shared["acc"] = torch.zeros(max(_group_floats(shapes), 4), dtype=torch.float32, device=device)
+        torch.autograd.Variable._execution_engine.queue_callback(lambda: shared.__setitem__("acc", None))
+    acc = shared["acc"]
+    views, off = [], 0
+    for shp in shapes:
+        numel = 1
+        for d in shp:
+            numel *= d
+        views.append(acc[off:off + numel].view(shp))
+        off += (numel + 3) // 4 * 4
+    return views, acc, first
+
+
+# --------------------------------------------------------------------------------------
 # LayerNorm + tanh bound (prologue of the ECG right-hand side)
 # --------------------------------------------------------------------------------------
 class LnTanhFn(torch.autograd.Function):
     """y = h_bound * tanh(LayerNorm(x) / h_bound), train_ecg_kan_fet_nn_ode.py:459-461, one launch each way."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps, h_bound):
+    def forward(ctx, x, gamma, beta, eps, h_bound, handle=None):
+        """handle: ParamGroup handle of (gamma, beta) -- their gradients then go through it (gamma / beta are passed
+        detached), one accumulator per backward pass."""
         B, D = x.shape
         y = torch.empty_like(x)
         stats = torch.empty(2, B, dtype=torch.float32, device=x.device)
@@ -328,7 +420,7 @@ class LnTanhFn(torch.autograd.Function):
         check(lib().fetode_ln_tanh_fwd(ptr(x), ptr(g), ptr(b), ptr(y), ptr(stats[0]), ptr(stats[1]), C.c_int64(B),
                                        C.c_int32(D), C.c_float(eps), C.c_float(h_bound), stream()), "ln_tanh_fwd")
         ctx.save_for_backward(x, g, stats, y)
-        ctx.h_bound = h_bound
+        ctx.h_bound, ctx.handle = h_bound, handle
         return y
 
     @staticmethod
@@ -337,12 +429,20 @@ class LnTanhFn(torch.autograd.Function):
         B, D = x.shape
         gy = f32c(gy)
         gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-        gp = torch.zeros(2, D, dtype=torch.float32, device=x.device)
+        h = ctx.handle if (ctx.handle is not None and ctx.needs_input_grad[5]) else None
+        if h is not None:
+            (gg, gb), acc, first = group_grad_views(h, x.device)
+            want_g = want_b = True
+        else:
+            gp = torch.zeros(2, D, dtype=torch.float32, device=x.device)
+            gg, gb = gp[0], gp[1]
+            want_g, want_b = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
         check(lib().fetode_ln_tanh_bwd(ptr(x), ptr(g), ptr(stats[0]), ptr(stats[1]), ptr(y), ptr(gy), ptr(gx),
-                                       ptr(gp[0]) if ctx.needs_input_grad[1] else None,
-                                       ptr(gp[1]) if ctx.needs_input_grad[2] else None, C.c_int64(B), C.c_int32(D),
+                                       ptr(gg) if want_g else None, ptr(gb) if want_b else None, C.c_int64(B), C.c_int32(D),
                                        C.c_float(ctx.h_bound), stream()), "ln_tanh_bwd")
-        return (gx, gp[0] if ctx.needs_input_grad[1] else None, gp[1] if ctx.needs_input_grad[2] else None, None, None)
+        if h is not None:
+            return (gx, None, None, None, None, acc if first else None)
+        return (gx, gg if want_g else None, gb if want_b else None, None, None, None)
 
 
 def ln_tanh(x: torch.Tensor, ln: torch.nn.LayerNorm, h_bound: float) -> torch.Tensor:
@@ -351,6 +451,12 @@ def ln_tanh(x: torch.Tensor, ln: torch.nn.LayerNorm, h_bound: float) -> torch.Te
     _require_cuda(x, "input")
     if (x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and ln.elementwise_affine and ln.bias is not None
             and tuple(ln.normalized_shape) == (x.shape[1],) and x.shape[1] <= 256 and h_bound > 0):
+        grp = ln.__dict__.get("_fetode_pgroup")
+        if grp is None:
+            grp = ln.__dict__["_fetode_pgroup"] = ParamGroup()
+        h = grp.handle([ln.weight, ln.bias])
+        if h is not None:
+            return LnTanhFn.apply(f32c(x), ln.weight.detach(), ln.bias.detach(), float(ln.eps), float(h_bound), h)
         return LnTanhFn.apply(f32c(x), ln.weight, ln.bias, float(ln.eps), float(h_bound))
     h = ln(x)
     return torch.tanh(h) if h_bound == 1.0 else h_bound * torch.tanh(h / h_bound)
@@ -360,7 +466,8 @@ class LinearFn(torch.autograd.Function):
     """y = x W^T + b in fp32 FMA arithmetic (csrc/linear.cu): the dense head of the ECG right-hand side."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias):
+    def forward(ctx, x, weight, bias, handle=None):
+        """handle: ParamGroup handle of (weight[, bias]) -- see LnTanhFn.forward."""
         B, K = x.shape
         O = weight.shape[0]
         y = torch.empty(B, O, dtype=torch.float32, device=x.device)
@@ -369,7 +476,7 @@ class LinearFn(torch.autograd.Function):
         check(lib().fetode_linear_fwd(ptr(x), ptr(w), ptr(b), ptr(y), C.c_int64(B), C.c_int32(K), C.c_int32(O),
                                       stream()), "linear_fwd")
         ctx.save_for_backward(x, w)
-        ctx.has_bias = bias is not None
+        ctx.has_bias, ctx.handle = bias is not None, handle
         return y
 
     @staticmethod
@@ -379,6 +486,13 @@ class LinearFn(torch.autograd.Function):
         O = w.shape[0]
         gy = f32c(gy)
         gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        h = ctx.handle if (ctx.handle is not None and ctx.needs_input_grad[3]) else None
+        if h is not None:
+            views, acc, first = group_grad_views(h, x.device)
+            gw, gb = views[0], (views[1] if ctx.has_bias else None)
+            check(lib().fetode_linear_bwd(ptr(x), ptr(w), ptr(gy), ptr(gx), ptr(gw), ptr(gb), C.c_int64(B), C.c_int32(K),
+                                          C.c_int32(O), stream()), "linear_bwd")
+            return gx, None, None, (acc if first else None)
         want_w = ctx.needs_input_grad[1]
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         flat = torch.zeros(O * K + O, dtype=torch.float32, device=x.device) if (want_w or want_b) else None
@@ -386,7 +500,7 @@ class LinearFn(torch.autograd.Function):
         gb = flat[O * K:] if want_b else None
         check(lib().fetode_linear_bwd(ptr(x), ptr(w), ptr(gy), ptr(gx), ptr(gw), ptr(gb), C.c_int64(B), C.c_int32(K),
                                       C.c_int32(O), stream()), "linear_bwd")
-        return gx, gw, gb
+        return gx, gw, gb, None
 
 
 def linear(x: torch.Tensor, lin: torch.nn.Linear) -> torch.Tensor:
@@ -394,6 +508,13 @@ def linear(x: torch.Tensor, lin: torch.nn.Linear) -> torch.Tensor:
     (on the device: CPU tensors are refused like everywhere else)."""
     _require_cuda(x, "input")
     if x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and lin.weight.dtype == torch.float32:
+        grp = lin.__dict__.get("_fetode_pgroup")
+        if grp is None:
+            grp = lin.__dict__["_fetode_pgroup"] = ParamGroup()
+        params = [lin.weight] + ([lin.bias] if lin.bias is not None else [])
+        h = grp.handle(params)
+        if h is not None and all(p.requires_grad for p in params):
+            return LinearFn.apply(f32c(x), lin.weight.detach(), None if lin.bias is None else lin.bias.detach(), h)
         return LinearFn.apply(f32c(x), lin.weight, lin.bias)
     return lin(x)
 
@@ -577,7 +698,10 @@ class FerroFn(torch.autograd.Function):
     (ferro_class.py:381-382).  Side outputs (basis, new branch_sign, gate bits) are left in cfg["side"]."""
 
     @staticmethod
-    def forward(ctx, cfg, prev, br, x, k, Ec, Ps, bias, coef):
+    def forward(ctx, cfg, prev, br, x, k, Ec, Ps, bias, coef, handle=None):
+        """handle: ParamGroup handle of the (non-None) parameters in the order k, Ec, Ps, bias, coef -- their gradients
+        then go through it (the parameters are passed detached): one accumulator per backward pass for a neuron that
+        is applied once per Runge-Kutta stage."""
         _require_cuda(x, "input")
         B = x.shape[0]
         I, O, K = cfg["I"], cfg["O"], cfg["K"]
@@ -600,7 +724,7 @@ class FerroFn(torch.autograd.Function):
                                          C.c_int64(B), stream()), "ferro_fwd")
         side.update(basis=basis, br_out=br_out, gate=gate)
         cfg["side"] = side
-        ctx.cfg, ctx.prev, ctx.br, ctx.mode = cfg, (prev if mode == 0 else None), br, mode
+        ctx.cfg, ctx.prev, ctx.br, ctx.mode, ctx.handle = cfg, (prev if mode == 0 else None), br, mode, handle
         ctx.save_for_backward(x, k, Ec, Ps, bias, coef if coef is not None else x.new_empty(0),
                               out if cfg.get("post_op", 0) else x.new_empty(0))
         ctx.has_coef = coef is not None
@@ -619,16 +743,26 @@ class FerroFn(torch.autograd.Function):
         s = _ferro_struct(cfg, k, Ec, Ps, bias, coef)
         g = _lib.FerroGrads()
         grads = []
-        for idx, (name, t) in enumerate((("k", k), ("Ec", Ec), ("Ps", Ps), ("bias", bias), ("coef", coef))):
-            gt = None
-            if t is not None and ctx.needs_input_grad[4 + idx]:
-                gt = torch.zeros(t.shape, dtype=torch.float32, device=x.device)
-            setattr(g, name, ptr(gt).value)
-            grads.append(gt)
+        h = ctx.handle if (ctx.handle is not None and ctx.needs_input_grad[9]) else None
+        named = (("k", k), ("Ec", Ec), ("Ps", Ps), ("bias", bias), ("coef", coef))
+        acc, first = None, False
+        if h is not None:
+            views, acc, first = group_grad_views(h, x.device)
+            vi = iter(views)
+            for name, t in named:
+                setattr(g, name, ptr(next(vi) if t is not None else None).value)
+            grads = [None] * 5
+        else:
+            for idx, (name, t) in enumerate(named):
+                gt = None
+                if t is not None and ctx.needs_input_grad[4 + idx]:
+                    gt = torch.zeros(t.shape, dtype=torch.float32, device=x.device)
+                setattr(g, name, ptr(gt).value)
+                grads.append(gt)
         gx = torch.empty_like(x) if ctx.needs_input_grad[3] else None
         check(lib().fetode_ferro_bwd_fused(C.byref(s), ptr(x), ptr(ctx.prev), C.c_int(ctx.mode), ptr(ctx.br), ptr(gout),
                                            ptr(yout), ptr(gx), C.byref(g), C.c_int64(B), stream()), "ferro_bwd")
-        return (None, None, None, gx, *grads)
+        return (None, None, None, gx, *grads, (acc if first else None))
 
 
 def ferro_apply(module, variant: int, x2: torch.Tensor, prev: Optional[torch.Tensor], *, br=None,
@@ -654,7 +788,20 @@ def ferro_apply(module, variant: int, x2: torch.Tensor, prev: Optional[torch.Ten
         cfg["prev_mode"] = int(prev_mode)
     if variant == FERRO_LOGISTIC:
         cfg["gate_slope"], cfg["alpha"] = 0.0, 0.0
-    out = FerroFn.apply(cfg, prev, br, x2, k, Ec, Ps, bias, coef)
+    params = [t for t in (k, Ec, Ps, bias, coef) if t is not None]
+    handle = None
+    if all(isinstance(t, torch.nn.Parameter) for t in params):
+        grp = module.__dict__.get("_fetode_pgroup")
+        if grp is None:
+            grp = module.__dict__["_fetode_pgroup"] = ParamGroup()
+        handle = grp.handle(params)
+        if handle is not None and not all(t.requires_grad for t in params):
+            handle = None                                     # mixed frozen / trainable: the plain route
+    if handle is not None:
+        det = [None if t is None else t.detach() for t in (k, Ec, Ps, bias, coef)]
+        out = FerroFn.apply(cfg, prev, br, x2, *det, handle)
+    else:
+        out = FerroFn.apply(cfg, prev, br, x2, k, Ec, Ps, bias, coef)
     return out, cfg["side"]
 
 

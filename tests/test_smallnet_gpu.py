@@ -105,8 +105,9 @@ def test_ragged_and_empty_batches(cuda):
 
 def test_long_horizon_properties_full_size(cuda):
     """At the benchmark's own size (2^20 trajectories) the oracle is too slow; check size-independent
-    properties instead: (i) the first 512 rows of the big run equal a 512-row run bit for bit
-    (trajectories are independent), (ii) integrating 2 x 50 steps with the state carried equals 1 x 100."""
+    properties instead: (i) trajectories are independent -- the first 2^18 rows of the big run equal a 2^18-row run
+    bit for bit (same launch shape), and a 512-row run (a different launch shape: two lanes per trajectory pair, other
+    summation order) to the trajectory tolerance; (ii) integrating 2 x 50 steps with the state carried equals 1 x 100."""
     layers, m = fetode_kan_random([2, 10, 2], "ferro2d", seed=8, device=cuda)
     plan = m.small_plan()
     from fetode._lib import TABLEAU
@@ -114,9 +115,13 @@ def test_long_horizon_properties_full_size(cuda):
     x0 = lv_inputs(B, 1, cuda)
     st = torch.empty(B, plan.state_floats, device=cuda)
     big = plan.rk_fwd(TABLEAU["rk4_classic"], x0, 0.014, 100, state=st, state_is_zero=True)
+    n_mid = 1 << 18
+    st_m = torch.empty(n_mid, plan.state_floats, device=cuda)
+    mid = plan.rk_fwd(TABLEAU["rk4_classic"], x0[:n_mid].contiguous(), 0.014, 100, state=st_m, state_is_zero=True)
+    assert torch.equal(big[:n_mid], mid)
     st_s = torch.empty(512, plan.state_floats, device=cuda)
     small = plan.rk_fwd(TABLEAU["rk4_classic"], x0[:512].contiguous(), 0.014, 100, state=st_s, state_is_zero=True)
-    assert torch.equal(big[:512], small)
+    assert max_rel(small, big[:512]) < TRAJ_TOL
     st2 = torch.empty(B, plan.state_floats, device=cuda)
     half = plan.rk_fwd(TABLEAU["rk4_classic"], x0, 0.014, 50, state=st2, state_is_zero=True)
     full = plan.rk_fwd(TABLEAU["rk4_classic"], half, 0.014, 50, state=st2, state_is_zero=False)
