@@ -517,6 +517,115 @@ extern "C" int fetode_ferro_bwd_fused(const fetode_ferro_t* F, const float* x, c
     return FETODE_LAUNCH_RC();
 }
 
+// ---- OriginalBatchedFerroelectricBasis (ferro_class.py:9-104) -----------------------------------------------------
+// A sequential scan over the batch: sample b sees prev_x = x[b-1] and the branch momentum left by sample b-1, and --
+// unlike every other variant -- that momentum IS the carried branch_sign (:73) and stays on the autograd graph, so the
+// gradient of sample b reaches Ec and x of all earlier samples through a linear recurrence
+//     br_b = A_b br_{b-1} + C_b ,  A_b = alpha + (1-alpha)(1 - su_b - sl_b).
+// CTA = one output o; thread = elements (i, j) of that output, their br / prev in registers; the B steps run in-kernel
+// with one block reduction per sample for out[b, o].  The backward walks the samples in reverse with the adjoint of br
+// in a register; every parameter gradient is private to its thread (no reduction), gx needs one atomic per element.
+constexpr int FS_THREADS = 256, FS_EPT = 4;               // up to 1024 (i, j) elements per output
+
+struct FerroSeqArgs {
+    const float *k, *Ec, *Ps, *bias, *coef;
+    const float *x, *prev0, *br0, *gout, *br_hist_in;
+    float *out, *basis_out, *br_hist, *br_final, *gx;
+    float *gk, *gEc, *gPs, *gbias, *gcoef;
+    long long B;
+    int I, O, K;
+    float g, alpha;
+};
+
+__global__ void __launch_bounds__(FS_THREADS) ferro_seq_fwd_kernel(const FerroSeqArgs a) {
+    __shared__ float part[2][FS_THREADS / 32];
+    const int o = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int I = a.I, O = a.O, K = a.K, n = I * K;
+    float k[FS_EPT], Ec[FS_EPT], Ps[FS_EPT], bs[FS_EPT], cf[FS_EPT], br[FS_EPT], pv[FS_EPT];
+    int ii[FS_EPT];
+    size_t base[FS_EPT];
+#pragma unroll
+    for (int e = 0; e < FS_EPT; ++e) {
+        const int q = tid + e * FS_THREADS;
+        ii[e] = -1;
+        if (q < n) {
+            const int i = q / K, j = q % K;
+            ii[e] = i;
+            base[e] = ((size_t)i * O + o) * K + j;
+            k[e] = a.k[base[e]]; Ec[e] = a.Ec[base[e]]; Ps[e] = a.Ps[base[e]]; bs[e] = a.bias[base[e]]; cf[e] = a.coef[base[e]];
+            br[e] = a.br0 ? a.br0[base[e]] : 1.0f;
+            pv[e] = a.prev0 ? a.prev0[i] : 0.f;
+        }
+    }
+    const size_t IOK = (size_t)I * O * K;
+    for (long long b = 0; b < a.B; ++b) {
+        float acc = 0.f;
+#pragma unroll
+        for (int e = 0; e < FS_EPT; ++e) {
+            if (ii[e] < 0) continue;
+            const float x = a.x[b * I + ii[e]];
+            if (a.br_hist) a.br_hist[b * IOK + base[e]] = br[e];                 // branch_sign BEFORE this sample
+            const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv[e])), k[e], Ec[e], br[e], a.g, a.alpha);
+            const float P = fmaf(Ps[e], s.T, bs[e]);
+            acc = fmaf(cf[e], P, acc);
+            if (a.basis_out) a.basis_out[b * IOK + base[e]] = P;
+            br[e] = s.m;                                                       // :73  branch_sign <- momentum
+            pv[e] = x;                                                         // :87
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) part[b & 1][w] = acc;
+        __syncthreads();
+        if (tid == 0) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < FS_THREADS / 32; ++q) t += part[b & 1][q];
+            a.out[b * O + o] = t;
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < FS_EPT; ++e)
+        if (ii[e] >= 0 && a.br_final) a.br_final[base[e]] = br[e];
+}
+
+__global__ void __launch_bounds__(FS_THREADS) ferro_seq_bwd_kernel(const FerroSeqArgs a) {
+    const int o = blockIdx.x, tid = threadIdx.x;
+    const int I = a.I, O = a.O, K = a.K, n = I * K;
+    const size_t IOK = (size_t)I * O * K;
+#pragma unroll 1
+    for (int e = 0; e < FS_EPT; ++e) {
+        const int q = tid + e * FS_THREADS;
+        if (q >= n) break;
+        const int i = q / K, j = q % K;
+        const size_t base = ((size_t)i * O + o) * K + j;
+        const float k = a.k[base], Ec = a.Ec[base], Ps = a.Ps[base], bias = a.bias[base], coef = a.coef[base];
+        float ak = 0.f, aEc = 0.f, aPs = 0.f, ab = 0.f, ac = 0.f, lam = 0.f;     // lam: adjoint of the carried branch_sign
+        for (long long b = a.B - 1; b >= 0; --b) {
+            const float x = a.x[b * I + i];
+            const float pv = b > 0 ? a.x[(b - 1) * I + i] : (a.prev0 ? a.prev0[i] : 0.f);
+            const float br = a.br_hist_in[b * IOK + base];
+            const SoftBranch s = soft_branch(x, sigm(a.g * (x - pv)), k, Ec, br, a.g, a.alpha);
+            float dm_dx, dm_dEc;
+            soft_branch_grad(s, br, a.g, a.alpha, dm_dx, dm_dEc);
+            const float go = a.gout[b * O + o];
+            ac = fmaf(go, fmaf(Ps, s.T, bias), ac);
+            const float gP = go * coef;
+            aPs = fmaf(gP, s.T, aPs);
+            ab += gP;
+            const float dz = gP * Ps * (1.0f - s.T * s.T);
+            ak = fmaf(dz, fmaf(Ec, s.m, x), ak);
+            const float mu = fmaf(dz * k, Ec, lam);                             // adjoint of this sample's momentum
+            aEc = fmaf(dz * k, s.m, fmaf(mu, dm_dEc, aEc));
+            if (a.gx) atomicAdd(a.gx + b * I + i, fmaf(mu, dm_dx, dz * k));
+            lam = mu * (a.alpha + (1.0f - a.alpha) * (1.0f - s.su - s.sl));     // d m / d br_{b-1}
+        }
+        if (a.gk) atomicAdd(a.gk + base, ak);
+        if (a.gEc) atomicAdd(a.gEc + base, aEc);
+        if (a.gPs) atomicAdd(a.gPs + base, aPs);
+        if (a.gbias) atomicAdd(a.gbias + base, ab);
+        if (a.gcoef) atomicAdd(a.gcoef + base, ac);
+    }
+}
+
 // ---- FerroelectricBasisConv2d / MemEfficient_FerroelectricBasisConv2d (ferro_class.py:601-944) -------------------
 static int conv_check(const fetode_ferro_t* F, const fetode_conv2d_t* G) {
     if (!G) return FETODE_EINVAL;
@@ -580,5 +689,43 @@ extern "C" int fetode_ferro_conv2d_bwd(const fetode_ferro_t* F, const fetode_con
     const dim3 grid((unsigned)a.I, (unsigned)((a.O + 31) / 32), (unsigned)bz);
     if (br) ferro_full_bwd_kernel<true><<<grid, FF_THREADS, 0, st>>>(a);
     else ferro_full_bwd_kernel<false><<<grid, FF_THREADS, 0, st>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_ferro_seq_fwd(const fetode_ferro_t* F, const float* x, const float* prev0, const float* br0,
+                                    float* out, float* basis_out, float* br_hist, float* br_final, int64_t B,
+                                    void* stream) {
+    int rc = ferro_check(F);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(F->variant == FETODE_FERRO_FULL && x && out && B >= 0);
+    FETODE_CHECK_SUPPORTED(F->in_dim * F->num_basis <= FS_THREADS * FS_EPT);
+    if (B == 0) return FETODE_OK;
+    FerroSeqArgs a{};
+    a.k = F->k; a.Ec = F->Ec; a.Ps = F->Ps; a.bias = F->bias; a.coef = F->coef;
+    a.x = x; a.prev0 = prev0; a.br0 = br0; a.out = out; a.basis_out = basis_out; a.br_hist = br_hist; a.br_final = br_final;
+    a.B = B; a.I = F->in_dim; a.O = F->out_dim; a.K = F->num_basis; a.g = F->gate_slope; a.alpha = F->alpha;
+    ferro_seq_fwd_kernel<<<(unsigned)a.O, FS_THREADS, 0, (cudaStream_t)stream>>>(a);
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_ferro_seq_bwd(const fetode_ferro_t* F, const float* x, const float* prev0, const float* br_hist,
+                                    const float* gout, float* gx, const fetode_ferro_grads_t* grads, int64_t B,
+                                    void* stream) {
+    int rc = ferro_check(F);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(F->variant == FETODE_FERRO_FULL && x && br_hist && gout && B >= 0);
+    FETODE_CHECK_SUPPORTED(F->in_dim * F->num_basis <= FS_THREADS * FS_EPT);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (gx) {
+        cudaError_t e = cudaMemsetAsync(gx, 0, (size_t)B * F->in_dim * sizeof(float), st);
+        if (e) return (int)e;
+    }
+    if (B == 0) return FETODE_OK;
+    FerroSeqArgs a{};
+    a.k = F->k; a.Ec = F->Ec; a.Ps = F->Ps; a.bias = F->bias; a.coef = F->coef;
+    a.x = x; a.prev0 = prev0; a.br_hist_in = br_hist; a.gout = gout; a.gx = gx;
+    if (grads) { a.gk = grads->k; a.gEc = grads->Ec; a.gPs = grads->Ps; a.gbias = grads->bias; a.gcoef = grads->coef; }
+    a.B = B; a.I = F->in_dim; a.O = F->out_dim; a.K = F->num_basis; a.g = F->gate_slope; a.alpha = F->alpha;
+    ferro_seq_bwd_kernel<<<(unsigned)a.O, FS_THREADS, 0, st>>>(a);
     return FETODE_LAUNCH_RC();
 }

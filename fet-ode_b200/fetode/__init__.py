@@ -15,6 +15,7 @@ from . import _lib  # noqa: F401
 from .efficientkan import KAN, KANFET, KANLinear, LogisticBasis  # noqa: F401
 from .ferro_class import (BatchedFerroelectricBasis, FerroelectricBasis, FerroelectricBasisConv2d,  # noqa: F401
                           MemEfficient_FerroelectricBasisConv2d, NoisyBatchedFerroelectricBasis,
+                          OriginalBatchedFerroelectricBasis,
                           NoisyFerroelectricBasis, TwoDimensionFerroelectricBasis)
 from . import compat, diffusion, ecg, ett, graphs, mnist_kuramoto_kan, optim  # noqa: F401
 from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odeint,  # noqa: F401
@@ -22,6 +23,6 @@ from .odeint import (as_rhs, integrate_euler, integrate_rk2, integrate_rk4, odei
 
 __all__ = ["KAN", "KANFET", "KANLinear", "LogisticBasis", "TwoDimensionFerroelectricBasis", "FerroelectricBasis",
            "NoisyFerroelectricBasis", "BatchedFerroelectricBasis", "NoisyBatchedFerroelectricBasis",
-           "FerroelectricBasisConv2d", "MemEfficient_FerroelectricBasisConv2d", "ecg",
+           "FerroelectricBasisConv2d", "MemEfficient_FerroelectricBasisConv2d", "OriginalBatchedFerroelectricBasis", "ecg",
            "mnist_kuramoto_kan", "optim", "graphs", "compat", "ett", "diffusion", "odeint",
            "integrate_euler", "integrate_rk2", "integrate_rk4", "odeint_rk4", "as_rhs"]

@@ -355,3 +355,105 @@ class MemEfficient_FerroelectricBasisConv2d(FerroelectricBasisConv2d):
         super().__init__(in_channels, out_channels, kernel_size, num_basis, stride, padding, use_noise, noise_std,
                          gate_slope, alpha, stateful)
         self.out_chunk = out_chunk
+
+
+class _FerroSeqFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod, x, prev0, br0, k, Ec, Ps, bias, coef, want_basis):
+        import ctypes as C
+        from ._lib import check, lib, ptr, stream
+        ops._require_cuda(x, "input")
+        B, I = x.shape
+        _, O, K = k.shape
+        need = any(ctx.needs_input_grad)
+        out = torch.empty(B, O, dtype=torch.float32, device=x.device)
+        basis = torch.empty(B, I, O, K, dtype=torch.float32, device=x.device) if want_basis else None
+        hist = torch.empty(B, I, O, K, dtype=torch.float32, device=x.device) if need else None
+        br_final = torch.empty(I, O, K, dtype=torch.float32, device=x.device)
+        s = ops._ferro_struct(dict(variant=ops.FERRO_FULL, I=I, O=O, K=K, gate_slope=mod.gate_slope, alpha=mod.alpha),
+                              k, Ec, Ps, bias, coef)
+        if B:
+            check(lib().fetode_ferro_seq_fwd(C.byref(s), ptr(x), ptr(prev0), ptr(br0), ptr(out), ptr(basis), ptr(hist),
+                                             ptr(br_final), C.c_int64(B), stream()), "ferro_seq_fwd")
+        else:
+            br_final = br0.clone() if br0 is not None else torch.ones(I, O, K, device=x.device)
+        ctx.mod, ctx.prev0 = mod, prev0
+        ctx.save_for_backward(x, k, Ec, Ps, bias, coef, hist if hist is not None else x.new_empty(0))
+        ctx.mark_non_differentiable(br_final)
+        if basis is not None:
+            ctx.mark_non_differentiable(basis)
+            return out, br_final, basis
+        return out, br_final, x.new_empty(0)
+
+    @staticmethod
+    def backward(ctx, gout, _gbr, _gbasis):
+        import ctypes as C
+        from . import _lib
+        from ._lib import check, lib, ptr, stream
+        x, k, Ec, Ps, bias, coef, hist = ctx.saved_tensors
+        B, I = x.shape
+        _, O, K = k.shape
+        mod = ctx.mod
+        gout = ops.f32c(gout)
+        s = ops._ferro_struct(dict(variant=ops.FERRO_FULL, I=I, O=O, K=K, gate_slope=mod.gate_slope, alpha=mod.alpha),
+                              k, Ec, Ps, bias, coef)
+        g = _lib.FerroGrads()
+        grads = []
+        for idx, (name, t) in enumerate((("k", k), ("Ec", Ec), ("Ps", Ps), ("bias", bias), ("coef", coef))):
+            gt = torch.zeros(t.shape, dtype=torch.float32, device=x.device) if ctx.needs_input_grad[4 + idx] else None
+            setattr(g, name, ptr(gt).value)
+            grads.append(gt)
+        gx = torch.empty_like(x) if ctx.needs_input_grad[1] else None
+        check(lib().fetode_ferro_seq_bwd(C.byref(s), ptr(x), ptr(ctx.prev0), ptr(hist), ptr(gout), ptr(gx), C.byref(g),
+                                         C.c_int64(B), stream()), "ferro_seq_bwd")
+        return (None, gx, None, None, *grads, None)
+
+
+class OriginalBatchedFerroelectricBasis(nn.Module):
+    """ferro_class.py:9-104: the per-sample loop in which sample b sees the previous ROW and the branch momentum it
+    left, and that momentum -- not a detached snapshot -- enters the shifted field, so gradients flow through the
+    recurrence over the batch.  One launch runs the scan (csrc/ferro.cu, ferro_seq_*).  Buffers ``prev_x`` /
+    ``branch_sign`` keep the reference's [1, I, O, K] shapes; the state is detached between calls (the reference leaves
+    the previous call's graph attached to the buffer, which only makes a second backward fail)."""
+
+    def __init__(self, in_dim, out_dim, num_basis, use_noise=False, gate_slope=10.0, alpha=0.8, noise_std=0.05):
+        super().__init__()
+        self.in_dim, self.out_dim, self.num_basis = in_dim, out_dim, num_basis
+        self.use_noise, self.noise_std = use_noise, noise_std
+        self.gate_slope, self.alpha = gate_slope, alpha
+        shape = (in_dim, out_dim, num_basis)
+        self.k = nn.Parameter(torch.rand(*shape) * 2 + 0.5)
+        self.Ec = nn.Parameter(torch.rand(*shape) * 2 + 0.5)
+        self.Ps = nn.Parameter(torch.rand(*shape) * 1.5 + 0.5)
+        self.bias = nn.Parameter(torch.randn(*shape) * 0.1)
+        self.coef = nn.Parameter(torch.randn(*shape))
+        self.register_buffer("prev_x", torch.zeros(1, *shape))
+        self.register_buffer("branch_sign", torch.ones(1, *shape))
+
+    def forward(self, x, return_activations=False):
+        ops.abort_if_tracing()
+        if x.dim() > 2:
+            x = x.view(x.shape[0], -1)
+        x2 = ops.f32c(x)
+        B = x2.shape[0]
+        if B == 0:
+            return x2.new_empty(0, self.out_dim)
+        prev0 = self.prev_x[0, :, 0, 0].contiguous()                 # the buffer is x expanded over (O, K)
+        br0 = self.branch_sign[0].contiguous()
+        noisy = self.use_noise and self.noise_std != 0.0
+        out, br_final, basis = _FerroSeqFn.apply(self, x2, prev0, br0, self.k, self.Ec, self.Ps, self.bias, self.coef,
+                                                 bool(return_activations or noisy))
+        if noisy:
+            noise = torch.randn_like(basis) * self.noise_std         # basis + noise.detach()  (:82-84)
+            out = out + (noise * self.coef).sum(dim=(1, 3))
+            basis = basis + noise
+        with torch.no_grad():
+            self.prev_x = x2.detach()[-1].view(1, -1, 1, 1).expand(1, self.in_dim, self.out_dim, self.num_basis).clone()
+            self.branch_sign = br_final.unsqueeze(0)
+        if return_activations:
+            return out, basis.detach(), self.coef.detach()
+        return out
+
+    def reset_state(self):
+        self.prev_x.zero_()
+        self.branch_sign.fill_(1.0)

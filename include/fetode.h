@@ -262,6 +262,18 @@ FETODE_API int fetode_ferro_bwd_fused(const fetode_ferro_t* F, const float* x, c
                      const float* br, const float* gout, const float* yout, float* gx,
                      const fetode_ferro_grads_t* grads, int64_t B, void* stream);
 
+/* ---- OriginalBatchedFerroelectricBasis.forward (ferro_class.py:49-99) + autograd ------------------------------------
+ * Sequential scan over the batch: sample b uses prev_x = x[b-1] (prev0 [I] for b = 0, NULL = zeros) and the branch
+ * momentum left by sample b-1 (br0 [I,O,K] for b = 0, NULL = +1), which is ALSO the value used in the shifted field
+ * (:73-77) and stays differentiable across samples.  br_hist [B,I,O,K] (branch_sign before each sample) is what the
+ * backward replays; br_final [I,O,K] is the state after the last sample.  F: variant FULL.  I*K <= 1024. */
+FETODE_API int fetode_ferro_seq_fwd(const fetode_ferro_t* F, const float* x, const float* prev0, const float* br0,
+                     float* out /* [B,O] */, float* basis_out /* [B,I,O,K] or NULL */, float* br_hist /* or NULL */,
+                     float* br_final /* or NULL */, int64_t B, void* stream);
+FETODE_API int fetode_ferro_seq_bwd(const fetode_ferro_t* F, const float* x, const float* prev0, const float* br_hist,
+                     const float* gout, float* gx /* [B,I] overwritten, or NULL */,
+                     const fetode_ferro_grads_t* grads /* accumulated */, int64_t B, void* stream);
+
 /* ---- FerroelectricBasisConv2d / MemEfficient_FerroelectricBasisConv2d (ferro_class.py:601-779, :783-944) ----------
  * The same neuron applied to the kH x kW patches of an image, WITHOUT materialising F.unfold's (B, Cin*kH*kW, L)
  * matrix (:699-703) or the (B,Cout,Cin,K,kH,kW,L) broadcast (:712-722): the kernel gathers each patch element from the

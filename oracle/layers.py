@@ -161,6 +161,50 @@ def ferro_full_forward(x: Tensor, p: Params, st: FerroFullState, *, gate_slope=1
     return out
 
 
+class FerroSeqState:
+    """prev_x / branch_sign [1,I,O,K] of OriginalBatchedFerroelectricBasis (ferro_class.py:44-46)."""
+
+    def __init__(self, p: Params):
+        shape = (1,) + tuple(p["k"].shape)
+        self.prev = torch.zeros(shape, dtype=p["k"].dtype)
+        self.br = torch.ones(shape, dtype=p["k"].dtype)
+
+    def reset(self):
+        self.prev = torch.zeros_like(self.prev)
+        self.br = torch.ones_like(self.br)
+
+
+def ferro_seq_forward(x: Tensor, p: Params, st: FerroSeqState, *, gate_slope=10.0, alpha=0.8, return_basis=False):
+    """OriginalBatchedFerroelectricBasis.forward (ferro_class.py:49-99): a Python loop over the batch in which sample b
+    sees prev_x = x[b-1] and the branch momentum of sample b-1, which is also the value used in shifted_x (:73-77) and
+    is NOT detached: the gradient flows through the recurrence (within one call; the state is detached between calls
+    here, the reference keeps the stale graph in the buffer)."""
+    if x.dim() > 2:
+        x = x.reshape(x.shape[0], -1)
+    I, O, K = p["k"].shape
+    x_exp = x.unsqueeze(2).unsqueeze(3).expand(-1, -1, O, K)
+    br, prev = st.br, st.prev
+    all_basis = []
+    for b in range(x.shape[0]):
+        xs = x_exp[b:b + 1]
+        dx = xs - prev
+        up = torch.sigmoid(gate_slope * dx)
+        cpos = torch.sigmoid(gate_slope * (xs - p["Ec"]))
+        cneg = torch.sigmoid(gate_slope * (-xs - p["Ec"]))
+        to_upper = up * cpos
+        to_lower = (1 - up) * cneg
+        tgt = to_upper * 1.0 + to_lower * (-1.0) + (1 - to_upper - to_lower) * br
+        br = alpha * br + (1.0 - alpha) * tgt
+        all_basis.append(p["Ps"] * torch.tanh(p["k"] * (xs + p["Ec"] * br)) + p["bias"])
+        prev = xs.detach().clone()
+    basis_all = torch.cat(all_basis, dim=0)
+    st.prev, st.br = prev, br.detach().clone()
+    out = (basis_all * p["coef"]).sum(dim=(1, 3))
+    if return_basis:
+        return out, basis_all.detach()
+    return out
+
+
 class FerroConvState:
     """_prev_x / _branch_sign / _state_ready of FerroelectricBasisConv2d (ferro_class.py:666-687) and of
     MemEfficient_FerroelectricBasisConv2d (:826-838): shape-checked, re-created as prev = x_exp, br = 1."""

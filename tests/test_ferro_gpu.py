@@ -244,3 +244,37 @@ def test_kanfet_ode_func_fused_glue_values_and_gradients(cuda, B):
             assert max_rel(t.grad, q[name].grad) < GRAD_TOL, name
     # state left behind: fc1 remembers the BOUNDED input, fc2 remembers tanh(fc1 out)
     assert max_rel(m.fc1._rows, 1.5 * torch.tanh(hs[1] / 1.5)) < 1e-6
+
+
+@pytest.mark.parametrize("B,I,O,K", [(1, 5, 3, 4), (9, 5, 3, 4), (64, 64, 16, 12)])
+def test_original_batched_scan_values_and_recurrent_gradients(cuda, B, I, O, K):
+    """OriginalBatchedFerroelectricBasis (ferro_class.py:9-104) as one in-kernel scan over the batch: two consecutive
+    calls (row and branch state carried) against the oracle, and the gradients -- which flow through the branch
+    momentum recurrence across samples -- against fp64 oracle autograd."""
+    gen = torch.Generator().manual_seed(B * 7 + I)
+    p = OL.make_ferro_params((I, O, K), gen)
+    m = fetode.OriginalBatchedFerroelectricBasis(I, O, K)
+    m.load_state_dict(p, strict=False)
+    m = m.to(cuda)
+    xs = [torch.randn(B, I, generator=gen) * 1.5, torch.randn(B, I, generator=gen) * 1.5]
+    st32 = OL.FerroSeqState(p)
+    with torch.no_grad():
+        want = [OL.ferro_seq_forward(x, p, st32) for x in xs]
+    p64 = {k: v.double().requires_grad_(True) for k, v in p.items()}
+    st64 = OL.FerroSeqState(p64)
+    x64 = [x.double().requires_grad_(True) for x in xs]
+    ws = [torch.randn(B, O, generator=gen, dtype=torch.float64) for _ in xs]
+    sum((OL.ferro_seq_forward(x, p64, st64) * w).sum() for x, w in zip(x64, ws)).backward()
+    xg = [x.to(cuda).requires_grad_(True) for x in xs]
+    outs = [m(x) for x in xg]
+    for o, w32 in zip(outs, want):
+        assert max_rel(o, w32) < RHS_TOL
+    sum((o * w.float().to(cuda)).sum() for o, w in zip(outs, ws)).backward()
+    for a, b in zip(xg, x64):
+        assert max_rel(a.grad, b.grad) < GRAD_TOL
+    for name, t in m.named_parameters():
+        assert max_rel(t.grad, p64[name].grad) < GRAD_TOL, name
+    assert m.prev_x.shape == (1, I, O, K) and m.branch_sign.shape == (1, I, O, K)
+    assert max_rel(m.branch_sign, st32.br) < 1e-5
+    m.reset_state()
+    assert float(m.prev_x.abs().max()) == 0.0 and float((m.branch_sign - 1).abs().max()) == 0.0
