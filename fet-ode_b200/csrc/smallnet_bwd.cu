@@ -67,35 +67,6 @@ __device__ __forceinline__ float spl_at(int s, int m, const float (&v)[4]) {
     return r;
 }
 
-// d(loss)/d(branch inputs) for one (input, basis j): given G = d(loss)/d r_j returns d(loss)/dx and the two
-// raw-parameter contributions.  FERRO2D: SURVEY appendix A.4 with branch_sign == 1; LOGISTIC: A.3.
-// HAVE_CN: cn_in holds crossed_neg from the forward evaluation of the same point (branch_eval's cn_out); otherwise it is
-// recomputed from et = 2^(x gl) * 2^(c1_j), the caller's ferro_ex(x, gl) times the packed constant (one rcp).
-template <int BR, bool HAVE_CN = false>
-__device__ __forceinline__ void branch_bwd(float x, float omu, float gl, float al2, float et, float r, float G,
-                                           float p0, float p1, float& gx, float& g0, float& g1, float cn_in = 0.f) {
-    if constexpr (BR == FETODE_BRANCH_FERRO2D) {
-        const float g = gl * (1.0f / FETODE_LOG2E);
-        const float k = p0, Ec = p1;
-        const float cn = HAVE_CN ? cn_in : rcp_approx(1.0f + fminf(et, 1073741824.0f));
-        const float dcn = -g * cn * (1.0f - cn);                  // d/dx == d/dEc
-        const float domu = -g * omu * (1.0f - omu);
-        const float m = 1.0f - al2 * omu * cn;
-        const float dm_dx = -al2 * (domu * cn + omu * dcn);
-        const float dm_dE = -al2 * omu * dcn;
-        const float e = G * (-2.0f) * r * (1.0f - r);             // d(loss)/dz,  z = k (x + Ec m)
-        gx = e * k * fmaf(Ec, dm_dx, 1.0f);
-        g0 = e * fmaf(Ec, m, x);
-        g1 = e * k * fmaf(Ec, dm_dE, m);
-    } else {
-        const float a = p0, b = p1;
-        const float e = G * r * (1.0f - r);
-        gx = e * a;
-        g0 = e * (x - b);
-        g1 = -e * a;
-    }
-}
-
 // Pull the adjoint `gout` of one right-hand-side evaluation out = KAN(y) back to its input (`gy`, overwritten)
 // and add this trajectory's parameter-gradient contributions to the per-CTA accumulators `sacc`.
 // prev1 / prev2 are the hysteresis snapshots the forward evaluation of this stage saw (read only).

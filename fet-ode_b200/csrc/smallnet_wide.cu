@@ -1,0 +1,555 @@
+// smallnet_wide.cu -- the fused KAN / KANFET([2,10,2]) Runge-Kutta loop and its reverse sweep with the HIDDEN UNITS on
+// the lanes (sm_100a): the training path.
+//
+// The lane-per-trajectory kernels (smallnet.cu / smallnet_v2.cu / smallnet_bwd.cu) are built for throughput over
+// 10^5..10^6 rows.  Training batches are small (the reference's own Lotka-Volterra run is ONE trajectory,
+// train_kanfet_node_predprey.py:149-155) and the reverse sweep must also reduce ~1000 parameter-gradient columns over
+// the lanes after every right-hand side (two thirds of its instructions).  Here a warp holds three trajectories, ten
+// lanes each: lane (g, h) owns hidden unit h of trajectory g -- its layer-1 output, its layer-2 input features, its
+// rows of both weight matrices.  Consequences:
+//   * the dependency chain of a right-hand side is 3 feature evaluations instead of 12 (B = 1: 8x shorter);
+//   * every parameter-gradient column of unit h is produced by ONE lane: it accumulates privately (shared memory,
+//     [column][lane]) over all stages, steps and trajectories the warp processes, and the cross-lane / cross-CTA
+//     reduction happens once, at the end of the launch -- no per-right-hand-side reduction at all;
+//   * the forward pass checkpoints every stage's input and hidden pre-activations ([step][slot][row][12] floats, one
+//     coalesced 48-byte record per trajectory and slot), so the reverse sweep recomputes nothing but features.
+// Lane exchanges are warp shuffles / a warp-private shared-memory transpose; there is no block-level synchronisation.
+//
+// Reference arithmetic replaced (reference checkout 704a0df4): as smallnet.cu (KAN.forward efficientkan.py:160-182,
+// 274-279; TwoDimensionFerroelectricBasis ferro_class.py:547-592; integrate_rk4 train_ecg_kan_fet_nn_ode.py:693-705)
+// and loss.backward() through the solver (train_kanfet_node_predprey.py:254-256).  Image: the first-generation layout
+// (smallnet.cuh); folded-gradient layout: sn_gfold_layout (smallnet_bwd.cu), unfolded by fetode_smallnet_unfold.
+#include <algorithm>
+#include "smallnet.cuh"
+
+namespace fetode {
+
+constexpr int SW_D = 2, SW_H = 10, SW_NB = 10, SW_G = 5, SW_GRP = 3;      // 3 trajectories x 10 lanes per warp
+constexpr int SW_WARPS = 4, SW_THREADS = SW_WARPS * 32;
+constexpr int SW_REC = SW_D + SW_H;                                        // checkpoint record: y[2] | x2[10]
+constexpr int SW_SLOTS = 5;                                                // slot 0: (prev1, prev2) at step start; 1+s: stage s
+
+struct SNGfoldW { int ws1, gsum1, ws2, gsum2, bp1, bp2, total; };
+__host__ __device__ inline SNGfoldW snw_gfold(int D, int H, int F, int NB) {
+    SNGfoldW g{};
+    int o = 0;
+    g.ws1 = o; o += D * F * H;
+    g.gsum1 = o; o += H;
+    g.ws2 = o; o += H * F * D;
+    g.gsum2 = o; o += D;
+    g.bp1 = o; o += 2 * D * NB;
+    g.bp2 = o; o += 2 * H * NB;
+    g.total = (o + 3) / 4 * 4;
+    return g;
+}
+
+struct SWArgs {
+    const float* packed;
+    const float* y0;          // [B, D]
+    float* y_out;             // [B, D]
+    float* state;             // [B, D + H] in/out or null
+    float* traj;              // [n_dump, B, D] or null
+    float* ckpt;              // [n_steps, SW_SLOTS, B, SW_REC] or null (forward: written; backward: read)
+    const float* g_yout;      // backward
+    const float* g_traj;
+    float* g_y0;
+    float* gfold;
+    long long B;
+    float dt;
+    float A[4][4], bw[4];     // stage s input = y + dt sum_r A[s][r] k_r ; y_next = y + dt sum_s bw[s] k_s
+    int nst, n_steps, dump_every, state_is_zero;
+};
+
+// sum over the ten lanes of a group (rotations by 1, 2, 4 and the two leftovers); every lane of the group gets the total
+__device__ __forceinline__ float grp_sum(float v, int gbase, int h, bool lane_ok) {
+    auto rot = [&](float x, int k) {
+        const int src = lane_ok ? gbase + (h + k >= SW_H ? h + k - SW_H : h + k) : (gbase + h);
+        return __shfl_sync(0xffffffffu, x, src);
+    };
+    const float s1 = v + rot(v, 1);          // 2 consecutive
+    const float s2 = s1 + rot(s1, 2);        // 4
+    const float s4 = s2 + rot(s2, 4);        // 8
+    return s4 + rot(s1, 8);                  // + elements 8, 9
+}
+
+// per-lane layer-1 work of one input d: silu, 1 - moving_up, and the branch factor r of basis j = h
+template <int BR>
+__device__ __forceinline__ void sw_l1_own(const float* __restrict__ sm, const SNLayout& L, int d, int h, float x, float prev,
+                                          float gl1, float& silu, float& sg, float& omu, float& ex, float& r) {
+    sg = rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));
+    silu = x * sg;
+    const float4 bp = reinterpret_cast<const float4*>(sm + L.l1_bp)[d * SW_NB + h];
+    omu = 0.f;
+    ex = 0.f;
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) {
+        omu = rcp_approx(1.0f + ex2_approx(gl1 * (x - prev)));
+        ex = ferro_ex(x, gl1);
+        const float cn = rcp_approx(1.0f + fminf(ex * bp.x, 1073741824.0f));
+        const float t = fmaf(bp.w, omu * cn, fmaf(bp.y, x, bp.z));
+        r = rcp_approx(1.0f + ex2_approx(fminf(t, FETODE_EXP_CLAMP)));
+    } else {
+        r = rcp_approx(1.0f + ex2_approx(fminf(fmaf(x, bp.x, bp.y), FETODE_EXP_CLAMP)));
+    }
+}
+
+// One right-hand side for lane (g, h).  y / prev1 are replicated over the group; prev2 is this lane's.  Returns out[2]
+// (replicated) and leaves this lane's hidden pre-activation in x2.
+template <int BR>
+__device__ __forceinline__ void sw_rhs(const float* __restrict__ sm, const SNLayout& L, int gbase, int h, bool lane_ok,
+                                       const float (&y)[SW_D], float (&prev1)[SW_D], float& prev2, float (&out)[SW_D],
+                                       float& x2_out) {
+    constexpr int NB = SW_NB;
+    const int FU = L.FU;
+    const float gl1 = sm[L.hdr], gl2 = sm[L.hdr + 1];
+    const float* rec = sm + L.rec0 + h * L.REC;
+    float acc = rec[L.r_b1];
+#pragma unroll
+    for (int d = 0; d < SW_D; ++d) {
+        const float x = y[d];
+        float silu, sg, omu, ex, r;
+        sw_l1_own<BR>(sm, L, d, h, x, prev1[d], gl1, silu, sg, omu, ex, r);
+        prev1[d] = x;
+        const float* wu = rec + L.r_wu1 + d * FU;
+        acc = fmaf(wu[0], silu, acc);
+#pragma unroll
+        for (int j = 0; j < NB; ++j) acc = fmaf(wu[1 + j], __shfl_sync(0xffffffffu, r, lane_ok ? gbase + j : gbase + h), acc);
+        const float4 gi = reinterpret_cast<const float4*>(sm + L.l1_gi)[d];
+        if (x >= gi.x && x < gi.z) {                      // uniform over the group (x is replicated)
+            const float* kp = sm + L.l1_kn + d * L.NKP;
+            const int m = bspline_interval(x, kp, gi.x, gi.y, L.NK);
+            float v[4];
+            bspline3_local(x, kp, sm + L.l1_rd1 + d * L.NKP, sm + L.l1_rd2 + d * L.NKP, sm + L.l1_rd3 + d * L.NKP, m + 3, v);
+            const float* ws = rec + L.r_ws1 + d * L.SPP + m;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc = fmaf(ws[c], v[c], acc);
+        }
+    }
+    // ---- layer 2, input h
+    const float x = acc;
+    x2_out = x;
+    const float sl = x * rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));
+    float omu = 0.f;
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) omu = rcp_approx(1.0f + ex2_approx(gl2 * (x - prev2)));
+    prev2 = x;
+    float r2[NB];
+    branch_eval<NB, BR>(x, omu, gl2, reinterpret_cast<const float4*>(rec + L.r_bp), r2);
+    const float2* wu2 = reinterpret_cast<const float2*>(rec + L.r_wu2);
+    float p0 = wu2[0].x * sl, p1 = wu2[0].y * sl;
+#pragma unroll
+    for (int j = 0; j < NB; ++j) { const float2 w = wu2[1 + j]; p0 = fmaf(w.x, r2[j], p0); p1 = fmaf(w.y, r2[j], p1); }
+    const float4 gi = *reinterpret_cast<const float4*>(rec + L.r_gi);
+    if (x >= gi.x && x < gi.z) {
+        const float* kp = rec + L.r_kn;
+        const int m = bspline_interval(x, kp, gi.x, gi.y, L.NK);
+        float v[4];
+        bspline3_local(x, kp, rec + L.r_rd1, rec + L.r_rd2, rec + L.r_rd3, m + 3, v);
+        const float2* ws = reinterpret_cast<const float2*>(rec + L.r_ws2) + m;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { p0 = fmaf(ws[c].x, v[c], p0); p1 = fmaf(ws[c].y, v[c], p1); }
+    }
+    const float4 b2 = *reinterpret_cast<const float4*>(sm + L.b2);
+    out[0] = grp_sum(p0, gbase, h, lane_ok) + b2.x;
+    out[1] = grp_sum(p1, gbase, h, lane_ok) + b2.y;
+}
+
+template <int BR>
+__global__ void __launch_bounds__(SW_THREADS) smallnet_wide_fwd_kernel(const SWArgs a) {
+    extern __shared__ float4 sw_smem4[];
+    float* sm = reinterpret_cast<float*>(sw_smem4);
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    constexpr int SF = FERRO ? SW_D + SW_H : 0;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < L.total / 4; i += SW_THREADS) sw_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    __syncthreads();
+    const bool lane_ok = lane < SW_GRP * SW_H;
+    const int g = lane_ok ? lane / SW_H : 0, h = lane_ok ? lane % SW_H : 0, gbase = lane_ok ? g * SW_H : lane;
+    const long long n_tri = (a.B + SW_GRP - 1) / SW_GRP;
+    for (long long tri = (long long)blockIdx.x * SW_WARPS + warp; tri < n_tri; tri += (long long)gridDim.x * SW_WARPS) {
+        const long long t = tri * SW_GRP + g;
+        const bool live = lane_ok && t < a.B;
+        const long long tt = live ? t : 0;
+        float y[SW_D], prev1[SW_D], prev2 = 0.f;
+#pragma unroll
+        for (int d = 0; d < SW_D; ++d) { y[d] = a.y0[tt * SW_D + d]; prev1[d] = 0.f; }
+        if (FERRO && !a.state_is_zero) {
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) prev1[d] = a.state[tt * SF + d];
+            prev2 = a.state[tt * SF + SW_D + h];
+        }
+        for (int step = 0; step < a.n_steps; ++step) {
+            float* ck = a.ckpt ? a.ckpt + (((size_t)step * SW_SLOTS) * a.B + tt) * SW_REC : nullptr;
+            const size_t slot_stride = (size_t)a.B * SW_REC;
+            if (ck && live) {
+                if (h < SW_D) ck[h] = prev1[h];
+                ck[SW_D + h] = prev2;
+            }
+            float ks[4][SW_D], ys[SW_D];
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) ys[d] = y[d];
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                if (s < a.nst) {
+                    float x2;
+                    sw_rhs<BR>(sm, L, gbase, h, lane_ok, ys, prev1, prev2, ks[s], x2);
+                    if (ck && live) {
+                        float* c = ck + (size_t)(1 + s) * slot_stride;
+                        if (h < SW_D) c[h] = ys[h];
+                        c[SW_D + h] = x2;
+                    }
+                    if (s + 1 < a.nst) {
+#pragma unroll
+                        for (int d = 0; d < SW_D; ++d) {
+                            float acc = 0.f;
+#pragma unroll
+                            for (int r = 0; r <= s; ++r) acc = fmaf(a.A[s + 1][r], ks[r][d], acc);
+                            ys[d] = fmaf(a.dt, acc, y[d]);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) {
+                float acc = 0.f;
+#pragma unroll
+                for (int s = 0; s < 4; ++s)
+                    if (s < a.nst) acc = fmaf(a.bw[s], ks[s][d], acc);
+                y[d] = fmaf(a.dt, acc, y[d]);
+            }
+            if (a.traj && (step + 1) % a.dump_every == 0 && live && h < SW_D)
+                a.traj[((size_t)((step + 1) / a.dump_every - 1) * a.B + tt) * SW_D + h] = y[h];
+        }
+        if (live) {
+            if (h < SW_D) a.y_out[tt * SW_D + h] = y[h];
+            if (FERRO && a.state) {
+                if (h < SW_D) a.state[tt * SF + h] = prev1[h];
+                a.state[tt * SF + SW_D + h] = prev2;
+            }
+        }
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------
+// reverse sweep
+// ------------------------------------------------------------------------------------------
+// private accumulator columns of lane (g, h), F = 1 + 8 + NB features (0 = silu, 1 + s = spline s, 9 + j = branch j)
+constexpr int SW_F = 1 + 8 + SW_NB;
+constexpr int SW_C_W2 = 0;                          // [f][o]
+constexpr int SW_C_BP2 = SW_C_W2 + SW_F * SW_D;      // c0[j] | c1[j]
+constexpr int SW_C_W1 = SW_C_BP2 + 2 * SW_NB;        // [d][f]
+constexpr int SW_C_GS1 = SW_C_W1 + SW_D * SW_F;
+constexpr int SW_C_BP1 = SW_C_GS1 + 1;               // c0[d] | c1[d]  of basis j = h
+constexpr int SW_C_GS2 = SW_C_BP1 + 2 * SW_D;        // lanes h < D
+constexpr int SW_NACC = SW_C_GS2 + 1;
+constexpr int SW_TSTRIDE = SW_NB + 1;                // transpose tile: [d][lane][j], padded
+
+// Adjoint of one right-hand side for lane (g, h): gk (replicated) -> gin (replicated); parameter contributions go to
+// this lane's accumulator columns acc[c * 32].  x2 is the saved hidden pre-activation of this stage.
+template <int BR>
+__device__ __forceinline__ void sw_rhs_bwd(const float* __restrict__ sm, const SNLayout& L, int gbase, int h, int lane,
+                                           bool lane_ok, const float (&y)[SW_D], const float (&pin1)[SW_D], float pin2,
+                                           float x2, const float (&gk)[SW_D], float (&gin)[SW_D], float* acc, float* tile) {
+    constexpr int NB = SW_NB, D = SW_D, H = SW_H;
+    const int FU = L.FU;
+    const float gl1 = sm[L.hdr], gl2 = sm[L.hdr + 1], al1 = sm[L.hdr + 2], al2 = sm[L.hdr + 3];
+    const float* rec = sm + L.rec0 + h * L.REC;
+    const float* raw1 = sm + L.raw1;
+    const float* raw2 = sm + L.raw2;
+    auto ACC = [&](int c) -> float& { return acc[c * 32]; };
+    // ---- layer-2 features of the saved pre-activation, d(loss)/d(x2)
+    const float x = x2;
+    const float sg = rcp_approx(1.0f + ex2_approx(-FETODE_LOG2E * x));
+    const float sl = x * sg;
+    float omu = 0.f;
+    if constexpr (BR == FETODE_BRANCH_FERRO2D) omu = rcp_approx(1.0f + ex2_approx(gl2 * (x - pin2)));
+    float r2[NB], cn2[NB];
+    branch_eval<NB, BR>(x, omu, gl2, reinterpret_cast<const float4*>(rec + L.r_bp), r2,
+                        BR == FETODE_BRANCH_FERRO2D ? cn2 : nullptr);
+    const float2* wu2 = reinterpret_cast<const float2*>(rec + L.r_wu2);
+    const float g0 = gk[0], g1 = gk[1];
+    float gx2 = fmaf(g0, wu2[0].x, g1 * wu2[0].y) * sg * fmaf(x, 1.0f - sg, 1.0f);
+    ACC(SW_C_W2 + 0) += sl * g0;
+    ACC(SW_C_W2 + 1) += sl * g1;
+    {
+        const float4 gi = *reinterpret_cast<const float4*>(rec + L.r_gi);
+        if (x >= gi.x && x < gi.z) {
+            const float* kp = rec + L.r_kn;
+            const int m = bspline_interval(x, kp, gi.x, gi.y, L.NK);
+            float v[4], dv[4];
+            bspline3_local_d(x, kp, rec + L.r_rd1, rec + L.r_rd2, rec + L.r_rd3, m + 3, v, dv);
+            const float2* ws = reinterpret_cast<const float2*>(rec + L.r_ws2) + m;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                gx2 = fmaf(dv[c], fmaf(g0, ws[c].x, g1 * ws[c].y), gx2);
+                const int sidx = m - 3 + c;                   // spline coefficient index (rows outside [0, 8) are padding)
+                if (sidx >= 0 && sidx < 8) {
+                    ACC(SW_C_W2 + (1 + sidx) * D) += v[c] * g0;
+                    ACC(SW_C_W2 + (1 + sidx) * D + 1) += v[c] * g1;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+        const float2 w = wu2[1 + j];
+        const float Gj = fmaf(g0, w.x, g1 * w.y);
+        const float4 bp = reinterpret_cast<const float4*>(rec + L.r_bp)[j];
+        float gx, c0, c1;
+        branch_bwd<BR, true>(x, omu, gl2, al2, bp.x, r2[j], Gj, raw2[h * NB + j], raw2[(H + h) * NB + j], gx, c0, c1,
+                             BR == FETODE_BRANCH_FERRO2D ? cn2[j] : 0.f);
+        gx2 += gx;
+        ACC(SW_C_W2 + (9 + j) * D) += r2[j] * g0;
+        ACC(SW_C_W2 + (9 + j) * D + 1) += r2[j] * g1;
+        ACC(SW_C_BP2 + j) += c0;
+        ACC(SW_C_BP2 + NB + j) += c1;
+    }
+    ACC(SW_C_GS1) += gx2;
+    if (h < D) ACC(SW_C_GS2) += (h == 0 ? g0 : g1);
+    // ---- layer 1: features of the stage input, W1 columns of unit h, adjoints back to the inputs
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const float xd = y[d];
+        float silu, sg1, omu1, ex1, r;
+        sw_l1_own<BR>(sm, L, d, h, xd, pin1[d], gl1, silu, sg1, omu1, ex1, r);
+        const float* wu = rec + L.r_wu1 + d * FU;
+        ACC(SW_C_W1 + d * SW_F) += silu * gx2;
+        float wd = gx2 * wu[0] * sg1 * fmaf(xd, 1.0f - sg1, 1.0f);            // silu' part of d(loss)/d(x_d), this unit's share
+        float* trow = tile + (d * 32 + lane) * SW_TSTRIDE;
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+            const float rj = __shfl_sync(0xffffffffu, r, lane_ok ? gbase + j : gbase + h);
+            ACC(SW_C_W1 + d * SW_F + 9 + j) += rj * gx2;
+            trow[j] = gx2 * wu[1 + j];                                      // this unit's share of d(loss)/d r1[d][j]
+        }
+        const float4 gi = reinterpret_cast<const float4*>(sm + L.l1_gi)[d];
+        if (xd >= gi.x && xd < gi.z) {
+            const float* kp = sm + L.l1_kn + d * L.NKP;
+            const int m = bspline_interval(xd, kp, gi.x, gi.y, L.NK);
+            float v[4], dv[4];
+            bspline3_local_d(xd, kp, sm + L.l1_rd1 + d * L.NKP, sm + L.l1_rd2 + d * L.NKP, sm + L.l1_rd3 + d * L.NKP,
+                             m + 3, v, dv);
+            const float* ws = rec + L.r_ws1 + d * L.SPP + m;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                wd = fmaf(gx2 * ws[c], dv[c], wd);
+                const int sidx = m - 3 + c;
+                if (sidx >= 0 && sidx < 8) ACC(SW_C_W1 + d * SW_F + 1 + sidx) += v[c] * gx2;
+            }
+        }
+        __syncwarp();
+        // d(loss)/d r1[d][j = h]: the shares of the ten units of this trajectory
+        float G1 = 0.f;
+        if (lane_ok) {
+#pragma unroll
+            for (int hh = 0; hh < H; ++hh) G1 += tile[(d * 32 + gbase + hh) * SW_TSTRIDE + h];
+        }
+        __syncwarp();
+        if constexpr (NB > 0) {
+            const float4 bp = reinterpret_cast<const float4*>(sm + L.l1_bp)[d * NB + h];
+            float gx, c0, c1;
+            branch_bwd<BR>(xd, omu1, gl1, al1, ex1 * bp.x, r, G1, raw1[d * NB + h], raw1[(D + d) * NB + h], gx, c0, c1);
+            wd += gx;
+            ACC(SW_C_BP1 + d) += c0;
+            ACC(SW_C_BP1 + D + d) += c1;
+        }
+        gin[d] = grp_sum(wd, gbase, h, lane_ok);
+    }
+}
+
+template <int BR>
+__global__ void __launch_bounds__(SW_THREADS) smallnet_wide_bwd_kernel(const SWArgs a) {
+    extern __shared__ float4 sw_smem4[];
+    float* sm = reinterpret_cast<float*>(sw_smem4);
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < L.total_ext / 4; i += SW_THREADS) sw_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    float* acc_all = sm + L.total_ext;                                   // [SW_WARPS][SW_NACC][32]
+    float* tile_all = acc_all + SW_WARPS * SW_NACC * 32;                 // [SW_WARPS][D][32][SW_TSTRIDE]
+    for (int i = tid; i < SW_WARPS * SW_NACC * 32; i += SW_THREADS) acc_all[i] = 0.f;
+    __syncthreads();
+    float* acc = acc_all + warp * SW_NACC * 32 + lane;
+    float* tile = tile_all + warp * SW_D * 32 * SW_TSTRIDE;
+    const bool lane_ok = lane < SW_GRP * SW_H;
+    const int g = lane_ok ? lane / SW_H : 0, h = lane_ok ? lane % SW_H : 0, gbase = lane_ok ? g * SW_H : lane;
+    const long long n_tri = (a.B + SW_GRP - 1) / SW_GRP;
+    const size_t slot_stride = (size_t)a.B * SW_REC;
+    for (long long tri = (long long)blockIdx.x * SW_WARPS + warp; tri < n_tri; tri += (long long)gridDim.x * SW_WARPS) {
+        const long long t = tri * SW_GRP + g;
+        const bool live = lane_ok && t < a.B;
+        const long long tt = live ? t : 0;
+        float gy[SW_D];
+#pragma unroll
+        for (int d = 0; d < SW_D; ++d) gy[d] = (live && a.g_yout) ? a.g_yout[tt * SW_D + d] : 0.f;
+        for (int step = a.n_steps - 1; step >= 0; --step) {
+            if (a.g_traj && (step + 1) % a.dump_every == 0 && live) {
+                const float* gt = a.g_traj + ((size_t)((step + 1) / a.dump_every - 1) * a.B + tt) * SW_D;
+#pragma unroll
+                for (int d = 0; d < SW_D; ++d) gy[d] += gt[d];
+            }
+            const float* ck = a.ckpt + (((size_t)step * SW_SLOTS) * a.B + tt) * SW_REC;
+            float ys[5][SW_D], x2s[5];                                   // slot 0 = the snapshots at the step start
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+                if (q <= a.nst) {
+                    const float* c = ck + (size_t)q * slot_stride;
+                    ys[q][0] = c[0]; ys[q][1] = c[1]; x2s[q] = c[SW_D + h];
+                } else { ys[q][0] = ys[q][1] = 0.f; x2s[q] = 0.f; }
+            }
+            float gys[4][SW_D], gnext[SW_D];
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) gnext[d] = gy[d];
+#pragma unroll
+            for (int s = 3; s >= 0; --s) {
+                if (s < a.nst) {
+                    float gk[SW_D], gin[SW_D];
+#pragma unroll
+                    for (int d = 0; d < SW_D; ++d) {
+                        float v = a.bw[s] * gy[d];
+#pragma unroll
+                        for (int q = s + 1; q < 4; ++q)
+                            if (q < a.nst) v = fmaf(a.A[q][s], gys[q][d], v);
+                        gk[d] = live ? a.dt * v : 0.f;               // dead lanes contribute exact zeros
+                    }
+                    // stage s saw prev = the previous stage's input / pre-activation (slot s = stage s-1, slot 0 = step start)
+                    sw_rhs_bwd<BR>(sm, L, gbase, h, lane, lane_ok, ys[1 + s], ys[s], FERRO ? x2s[s] : 0.f, x2s[1 + s], gk,
+                                   gin, acc, tile);
+#pragma unroll
+                    for (int d = 0; d < SW_D; ++d) { gys[s][d] = gin[d]; gnext[d] += gin[d]; }
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) gy[d] = gnext[d];
+        }
+        if (live && h < SW_D) a.g_y0[tt * SW_D + h] = gy[h];
+    }
+    // ---- flush: sum the lanes that own the same parameter (3 groups x SW_WARPS warps), one atomic per parameter and CTA
+    __syncthreads();
+    const SNGfoldW gf = snw_gfold(SW_D, SW_H, SW_F, SW_NB);
+    for (int i = tid; i < SW_NACC * SW_H; i += SW_THREADS) {
+        const int c = i / SW_H, hh = i % SW_H;
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < SW_WARPS; ++w)
+#pragma unroll
+            for (int gg = 0; gg < SW_GRP; ++gg) v += acc_all[(w * SW_NACC + c) * 32 + gg * SW_H + hh];
+        if (v == 0.f) continue;
+        int dst = -1;
+        if (c < SW_C_BP2) { const int f = c / SW_D, o = c % SW_D; dst = gf.ws2 + (hh * SW_F + f) * SW_D + o; }
+        else if (c < SW_C_W1) { const int q = c - SW_C_BP2; dst = gf.bp2 + (q / SW_NB) * SW_H * SW_NB + hh * SW_NB + q % SW_NB; }
+        else if (c < SW_C_GS1) { const int q = c - SW_C_W1; dst = gf.ws1 + q * SW_H + hh; }         // q = d * F + f
+        else if (c == SW_C_GS1) dst = gf.gsum1 + hh;
+        else if (c < SW_C_GS2) { const int q = c - SW_C_BP1; dst = gf.bp1 + (q / SW_D) * SW_D * SW_NB + (q % SW_D) * SW_NB + hh; }
+        else if (hh < SW_D) dst = gf.gsum2 + hh;
+        if (dst >= 0) atomicAdd(a.gfold + dst, v);
+    }
+}
+
+}  // namespace fetode
+
+using namespace fetode;
+
+static bool snw_has(const fetode_smallnet_t* net) {
+    return net && net->n_layers == 2 && net->widths[0] == SW_D && net->widths[1] == SW_H && net->widths[2] == SW_D &&
+           net->grid_size == SW_G && net->spline_order == 3 && net->num_basis == SW_NB &&
+           (net->branch == FETODE_BRANCH_FERRO2D || net->branch == FETODE_BRANCH_LOGISTIC);
+}
+
+static int snw_tableau(int tableau, SWArgs& a) {
+    for (int i = 0; i < 4; ++i) { a.bw[i] = 0.f; for (int j = 0; j < 4; ++j) a.A[i][j] = 0.f; }
+    switch (tableau) {
+        case FETODE_TABLEAU_EULER: a.nst = 1; a.bw[0] = 1.f; break;
+        case FETODE_TABLEAU_MIDPOINT: a.nst = 2; a.A[1][0] = 0.5f; a.bw[1] = 1.f; break;
+        case FETODE_TABLEAU_RK4:
+            a.nst = 4; a.A[1][0] = 0.5f; a.A[2][1] = 0.5f; a.A[3][2] = 1.f;
+            a.bw[0] = a.bw[3] = (float)(1.0 / 6.0); a.bw[1] = a.bw[2] = (float)(1.0 / 3.0);
+            break;
+        case FETODE_TABLEAU_RK4_38:
+            a.nst = 4; a.A[1][0] = (float)(1.0 / 3.0); a.A[2][0] = (float)(-1.0 / 3.0); a.A[2][1] = 1.f;
+            a.A[3][0] = 1.f; a.A[3][1] = -1.f; a.A[3][2] = 1.f;
+            a.bw[0] = a.bw[3] = 0.125f; a.bw[1] = a.bw[2] = 0.375f;
+            break;
+        default: return FETODE_EINVAL;
+    }
+    return FETODE_OK;
+}
+
+static unsigned snw_grid(long long B, int ctas_per_sm) {
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long n_tri = (B + SW_GRP - 1) / SW_GRP;
+    const long long want = (n_tri + SW_WARPS - 1) / SW_WARPS;
+    return (unsigned)std::max(1LL, std::min<long long>(want, (long long)sms * ctas_per_sm));
+}
+
+extern "C" int fetode_smallnet_wide_supported(const fetode_smallnet_t* net) {
+    return snw_has(net) ? FETODE_OK : FETODE_EUNSUPPORTED;
+}
+
+extern "C" int64_t fetode_smallnet_wide_ckpt_floats(const fetode_smallnet_t* net, int64_t B, int32_t n_steps) {
+    if (!snw_has(net) || B < 0 || n_steps < 0) return -1;
+    return (int64_t)n_steps * SW_SLOTS * B * SW_REC;
+}
+
+extern "C" int fetode_smallnet_wide_fwd(const fetode_smallnet_t* net, const float* packed, int tableau, const float* y0,
+                                        float* y_out, float* state, int state_is_zero, int64_t B, double dt,
+                                        int32_t n_steps, float* traj, int32_t dump_every, float* ckpt, void* stream) {
+    if (!snw_has(net)) return FETODE_EUNSUPPORTED;
+    FETODE_CHECK_ARG(packed && y0 && y_out && B >= 0 && n_steps >= 0);
+    if (B == 0) return FETODE_OK;
+    if (net->branch == FETODE_BRANCH_FERRO2D && !state_is_zero) FETODE_CHECK_ARG(state != nullptr);
+    if (traj) FETODE_CHECK_ARG(dump_every >= 1);
+    SWArgs a{};
+    int rc = snw_tableau(tableau, a);
+    if (rc) return rc;
+    a.packed = packed; a.y0 = y0; a.y_out = y_out; a.state = state; a.traj = traj; a.ckpt = ckpt;
+    a.B = B; a.dt = (float)dt; a.n_steps = n_steps; a.dump_every = dump_every > 0 ? dump_every : 1;
+    a.state_is_zero = state_is_zero;
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    const size_t smem = (size_t)L.total * 4;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = snw_grid(B, 4);
+    if (net->branch == FETODE_BRANCH_FERRO2D) {
+        auto k = smallnet_wide_fwd_kernel<FETODE_BRANCH_FERRO2D>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    } else {
+        auto k = smallnet_wide_fwd_kernel<FETODE_BRANCH_LOGISTIC>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_smallnet_wide_bwd(const fetode_smallnet_t* net, const float* packed, int tableau, const float* ckpt,
+                                        const float* g_yout, const float* g_traj, int32_t dump_every, float* g_y0,
+                                        float* gfold, int64_t B, double dt, int32_t n_steps, void* stream) {
+    if (!snw_has(net)) return FETODE_EUNSUPPORTED;
+    FETODE_CHECK_ARG(packed && g_y0 && gfold && B >= 0 && n_steps >= 0 && (n_steps == 0 || ckpt));
+    if (g_traj) FETODE_CHECK_ARG(dump_every >= 1);
+    if (B == 0) return FETODE_OK;
+    SWArgs a{};
+    int rc = snw_tableau(tableau, a);
+    if (rc) return rc;
+    a.packed = packed; a.ckpt = const_cast<float*>(ckpt); a.g_yout = g_yout; a.g_traj = g_traj; a.g_y0 = g_y0; a.gfold = gfold;
+    a.B = B; a.dt = (float)dt; a.n_steps = n_steps; a.dump_every = dump_every > 0 ? dump_every : 1;
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    const size_t smem = (size_t)(L.total_ext + SW_WARPS * SW_NACC * 32 + SW_WARPS * SW_D * 32 * SW_TSTRIDE) * 4;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = snw_grid(B, 3);
+    if (net->branch == FETODE_BRANCH_FERRO2D) {
+        auto k = smallnet_wide_bwd_kernel<FETODE_BRANCH_FERRO2D>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    } else {
+        auto k = smallnet_wide_bwd_kernel<FETODE_BRANCH_LOGISTIC>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}

@@ -81,7 +81,8 @@ def lib() -> C.CDLL:
         _lib.fetode_strerror.argtypes = [C.c_int]
         for name in ("fetode_kanlinear_wcat_floats", "fetode_kanlinear_bwd_ws_floats",
                      "fetode_smallnet_packed_floats", "fetode_smallnet_state_floats",
-                     "fetode_smallnet_ckpt_floats", "fetode_smallnet_gfold_floats"):
+                     "fetode_smallnet_ckpt_floats", "fetode_smallnet_gfold_floats",
+                     "fetode_smallnet_wide_ckpt_floats"):
             if hasattr(_lib, name):
                 getattr(_lib, name).restype = C.c_int64
     return _lib

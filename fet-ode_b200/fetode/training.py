@@ -34,6 +34,26 @@ def _runs(times: List[float], uniform_dt: Optional[float]):
     return out
 
 
+WIDE_MAX_ROWS = 12288
+
+
+def _wide_ok(plan, B: int) -> bool:
+    """Use the hidden-units-on-lanes kernels (csrc/smallnet_wide.cu) for this solve?  They win while the batch does
+    not fill the machine -- measured fwd+bwd+Adam of the LV step (34 RK4 steps, B200): B = 1: 0.84 ms vs 4.3 ms,
+    B = 4096: 1.8 vs 4.7, B = 8192: 2.8 vs 4.7, B = 16384: 5.3 vs 4.8, B = 65536: 19.9 vs 9.8 -- the lane-per-trajectory
+    pair takes over from ~14 000 rows.  FETODE_SN_WIDE=0 / 1 forces either (A/B timing; read once)."""
+    global _WIDE_ENV
+    if _WIDE_ENV is None:
+        import os
+        _WIDE_ENV = os.environ.get("FETODE_SN_WIDE", "")
+    if lib().fetode_smallnet_wide_supported(C.byref(plan.net)) != 0 or _WIDE_ENV == "0":
+        return False
+    return _WIDE_ENV == "1" or B <= WIDE_MAX_ROWS
+
+
+_WIDE_ENV = None
+
+
 class FusedRKFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, model, times, kind, uniform_dt, y0, *params):
@@ -56,17 +76,27 @@ class FusedRKFn(torch.autograd.Function):
         ckpts = []
         cur = y0c
         NC = D + plan.state_floats
+        wide = _wide_ok(plan, B)
+        img = plan.image()
         for (i, n, dt) in runs:
-            ck = torch.empty(n, NC, B, dtype=torch.float32, device=y0c.device)
-            plan.rk_fwd(TABLEAU[kind], cur, dt, n, state=st, state_is_zero=fresh, traj=out[i + 1:i + n + 1],
-                        dump_every=1, ckpt=ck, y_out=out[i + n])
+            if wide:
+                nck = int(lib().fetode_smallnet_wide_ckpt_floats(C.byref(plan.net), C.c_int64(B), C.c_int32(n)))
+                ck = torch.empty(max(nck, 1), dtype=torch.float32, device=y0c.device)
+                check(lib().fetode_smallnet_wide_fwd(C.byref(plan.net), ptr(img), C.c_int(TABLEAU[kind]), ptr(cur),
+                                                     ptr(out[i + n]), ptr(st), C.c_int(1 if fresh else 0), C.c_int64(B),
+                                                     C.c_double(dt), C.c_int32(n), ptr(out[i + 1:i + n + 1]), C.c_int32(1),
+                                                     ptr(ck), stream()), "smallnet_wide_fwd")
+            else:
+                ck = torch.empty(n, NC, B, dtype=torch.float32, device=y0c.device)
+                plan.rk_fwd(TABLEAU[kind], cur, dt, n, state=st, state_is_zero=fresh, traj=out[i + 1:i + n + 1],
+                            dump_every=1, ckpt=ck, y_out=out[i + n])
             ckpts.append(ck)
             fresh = False
             cur = out[i + n]
         if ferro:
             model.adopt_state(st)
-        ctx.model, ctx.plan, ctx.kind, ctx.runs, ctx.ckpts = model, plan, kind, runs, ckpts
-        ctx.image = plan.image()
+        ctx.model, ctx.plan, ctx.kind, ctx.runs, ctx.ckpts, ctx.wide = model, plan, kind, runs, ckpts, wide
+        ctx.image = img
         ctx.shape = (T, B, D)
         return out
 
@@ -81,10 +111,11 @@ class FusedRKFn(torch.autograd.Function):
         carry = None
         for (i, n, dt), ck in zip(reversed(ctx.runs), reversed(ctx.ckpts)):
             g_y0 = torch.empty(B, D, dtype=torch.float32, device=dev)
-            check(L.fetode_smallnet_rk_bwd(C.byref(plan.net), ptr(ctx.image), C.c_int(TABLEAU[ctx.kind]), ptr(ck),
-                                           ptr(carry), ptr(g_out[i + 1:i + n + 1]), C.c_int32(1), ptr(g_y0),
-                                           ptr(gfold), C.c_int64(B), C.c_double(dt), C.c_int32(n), stream()),
-                  "smallnet_rk_bwd")
+            fn = L.fetode_smallnet_wide_bwd if ctx.wide else L.fetode_smallnet_rk_bwd
+            check(fn(C.byref(plan.net), ptr(ctx.image), C.c_int(TABLEAU[ctx.kind]), ptr(ck),
+                     ptr(carry), ptr(g_out[i + 1:i + n + 1]), C.c_int32(1), ptr(g_y0),
+                     ptr(gfold), C.c_int64(B), C.c_double(dt), C.c_int32(n), stream()),
+                  "smallnet_wide_bwd" if ctx.wide else "smallnet_rk_bwd")
             carry = g_y0
         gy0 = g_out[0] if carry is None else carry + g_out[0]
         # chain rule folded -> reference parameters

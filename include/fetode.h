@@ -202,6 +202,22 @@ FETODE_API int fetode_smallnet_rk_bwd(const fetode_smallnet_t* net, const float*
 FETODE_API int fetode_smallnet_unfold(const fetode_smallnet_t* net, const fetode_kanlayer_t* layers, float* gfold,
                            const fetode_kanlayer_grads_t* grads, void* stream);
 /* one RHS evaluation y -> f(y) (KAN.forward), same state rules */
+/* The same fused integration and its reverse sweep with the HIDDEN UNITS on the lanes (csrc/smallnet_wide.cu): a warp
+ * holds three trajectories, ten lanes each.  Built for training (train_kanfet_node_predprey.py:246-257: the reference's
+ * run is ONE trajectory): the dependency chain of a right-hand side is 3 feature evaluations instead of 12, and every
+ * parameter-gradient column is accumulated privately by the lane that owns the hidden unit, reduced once per launch.
+ * Supported: widths [2,10,2], grid 5, order 3, num_basis 10, branch LOGISTIC | FERRO2D; `packed` as fetode_smallnet_pack.
+ * ckpt: fetode_smallnet_wide_ckpt_floats(net, B, n_steps) floats = [n_steps][5][B][12] (slot 0: hysteresis snapshots at
+ * the step start, slot 1+s: input and hidden pre-activations of stage s); written by _wide_fwd (NULL: not kept), read by
+ * _wide_bwd.  Every other argument as fetode_smallnet_rk_fwd / _rk_bwd; gfold is the same folded-gradient buffer. */
+FETODE_API int fetode_smallnet_wide_supported(const fetode_smallnet_t* net);
+FETODE_API int64_t fetode_smallnet_wide_ckpt_floats(const fetode_smallnet_t* net, int64_t B, int32_t n_steps);
+FETODE_API int fetode_smallnet_wide_fwd(const fetode_smallnet_t* net, const float* packed, int tableau, const float* y0,
+                         float* y_out, float* state, int state_is_zero, int64_t B, double dt, int32_t n_steps,
+                         float* traj, int32_t dump_every, float* ckpt, void* stream);
+FETODE_API int fetode_smallnet_wide_bwd(const fetode_smallnet_t* net, const float* packed, int tableau, const float* ckpt,
+                         const float* g_yout, const float* g_traj, int32_t dump_every, float* g_y0, float* gfold,
+                         int64_t B, double dt, int32_t n_steps, void* stream);
 FETODE_API int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
                         float* dy, float* state, int state_is_zero, int64_t B, void* stream);
 

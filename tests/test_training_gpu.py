@@ -122,3 +122,37 @@ def test_dopri5_on_kanfet_rhs_and_backward(cuda):
     got[:, 0, :].square().mean().backward()
     assert xg.grad is not None and torch.isfinite(xg.grad).all()
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters())
+
+
+@pytest.mark.parametrize("B", [1, 5, 300])
+@pytest.mark.parametrize("branch", ["logistic", "ferro2d"])
+def test_both_training_kernel_pairs_agree_with_oracle_autograd(cuda, branch, B, monkeypatch):
+    """The hidden-units-on-lanes pair (csrc/smallnet_wide.cu, small batches) and the lane-per-trajectory pair
+    (smallnet_v2.cu + smallnet_bwd.cu, large batches) are selected by batch size; force each in turn on the same
+    problem: trajectory, input gradient and every parameter gradient against fp64 oracle autograd."""
+    from fetode import training
+    layers, m = fetode_kan_random([2, 10, 2], branch, seed=31 + B, device=cuda)
+    l64 = [{k: v.double().requires_grad_(k != "grid") for k, v in lay.items()} for lay in layers]
+    x0 = lv_inputs(B, 3) if B > 1 else torch.ones(1, 2)
+    n, T = 12, 0.6
+    gen = torch.Generator().manual_seed(5)
+    w = torch.randn(n + 1, B, 2, generator=gen, dtype=torch.float64)
+    x64 = x0.double().requires_grad_(True)
+    st = OL.kanfet_states(l64) if branch == "ferro2d" else None
+    f = lambda t, h: OL.kan_forward(h, l64, branch=branch, states=st)
+    want = OS.rk4_classic(f, x64, 0.0, T, n, trajectory=True)
+    (want * w).sum().backward()
+    t = torch.linspace(0, T, n + 1, dtype=torch.float64)
+    for mode in ("1", "0"):
+        monkeypatch.setattr(training, "_WIDE_ENV", mode)
+        m.zero_grad()
+        if branch == "ferro2d":
+            m.reset_state()
+        xg = x0.to(cuda).requires_grad_(True)
+        got = fetode.odeint(lambda tt, X: m(X), xg, t, method="rk4_classic")
+        assert max_rel(got, want) < 1e-4, mode
+        (got * w.float().to(cuda)).sum().backward()
+        assert max_rel(xg.grad, x64.grad) < 5e-4, mode
+        for li, layer in enumerate(m.layers):
+            for name, p in layer.named_parameters():
+                assert max_rel(p.grad, l64[li][name].grad) < 5e-4, (mode, li, name)
