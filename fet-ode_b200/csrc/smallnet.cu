@@ -277,7 +277,12 @@ static bool sn_force_v1() {
     return v == 1;
 }
 
+bool snw_prefers(const fetode_smallnet_t* net, long long B, bool wants_v1_ckpt);      // smallnet_wide.cu
+int snw_forward(const fetode_smallnet_t* net, const SNArgs& s, cudaStream_t st);
+
 static int sn_launch(const fetode_smallnet_t* net, const SNArgs& a, cudaStream_t st) {
+    // small batches: hidden units on the lanes (a dependency chain of 3 feature evaluations per right-hand side)
+    if (a.tab != TAB_RHS_ONLY && !sn_force_v1() && snw_prefers(net, a.B, a.ckpt != nullptr)) return snw_forward(net, a, st);
     if (sn2_has(net) && !sn_force_v1()) {
         const int off = sn_layout(net->widths[0], net->widths[1], net->num_basis, net->grid_size).total_ext;
         return sn2_launch(net, a, a.packed + off, st);

@@ -20,6 +20,7 @@
 // and loss.backward() through the solver (train_kanfet_node_predprey.py:254-256).  Image: the first-generation layout
 // (smallnet.cuh); folded-gradient layout: sn_gfold_layout (smallnet_bwd.cu), unfolded by fetode_smallnet_unfold.
 #include <algorithm>
+#include <cstdlib>
 #include "smallnet.cuh"
 
 namespace fetode {
@@ -450,6 +451,10 @@ __global__ void __launch_bounds__(SW_THREADS) smallnet_wide_bwd_kernel(const SWA
 
 using namespace fetode;
 
+extern "C" int fetode_smallnet_wide_fwd(const fetode_smallnet_t* net, const float* packed, int tableau, const float* y0,
+                                        float* y_out, float* state, int state_is_zero, int64_t B, double dt,
+                                        int32_t n_steps, float* traj, int32_t dump_every, float* ckpt, void* stream);
+
 static bool snw_has(const fetode_smallnet_t* net) {
     return net && net->n_layers == 2 && net->widths[0] == SW_D && net->widths[1] == SW_H && net->widths[2] == SW_D &&
            net->grid_size == SW_G && net->spline_order == 3 && net->num_basis == SW_NB &&
@@ -482,6 +487,20 @@ static unsigned snw_grid(long long B, int ctas_per_sm) {
     const long long want = (n_tri + SW_WARPS - 1) / SW_WARPS;
     return (unsigned)std::max(1LL, std::min<long long>(want, (long long)sms * ctas_per_sm));
 }
+
+namespace fetode {
+// entry for the generic forward dispatch (smallnet.cu): small batches without lane-per-trajectory checkpoints
+bool snw_prefers(const fetode_smallnet_t* net, long long B, bool wants_v1_ckpt) {
+    static int forced = -2;
+    if (forced == -2) { const char* e = getenv("FETODE_SN_WIDE_FWD"); forced = e ? atoi(e) : -1; }
+    if (!snw_has(net) || wants_v1_ckpt || forced == 0) return false;
+    return forced == 1 || B <= 8192;      // measured (1000 RK4 steps): B = 1: 4.5 vs 27 ms, 4096: 12.3 vs 27.4, 16384: 39 vs 27.6
+}
+int snw_forward(const fetode_smallnet_t* net, const SNArgs& s, cudaStream_t st) {
+    return fetode_smallnet_wide_fwd(net, s.packed, s.tab, s.y0, s.y_out, s.state, s.state_is_zero, s.B, (double)s.dt,
+                                    s.n_steps, s.traj, s.dump_every, nullptr, (void*)st);
+}
+}  // namespace fetode
 
 extern "C" int fetode_smallnet_wide_supported(const fetode_smallnet_t* net) {
     return snw_has(net) ? FETODE_OK : FETODE_EUNSUPPORTED;
