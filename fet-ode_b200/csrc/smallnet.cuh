@@ -62,6 +62,9 @@ __host__ __device__ constexpr SNLayout sn_layout(int D, int H, int NB, int G) {
     L.r_bq = r; r += NB * 4;
     L.r_wu2 = r; r += L.FU * L.DV;
     L.r_ws2 = r; r += L.SPP * L.DV;
+    r = round_up(r, 4);
+    if ((r / 4) % 2 == 0) r += 4;       // record stride = an odd number of 16-byte units: lanes that read DIFFERENT records (the
+                                        // hidden-units-on-lanes kernels) spread over the shared-memory banks (<= 2-way conflicts)
     L.REC = r;
     L.total = o + H * r;
     L.raw1 = L.total;

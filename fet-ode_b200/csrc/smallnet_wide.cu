@@ -494,7 +494,7 @@ bool snw_prefers(const fetode_smallnet_t* net, long long B, bool wants_v1_ckpt) 
     static int forced = -2;
     if (forced == -2) { const char* e = getenv("FETODE_SN_WIDE_FWD"); forced = e ? atoi(e) : -1; }
     if (!snw_has(net) || wants_v1_ckpt || forced == 0) return false;
-    return forced == 1 || B <= 8192;      // measured (1000 RK4 steps): B = 1: 4.5 vs 27 ms, 4096: 12.3 vs 27.4, 16384: 39 vs 27.6
+    return forced == 1 || B <= 12288;     // measured (1000 RK4 steps): B = 1: 3.8 vs 27 ms, 4096: 7.4 vs 27.4; 16384: ~28 vs 27.6
 }
 int snw_forward(const fetode_smallnet_t* net, const SNArgs& s, cudaStream_t st) {
     return fetode_smallnet_wide_fwd(net, s.packed, s.tab, s.y0, s.y_out, s.state, s.state_is_zero, s.B, (double)s.dt,
@@ -528,7 +528,7 @@ extern "C" int fetode_smallnet_wide_fwd(const fetode_smallnet_t* net, const floa
     constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
     const size_t smem = (size_t)L.total * 4;
     cudaStream_t st = (cudaStream_t)stream;
-    const unsigned grid = snw_grid(B, 4);
+    const unsigned grid = snw_grid(B, 6);
     if (net->branch == FETODE_BRANCH_FERRO2D) {
         auto k = smallnet_wide_fwd_kernel<FETODE_BRANCH_FERRO2D>;
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -34,14 +34,14 @@ def _runs(times: List[float], uniform_dt: Optional[float]):
     return out
 
 
-WIDE_MAX_ROWS = 12288
+WIDE_MAX_ROWS = 20480
 
 
 def _wide_ok(plan, B: int) -> bool:
     """Use the hidden-units-on-lanes kernels (csrc/smallnet_wide.cu) for this solve?  They win while the batch does
-    not fill the machine -- measured fwd+bwd+Adam of the LV step (34 RK4 steps, B200): B = 1: 0.84 ms vs 4.3 ms,
-    B = 4096: 1.8 vs 4.7, B = 8192: 2.8 vs 4.7, B = 16384: 5.3 vs 4.8, B = 65536: 19.9 vs 9.8 -- the lane-per-trajectory
-    pair takes over from ~14 000 rows.  FETODE_SN_WIDE=0 / 1 forces either (A/B timing; read once)."""
+    not fill the machine -- measured fwd+bwd+Adam of the LV step (34 RK4 steps, B200): B = 1: 0.76 ms vs 4.3 ms,
+    B = 4096: 1.4 vs 4.7, B = 16384: 4.0 vs 4.8, B = 32768: ~7.7 vs 5.7, B = 65536: 15.0 vs 9.8 -- the
+    lane-per-trajectory pair takes over from ~20 000 rows.  FETODE_SN_WIDE=0 / 1 forces either (A/B timing; read once)."""
     global _WIDE_ENV
     if _WIDE_ENV is None:
         import os
