@@ -18,7 +18,8 @@ Prints ONE JSON line (rank 0).
   fwd_bwd    BASELINE's "fwd+bwd step ms": LV training (config 1: 34 classic-RK4 steps, MSE, Adam; B = 1 as the script runs
              it and B = 65 536 per GPU) and ECG training (config 3: B = 4096 per GPU, RK4 x 8, cross-entropy, clip 1.0,
              AdamW), whole step replayed from a CUDA graph, the flat-gradient NCCL all-reduce inside the step at N > 1
-             (allreduce_ms = the collective alone), each with its roofline fraction and, at N = 1, its CPU leg
+             (allreduce_ms = the collective alone), each with its roofline fraction and, at N = 1, its CPU leg; plus the
+             config-4 ETT encoder (fwd+bwd, B = 4096) and the config-5 MNIST-Kuramoto training step (B = 1024 per GPU)
   roofline   dominant kernel of the primary workload against the FP32 CUDA-core peak measured live (FFMA probe)
   cpu_baseline (N = 1) the oracle port of the reference's PyTorch arithmetic on all host cores, bounded sample
 `--impl reference` times that CPU port alone (rank 0), same metric / config, 65 536 trajectories x 10 steps per step.
@@ -400,6 +401,66 @@ def ecg_train_section(ctx, B, tf32_peak, with_cpu):
     return out
 
 
+def ett_encoder_section(ctx, B, tf32_peak):
+    """Config 4: the wide KAN encoder of the ETT forecaster, Flatten -> KAN([336*7, 128]) -> ReLU -> KAN([128, 64])
+    (train_kan_fet_ett.py:676-681), fwd+bwd of a squared-output loss, B rows per GPU (no optimiser: the encoder is one
+    block of the forecaster)."""
+    import fetode
+    torch.manual_seed(0)
+    enc = torch.nn.Sequential(torch.nn.Flatten(), fetode.KAN([336 * 7, 128]), torch.nn.ReLU(), fetode.KAN([128, 64])).to(ctx.dev)
+    gen = torch.Generator().manual_seed(300 + ctx.rank)
+    x = torch.randn(B, 336, 7, generator=gen).to(ctx.dev)
+
+    def step():
+        enc.zero_grad(set_to_none=True)
+        enc(x).square().mean().backward()
+
+    def fwd():
+        with torch.no_grad():
+            enc(x)
+    k = 10
+    ms = ctx.timed(step, k, 3, flush=False, grad=True) / k
+    fms = ctx.timed(fwd, k, 3, flush=False) / k
+    flop_row = 12.0e6                                              # SURVEY section 8(d): encoder with the logistic branch
+    ach = 3.0 * flop_row * B / (ms * 1e-3) / 1e12
+    peak = tf32_peak / 3.0 if tf32_peak else None
+    return {"workload": "config 4: ETT encoder KAN([2352,128]) -> ReLU -> KAN([128,64]) (train_kan_fet_ett.py:676-681), fwd+bwd",
+            "rows_per_gpu": B, "ms_per_step": ms, "fwd_ms": fms, "graph_replayed": False,
+            "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
+                         "flop_per_row": flop_row, "convention": "useful FLOP, fwd+bwd = 3 x forward; TF32 dense (cuBLAS, this run) / 3"}}
+
+
+def mnist_train_section(ctx, B, fp32_peak):
+    """Config 5: KuramotoKANClassifier(steps=10, num_basis=8) training step (mnist_kuramoto_kan.py:228-283): 10 Euler
+    steps of the phase lattice + KANLinear(1568 -> 10) head, cross-entropy, fused AdamW; B images per GPU,
+    graph-replayed, flat-gradient all-reduce inside at N > 1."""
+    import torch.nn.functional as F
+
+    import fetode
+    from fetode import mnist_kuramoto_kan as MK
+    torch.manual_seed(0)
+    model = MK.KuramotoKANClassifier(kuramoto_steps=10, num_basis=8).to(ctx.dev)
+    gen = torch.Generator().manual_seed(400 + ctx.rank)
+    x = torch.rand(B, 1, 28, 28, generator=gen).to(ctx.dev)
+    y = torch.randint(0, 10, (B,), generator=gen).to(ctx.dev)
+    gopt = fetode.optim.AdamW(model.parameters(), lr=1e-3, capturable=True)
+    gstep = fetode.graphs.GraphedTrainStep(model, gopt, F.cross_entropy, x, y, warmup=2, allreduce=ctx.world > 1)
+    k = 20
+    ms = ctx.timed(lambda: gstep(gstep.x, gstep.y), k, 3, flush=False, grad=True) / k
+    ar_ms = None
+    if ctx.world > 1:
+        ar_ms = ctx.timed(lambda: ctx.dist.all_reduce(gopt.flat_grad), 20, 5, flush=False) / 20
+    ach = 3.0 * 0.83e6 * B / (ms * 1e-3) / 1e12
+    out = {"workload": "config 5: MNIST KuramotoKANClassifier(steps=10, nb=8), CE, fused AdamW (mnist_kuramoto_kan.py:228-283)",
+           "rows_per_gpu": B, "ms_per_step": ms, "graph_replayed": True, "images_per_s": B * ctx.world / (ms * 1e-3),
+           "allreduce_ms": ar_ms, "allreduce_bytes": int(gopt.flat_grad.numel()) * 4 if ctx.world > 1 else 0,
+           "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
+                        "frac": ach / fp32_peak if fp32_peak else None, "flop_per_image": 0.83e6,
+                        "convention": "SURVEY 8(d) count x 3; at 1024 images the step is ~90 launches of a few microseconds: latency-bound"}}
+    del gstep, gopt
+    return out
+
+
 def inspan_fractions(x0, yT, state, D):
     """Share of layer inputs inside the knot span [-2.2, 2.2) (where the spline term is non-zero): layer 1 = the ODE
     state (at t = 0 and at the horizon), layer 2 = the hidden pre-activations of the last right-hand-side call (the
@@ -489,7 +550,9 @@ def run_ours(args):
         fwd_bwd = {}
         for name, fn, a in (("lv_train_B1", lv_train_section, (1, fp32_peak, with_cpu)),
                             ("lv_train_B65536", lv_train_section, (65536, fp32_peak, with_cpu)),
-                            ("ecg_train_B4096", ecg_train_section, (4096, tf32_peak, with_cpu))):
+                            ("ecg_train_B4096", ecg_train_section, (4096, tf32_peak, with_cpu)),
+                            ("ett_encoder_B4096", ett_encoder_section, (4096, tf32_peak)),
+                            ("mnist_train_B1024", mnist_train_section, (1024, fp32_peak))):
             try:
                 fwd_bwd[name] = fn(ctx, *a)
             except Exception as e:                                   # noqa: BLE001 -- the primary number must still print
