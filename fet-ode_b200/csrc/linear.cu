@@ -19,6 +19,7 @@ struct GemmArgs {
     const float* A; const float* B; const float* bias; float* C;
     long long M, sAm, sAk, sBk, sBn;
     int N, K, k_per_split;
+    int accumulate;          // C += (the weight-gradient buffer is shared by every call of a step), never overwritten
 };
 
 // C[m,n] (+)= sum_k A[m*sAm + k*sAk] * B[k*sBk + n*sBn] (+ bias[n]);  C row-major [M, N].
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
             if (n >= a.N) continue;
             float v = acc[i][j];
             if (a.bias && blockIdx.z == 0) v += a.bias[n];
-            if (gridDim.z == 1) a.C[m * a.N + n] = v;
+            if (gridDim.z == 1 && !a.accumulate) a.C[m * a.N + n] = v;
             else atomicAdd(a.C + m * a.N + n, v);
         }
     }
@@ -146,6 +147,7 @@ extern "C" int fetode_linear_bwd(const float* x, const float* weight, const floa
         a.A = gy; a.sAm = 1; a.sAk = out_features;          // A(m = o, k = b) = gy[b, o]
         a.B = x; a.sBk = in_features; a.sBn = 1;            // B(k = b, n) = x[b, n]
         a.C = gweight; a.M = out_features; a.N = in_features; a.K = (int)B;
+        a.accumulate = 1;                                   // also when a tiny batch leaves a single K split
         const long long tiles = ((out_features + LG_BM - 1) / LG_BM) * (long long)((in_features + LG_BN - 1) / LG_BN);
         int splits = (int)std::max(1LL, std::min<long long>(148LL * 2 / tiles, (B + 127) / 128));
         if (splits < 2) splits = 2;                         // always the accumulate path: the buffer is added to

@@ -1,6 +1,8 @@
 """GPU parity of the fused LayerNorm + tanh-bound prologue (csrc/glue.cu) against the two torch ops the reference
 uses (train_ecg_kan_fet_nn_ode.py:459-461), forward and gradients, fp32.  Tolerance: 2e-6 of the max-norm forward
 (fp32 rounding of the statistics), 2e-5 for gradients (row reductions in a different order)."""
+import copy
+
 import pytest
 import torch
 
@@ -69,3 +71,33 @@ def test_linear_matches_torch_fp32(cuda, B, K, O, bias):
     assert max_rel(gw1, gw0) < 2e-5
     if bias:
         assert max_rel(gb1, gb0) < 2e-5
+
+
+@pytest.mark.parametrize("B", [3, 26, 33, 300])
+def test_shared_gradient_accumulators_over_repeated_calls(cuda, B):
+    """A module applied several times in one graph (once per Runge-Kutta stage) routes its parameter gradients through
+    ONE accumulator per backward pass (ops.ParamGroup): every call must ADD -- also for batches so small that the
+    weight-gradient GEMM has a single K split (regression: a 26-row shard overwrote the accumulator)."""
+    from fetode import ops
+    torch.manual_seed(B)
+    lin = torch.nn.Linear(24, 10).to(cuda)
+    ln = torch.nn.LayerNorm(24).to(cuda)
+    ref_lin, ref_ln = copy.deepcopy(lin), copy.deepcopy(ln)
+    xs = [torch.randn(B, 24, device=cuda, requires_grad=True) for _ in range(3)]
+    xr = [x.detach().clone().requires_grad_(True) for x in xs]
+    out = sum(ops.linear(ops.ln_tanh(x, ln, 1.5), lin).square().sum() for x in xs)
+    out.backward()
+    want = sum(ref_lin(1.5 * torch.tanh(ref_ln(x) / 1.5)).square().sum() for x in xr)
+    want.backward()
+    for a, b in zip(xs, xr):
+        assert max_rel(a.grad, b.grad) < 2e-4
+    for m, r in ((lin, ref_lin), (ln, ref_ln)):
+        for (n, p), q in zip(m.named_parameters(), r.parameters()):
+            assert max_rel(p.grad, q.grad) < 2e-4, n
+    # a second pass without an optimiser step accumulates on top, like torch
+    out2 = sum(ops.linear(ops.ln_tanh(x, ln, 1.5), lin).square().sum() for x in xs)
+    out2.backward()
+    want2 = sum(ref_lin(1.5 * torch.tanh(ref_ln(x) / 1.5)).square().sum() for x in xr)
+    want2.backward()
+    for (n, p), q in zip(lin.named_parameters(), ref_lin.parameters()):
+        assert max_rel(p.grad, q.grad) < 2e-4, n
