@@ -447,6 +447,220 @@ __global__ void __launch_bounds__(SW_THREADS) smallnet_wide_bwd_kernel(const SWA
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// one explicit Runge-Kutta ATTEMPT with an arbitrary tableau (<= 7 stages): the building block of the adaptive solver
+// ------------------------------------------------------------------------------------------
+// torchdiffeq's dopri5 (call sites train_kanfet_node_predprey.py:252, the reference's default LV solver) evaluates the
+// right-hand side six times per attempted step (stage 0 is the previous step's last stage: FSAL), forms the 5th-order
+// solution, an embedded error estimate and ONE error norm over the whole batch.  Here the whole attempt is one launch:
+//   k_0 given (first_eval = 1) or evaluated (first_eval = 0);  stage s input  ys_s = y + dt sum_{r<s} A[s][r] k_r ,
+//   k_s = f(ys_s) for s >= first_eval;  y1 = ys_{ns-1} (y1_last != 0);  outputs ks [ns, B, D], y1 [B, D];
+//   errsq += sum_{rows, d} ( dt sum_s E[s] k_s / (atol + rtol max(|y|, |y1|)) )^2     (one double, atomics per warp);
+//   hysteresis state advanced by every evaluated stage (also on attempts the controller later rejects, as the
+//   reference's modules are);  ckpt [1 + ns - first_eval][B][12] for the reverse sweep of an ACCEPTED attempt.
+constexpr int SW_MAXS = 7;
+
+struct SWStepArgs {
+    const float* packed;
+    const float* y;           // [B, D]
+    const float* k0;          // [B, D] when first_eval == 1
+    float* y1;                // [B, D] or null
+    float* ks;                // [ns, B, D]
+    float* state;             // [B, D + H] in/out (ferro) or null
+    float* ckpt;              // [slots, B, SW_REC] or null
+    double* errsq;            // or null
+    const float *g_y1, *g_ks; // backward inputs ([B, D] or null; [ns, B, D])
+    const float *x_y1, *x_klast, *x_y;   // optional [B, D] addends: to g_y1, to g_ks[ns-1], to the returned g_y
+    float *g_y, *g_k0, *gfold;
+    long long B;
+    float dt, rtol, atol;
+    float A[SW_MAXS][SW_MAXS], E[SW_MAXS];
+    int ns, first_eval, y1_last, state_is_zero;
+};
+
+template <int BR>
+__global__ void __launch_bounds__(SW_THREADS) smallnet_wide_step_fwd_kernel(const SWStepArgs a) {
+    extern __shared__ float4 sw_smem4[];
+    float* sm = reinterpret_cast<float*>(sw_smem4);
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    constexpr int SF = FERRO ? SW_D + SW_H : 0;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < L.total / 4; i += SW_THREADS) sw_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    __syncthreads();
+    const bool lane_ok = lane < SW_GRP * SW_H;
+    const int g = lane_ok ? lane / SW_H : 0, h = lane_ok ? lane % SW_H : 0, gbase = lane_ok ? g * SW_H : lane;
+    const long long n_tri = (a.B + SW_GRP - 1) / SW_GRP;
+    const size_t slot_stride = (size_t)a.B * SW_REC;
+    double esum = 0.0;
+    for (long long tri = (long long)blockIdx.x * SW_WARPS + warp; tri < n_tri; tri += (long long)gridDim.x * SW_WARPS) {
+        const long long t = tri * SW_GRP + g;
+        const bool live = lane_ok && t < a.B;
+        const long long tt = live ? t : 0;
+        float y[SW_D], prev1[SW_D] = {0.f, 0.f}, prev2 = 0.f, k[SW_MAXS][SW_D], ys[SW_D];
+#pragma unroll
+        for (int d = 0; d < SW_D; ++d) y[d] = a.y[tt * SW_D + d];
+        if (FERRO && !a.state_is_zero) {
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) prev1[d] = a.state[tt * SF + d];
+            prev2 = a.state[tt * SF + SW_D + h];
+        }
+        float* ck = a.ckpt ? a.ckpt + tt * SW_REC : nullptr;
+        if (ck && live) {
+            if (h < SW_D) ck[h] = prev1[h];
+            ck[SW_D + h] = prev2;
+        }
+#pragma unroll
+        for (int s = 0; s < SW_MAXS; ++s) { k[s][0] = 0.f; k[s][1] = 0.f; }
+        if (a.first_eval) {
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) k[0][d] = a.k0[tt * SW_D + d];
+        }
+#pragma unroll
+        for (int s = 0; s < SW_MAXS; ++s) {
+            if (s < a.ns) {
+#pragma unroll
+                for (int d = 0; d < SW_D; ++d) {
+                    float acc = 0.f;
+#pragma unroll
+                    for (int r = 0; r < s; ++r) acc = fmaf(a.A[s][r], k[r][d], acc);
+                    ys[d] = fmaf(a.dt, acc, y[d]);
+                }
+                if (s >= a.first_eval) {
+                    float x2;
+                    sw_rhs<BR>(sm, L, gbase, h, lane_ok, ys, prev1, prev2, k[s], x2);
+                    if (ck && live) {
+                        float* c = ck + (size_t)(1 + s - a.first_eval) * slot_stride;
+                        if (h < SW_D) c[h] = ys[h];
+                        c[SW_D + h] = x2;
+                    }
+                }
+            }
+        }
+        if (live && h < SW_D) {
+#pragma unroll
+            for (int s = 0; s < SW_MAXS; ++s)
+                if (s < a.ns) a.ks[((size_t)s * a.B + tt) * SW_D + h] = k[s][h];
+            if (a.y1) a.y1[tt * SW_D + h] = a.y1_last ? ys[h] : y[h];
+            if (a.errsq) {
+                float e = 0.f;
+#pragma unroll
+                for (int s = 0; s < SW_MAXS; ++s)
+                    if (s < a.ns) e = fmaf(a.E[s], k[s][h], e);
+                e *= a.dt;
+                const float tol = fmaf(a.rtol, fmaxf(fabsf(y[h]), fabsf(ys[h])), a.atol);
+                const float q = e / tol;
+                esum += (double)q * (double)q;
+            }
+        }
+        if (live && FERRO && a.state) {
+            if (h < SW_D) a.state[tt * SF + h] = prev1[h];
+            a.state[tt * SF + SW_D + h] = prev2;
+        }
+    }
+    if (a.errsq) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) esum += __shfl_xor_sync(0xffffffffu, esum, o);
+        if (lane == 0 && esum != 0.0) atomicAdd(a.errsq, esum);
+    }
+}
+
+template <int BR>
+__global__ void __launch_bounds__(SW_THREADS) smallnet_wide_step_bwd_kernel(const SWStepArgs a) {
+    extern __shared__ float4 sw_smem4[];
+    float* sm = reinterpret_cast<float*>(sw_smem4);
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < L.total_ext / 4; i += SW_THREADS) sw_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    float* acc_all = sm + L.total_ext;
+    float* tile_all = acc_all + SW_WARPS * SW_NACC * 32;
+    for (int i = tid; i < SW_WARPS * SW_NACC * 32; i += SW_THREADS) acc_all[i] = 0.f;
+    __syncthreads();
+    float* acc = acc_all + warp * SW_NACC * 32 + lane;
+    float* tile = tile_all + warp * SW_D * 32 * SW_TSTRIDE;
+    const bool lane_ok = lane < SW_GRP * SW_H;
+    const int g = lane_ok ? lane / SW_H : 0, h = lane_ok ? lane % SW_H : 0, gbase = lane_ok ? g * SW_H : lane;
+    const long long n_tri = (a.B + SW_GRP - 1) / SW_GRP;
+    const size_t slot_stride = (size_t)a.B * SW_REC;
+    for (long long tri = (long long)blockIdx.x * SW_WARPS + warp; tri < n_tri; tri += (long long)gridDim.x * SW_WARPS) {
+        const long long t = tri * SW_GRP + g;
+        const bool live = lane_ok && t < a.B;
+        const long long tt = live ? t : 0;
+        const float* ck = a.ckpt + tt * SW_REC;
+        float gY[SW_MAXS][SW_D];                       // adjoint of every stage INPUT
+#pragma unroll
+        for (int s = 0; s < SW_MAXS; ++s) { gY[s][0] = 0.f; gY[s][1] = 0.f; }
+        float gy[SW_D] = {0.f, 0.f};
+#pragma unroll
+        for (int s = SW_MAXS - 1; s >= 0; --s) {
+            if (s < a.ns && s >= a.first_eval) {
+                float gk[SW_D], gin[SW_D], yin[SW_D], pin[SW_D];
+                const int slot = 1 + s - a.first_eval;
+                const float* c = ck + (size_t)slot * slot_stride;
+                const float* cp = ck + (size_t)(slot - 1) * slot_stride;      // what this stage saw as prev_x
+#pragma unroll
+                for (int d = 0; d < SW_D; ++d) {
+                    float v = a.g_ks ? a.g_ks[((size_t)s * a.B + tt) * SW_D + d] : 0.f;
+                    if (s == a.ns - 1 && a.x_klast) v += a.x_klast[tt * SW_D + d];
+#pragma unroll
+                    for (int q = s + 1; q < SW_MAXS; ++q)
+                        if (q < a.ns) v = fmaf(a.dt * a.A[q][s], gY[q][d], v);
+                    gk[d] = live ? v : 0.f;
+                    yin[d] = c[d];
+                    pin[d] = cp[d];
+                }
+                sw_rhs_bwd<BR>(sm, L, gbase, h, lane, lane_ok, yin, pin, FERRO ? cp[SW_D + h] : 0.f, c[SW_D + h], gk, gin,
+                               acc, tile);
+#pragma unroll
+                for (int d = 0; d < SW_D; ++d) {
+                    float top = 0.f;
+                    if (a.y1_last && s == a.ns - 1 && live) {
+                        if (a.g_y1) top += a.g_y1[tt * SW_D + d];
+                        if (a.x_y1) top += a.x_y1[tt * SW_D + d];
+                    }
+                    gY[s][d] = gin[d] + top;
+                    gy[d] += gY[s][d];
+                }
+            }
+        }
+        if (live && h < SW_D) {
+            float v = gy[h];
+            if (!a.y1_last && a.g_y1) v += a.g_y1[tt * SW_D + h];
+            if (!a.y1_last && a.x_y1) v += a.x_y1[tt * SW_D + h];
+            if (a.x_y) v += a.x_y[tt * SW_D + h];
+            a.g_y[tt * SW_D + h] = v;
+            if (a.first_eval && a.g_k0) {
+                float w = a.g_ks ? a.g_ks[tt * SW_D + h] : 0.f;
+                if (a.ns == 1 && a.x_klast) w += a.x_klast[tt * SW_D + h];
+#pragma unroll
+                for (int q = 1; q < SW_MAXS; ++q)
+                    if (q < a.ns) w = fmaf(a.dt * a.A[q][0], gY[q][h], w);
+                a.g_k0[tt * SW_D + h] = w;
+            }
+        }
+    }
+    __syncthreads();
+    const SNGfoldW gf = snw_gfold(SW_D, SW_H, SW_F, SW_NB);
+    for (int i = tid; i < SW_NACC * SW_H; i += SW_THREADS) {
+        const int c = i / SW_H, hh = i % SW_H;
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < SW_WARPS; ++w)
+#pragma unroll
+            for (int gg = 0; gg < SW_GRP; ++gg) v += acc_all[(w * SW_NACC + c) * 32 + gg * SW_H + hh];
+        if (v == 0.f) continue;
+        int dst = -1;
+        if (c < SW_C_BP2) { const int f = c / SW_D, o = c % SW_D; dst = gf.ws2 + (hh * SW_F + f) * SW_D + o; }
+        else if (c < SW_C_W1) { const int q = c - SW_C_BP2; dst = gf.bp2 + (q / SW_NB) * SW_H * SW_NB + hh * SW_NB + q % SW_NB; }
+        else if (c < SW_C_GS1) { const int q = c - SW_C_W1; dst = gf.ws1 + q * SW_H + hh; }
+        else if (c == SW_C_GS1) dst = gf.gsum1 + hh;
+        else if (c < SW_C_GS2) { const int q = c - SW_C_BP1; dst = gf.bp1 + (q / SW_D) * SW_D * SW_NB + (q % SW_D) * SW_NB + hh; }
+        else if (hh < SW_D) dst = gf.gsum2 + hh;
+        if (dst >= 0) atomicAdd(a.gfold + dst, v);
+    }
+}
+
 }  // namespace fetode
 
 using namespace fetode;
@@ -566,6 +780,87 @@ extern "C" int fetode_smallnet_wide_bwd(const fetode_smallnet_t* net, const floa
         k<<<grid, SW_THREADS, smem, st>>>(a);
     } else {
         auto k = smallnet_wide_bwd_kernel<FETODE_BRANCH_LOGISTIC>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}
+
+// ---- one Runge-Kutta attempt with a caller-supplied tableau (adaptive solvers) ---------------------------------------
+static int snw_attempt_args(const fetode_smallnet_t* net, const fetode_rk_attempt_t* rk, SWStepArgs& a) {
+    if (!snw_has(net)) return FETODE_EUNSUPPORTED;
+    if (!rk || rk->n_stages < 1 || rk->n_stages > SW_MAXS || rk->first_eval < 0 || rk->first_eval > 1 ||
+        rk->first_eval >= rk->n_stages)
+        return FETODE_EINVAL;
+    a.ns = rk->n_stages; a.first_eval = rk->first_eval; a.y1_last = rk->y1_is_last_input ? 1 : 0;
+    a.dt = rk->dt; a.rtol = rk->rtol; a.atol = rk->atol;
+    for (int i = 0; i < SW_MAXS; ++i) {
+        a.E[i] = rk->e[i];
+        for (int j = 0; j < SW_MAXS; ++j) a.A[i][j] = j < i ? rk->a[i][j] : 0.f;
+    }
+    return FETODE_OK;
+}
+
+extern "C" int64_t fetode_smallnet_attempt_ckpt_floats(const fetode_smallnet_t* net, const fetode_rk_attempt_t* rk,
+                                                       int64_t B) {
+    SWStepArgs a{};
+    if (snw_attempt_args(net, rk, a) != FETODE_OK || B < 0) return -1;
+    return (int64_t)(1 + a.ns - a.first_eval) * B * SW_REC;
+}
+
+extern "C" int fetode_smallnet_attempt_fwd(const fetode_smallnet_t* net, const float* packed,
+                                           const fetode_rk_attempt_t* rk, const float* y, const float* k0, float* y1,
+                                           float* ks, float* state, int state_is_zero, int64_t B, float* ckpt,
+                                           double* errsq, void* stream) {
+    SWStepArgs a{};
+    int rc = snw_attempt_args(net, rk, a);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(packed && y && ks && B >= 0 && (!a.first_eval || k0));
+    if (B == 0) return FETODE_OK;
+    if (net->branch == FETODE_BRANCH_FERRO2D && !state_is_zero) FETODE_CHECK_ARG(state != nullptr);
+    a.packed = packed; a.y = y; a.k0 = k0; a.y1 = y1; a.ks = ks; a.state = state; a.ckpt = ckpt; a.errsq = errsq;
+    a.B = B; a.state_is_zero = state_is_zero;
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    const size_t smem = (size_t)L.total * 4;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = snw_grid(B, 4);
+    if (net->branch == FETODE_BRANCH_FERRO2D) {
+        auto k = smallnet_wide_step_fwd_kernel<FETODE_BRANCH_FERRO2D>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    } else {
+        auto k = smallnet_wide_step_fwd_kernel<FETODE_BRANCH_LOGISTIC>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_smallnet_attempt_bwd(const fetode_smallnet_t* net, const float* packed,
+                                           const fetode_rk_attempt_t* rk, const float* ckpt, const float* g_y1,
+                                           const float* g_ks, const float* x_y1, const float* x_klast, const float* x_y,
+                                           float* g_y, float* g_k0, float* gfold, int64_t B, void* stream) {
+    SWStepArgs a{};
+    int rc = snw_attempt_args(net, rk, a);
+    if (rc) return rc;
+    FETODE_CHECK_ARG(packed && ckpt && g_y && gfold && B >= 0);
+    if (B == 0) return FETODE_OK;
+    a.packed = packed; a.ckpt = const_cast<float*>(ckpt); a.g_y1 = g_y1; a.g_ks = g_ks; a.x_y1 = x_y1;
+    a.x_klast = x_klast; a.x_y = x_y; a.g_y = g_y; a.g_k0 = g_k0; a.gfold = gfold; a.B = B;
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    const size_t smem = (size_t)(L.total_ext + SW_WARPS * SW_NACC * 32 + SW_WARPS * SW_D * 32 * SW_TSTRIDE) * 4;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = snw_grid(B, 3);
+    if (net->branch == FETODE_BRANCH_FERRO2D) {
+        auto k = smallnet_wide_step_bwd_kernel<FETODE_BRANCH_FERRO2D>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<grid, SW_THREADS, smem, st>>>(a);
+    } else {
+        auto k = smallnet_wide_step_bwd_kernel<FETODE_BRANCH_LOGISTIC>;
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e) return (int)e;
         k<<<grid, SW_THREADS, smem, st>>>(a);

@@ -82,7 +82,7 @@ def lib() -> C.CDLL:
         for name in ("fetode_kanlinear_wcat_floats", "fetode_kanlinear_bwd_ws_floats",
                      "fetode_smallnet_packed_floats", "fetode_smallnet_state_floats",
                      "fetode_smallnet_ckpt_floats", "fetode_smallnet_gfold_floats",
-                     "fetode_smallnet_wide_ckpt_floats"):
+                     "fetode_smallnet_wide_ckpt_floats", "fetode_smallnet_attempt_ckpt_floats"):
             if hasattr(_lib, name):
                 getattr(_lib, name).restype = C.c_int64
     return _lib
@@ -115,6 +115,13 @@ def f32c(t: torch.Tensor) -> torch.Tensor:
     if t.dtype != torch.float32:
         t = t.float()
     return t.contiguous()
+
+
+class RkAttempt(C.Structure):
+    """fetode_rk_attempt_t (include/fetode.h)."""
+    _fields_ = [("n_stages", C.c_int32), ("first_eval", C.c_int32), ("y1_is_last_input", C.c_int32), ("_pad", C.c_int32),
+                ("a", (C.c_float * 7) * 7), ("e", C.c_float * 7), ("dt", C.c_float), ("rtol", C.c_float),
+                ("atol", C.c_float)]
 
 
 class Conv2d(C.Structure):

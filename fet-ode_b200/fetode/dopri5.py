@@ -5,6 +5,10 @@ train_kan_fet_ett.py:702) is an unpinned third-party dependency absent from the 
 algorithm (SURVEY appendix B -- PARITY UNPINNED): FSAL tableau, Hairer initial step, one RMS error norm over the whole
 state tensor, controller safety 0.9 / ifactor 10 / dfactor 0.2, 4th-order dense output, time kept in float64 on the host.
 
+Two execution paths (both on the GPU): FUSED when ``func(t, y)`` is a bare call of a small KAN / KANFET the
+hidden-units-on-lanes kernels support (the Lotka-Volterra script's model: one launch per attempted step, one per accepted
+step in the reverse sweep -- see ``_FusedSolve`` below), STAGED for any other callable:
+
 The right-hand side is called once per stage, in the order torchdiffeq calls it (stateful neurons mutate their
 hysteresis snapshot on every call, including the initial-step probe and rejected attempts).  Stage sums, the error
 estimate, the error norm and the dense-output polynomial are libfetode kernels (csrc/rkstage.cu): one launch per
@@ -58,6 +62,9 @@ def dopri5_integrate(func, y0, t, times: List[float], rtol, atol, options) -> to
     rtol, atol = float(rtol), float(atol)
     if times[-1] < times[0]:
         raise NotImplementedError("fetode.odeint(dopri5): decreasing t is not used by the reference")
+    model = fused_model(func, y0)
+    if model is not None:
+        return fused_dopri5(model, y0, times, rtol, atol, options)
     tt = _time_tensor_factory(t, y0.device)
     sync = options.get("norm_sync")                      # callable(tensor[2]) that sums across ranks, or None
     max_steps = int(options.get("max_num_steps", 2 ** 31 - 1))
@@ -121,18 +128,16 @@ def dopri5_integrate(func, y0, t, times: List[float], rtol, atol, options) -> to
     return torch.stack(sol, 0)
 
 
-def _dense_eval(dense, ta, tb, tq, combine):
-    """4th-order interpolant through (ya, fa), y_mid, (yb, fb) evaluated at tq in [ta, tb]: every monomial
-    coefficient is a linear combination of ya, yb and the stage slopes, so the whole evaluation is ONE
-    fetode_rk_combine launch."""
-    ya, yb, ks, h = dense
+def _dense_weights(ta, tb, tq, h):
+    """4th-order interpolant through (ya, fa), y_mid, (yb, fb) at tq in [ta, tb] as weights of a linear combination:
+    p = w_ya ya + w_yb yb + sum_s w_k[s] k_s.
+    y_mid = ya + h sum cm_i k_i ;  a = 2h(fb-fa) - 8(yb+ya) + 16 ymid ; b = h(5fa-3fb) + 18ya + 14yb - 32ymid ;
+    c = h(fb-4fa) - 11ya - 5yb + 16ymid ;  p(x) = ya + x h fa + x^2 c + x^3 b + x^4 a"""
     if tq == tb:
-        return yb
+        return 0.0, 1.0, [0.0] * 7
     if tq == ta:
-        return ya
+        return 1.0, 0.0, [0.0] * 7
     x = (tq - ta) / (tb - ta)
-    # y_mid = ya + h sum cm_i k_i ;  a = 2h(fb-fa) - 8(yb+ya) + 16 ymid ; b = h(5fa-3fb) + 18ya + 14yb - 32ymid ;
-    # c = h(fb-4fa) - 11ya - 5yb + 16ymid ;  p(x) = ya + x h fa + x^2 c + x^3 b + x^4 a
     x2, x3, x4 = x * x, x ** 3, x ** 4
     w_mid = 16 * x2 - 32 * x3 + 16 * x4
     w_ya = 1.0 - 11 * x2 + 18 * x3 - 8 * x4 + w_mid
@@ -140,9 +145,250 @@ def _dense_eval(dense, ta, tb, tq, combine):
     w_k = [w_mid * h * c for c in _C_MID]
     w_k[0] += h * (x - 4 * x2 + 5 * x3 - 2 * x4)
     w_k[6] += h * (x2 - 3 * x3 + 2 * x4)
+    return w_ya, w_yb, w_k
+
+
+def _dense_eval(dense, ta, tb, tq, combine):
+    """Every monomial coefficient of the interpolant is a linear combination of ya, yb and the stage slopes, so the
+    whole evaluation is ONE fetode_rk_combine launch (two when more than 8 terms are non-zero)."""
+    ya, yb, ks, h = dense
+    if tq == tb:
+        return yb
+    if tq == ta:
+        return ya
+    w_ya, w_yb, w_k = _dense_weights(ta, tb, tq, h)
     terms = [(ya, w_ya - 1.0), (yb, w_yb)] + [(k, w) for k, w in zip(ks, w_k) if w != 0.0]
     # fetode_rk_combine takes <= 8 terms per launch
     out = combine(ya, [v for v, _ in terms[:8]], [w for _, w in terms[:8]])
     if len(terms) > 8:
         out = combine(out, [v for v, _ in terms[8:]], [w for _, w in terms[8:]])
     return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# fused path: func(t, y) == model(y) for a small KAN / KANFET the hidden-units-on-lanes kernels support
+# ------------------------------------------------------------------------------------------------------------------
+# One launch per ATTEMPTED step (six right-hand sides, stage sums, solution, error norm: fetode_smallnet_attempt_fwd)
+# and one 8-byte read-back for the accept / reject decision; the reverse sweep is one launch per ACCEPTED step
+# (fetode_smallnet_attempt_bwd) walking the step checkpoints backwards.  Same controller, same call order of the
+# right-hand side (initial value, initial-step probe, six per attempt -- hysteresis state advances on rejected
+# attempts too) as the staged path above.
+def _rk_struct(n_stages, first_eval, y1_last, dt, rtol=0.0, atol=0.0, rows=(), err=()):
+    from ._lib import RkAttempt
+    rk = RkAttempt()
+    rk.n_stages, rk.first_eval, rk.y1_is_last_input = n_stages, first_eval, 1 if y1_last else 0
+    rk.dt, rk.rtol, rk.atol = float(dt), float(rtol), float(atol)
+    for i, row in enumerate(rows):
+        for j, v in enumerate(row):
+            rk.a[i + 1][j] = float(v)
+    for i, v in enumerate(err):
+        rk.e[i] = float(v)
+    return rk
+
+
+def fused_model(func, y0):
+    """The KAN / KANFET module if ``func(t, y) == model(y)`` and the attempt kernels support its shape, else None."""
+    import os
+    if y0.dim() != 2 or os.environ.get("FETODE_DOPRI5_FUSED", "1") == "0":
+        return None
+    from .odeint import recognise_kan_rhs
+    model = recognise_kan_rhs(func, y0)
+    if model is None:
+        return None
+    plan = model.small_plan()
+    if plan is None or lib().fetode_smallnet_wide_supported(C.byref(plan.net)) != 0:
+        return None
+    return model
+
+
+class _FusedSolve:
+    """Forward pass of the fused adaptive solve; ``keep`` retains what the reverse sweep needs."""
+
+    def __init__(self, model, y0c, times, rtol, atol, options, keep):
+        self.model, self.plan = model, model.small_plan()
+        self.keep = keep
+        self.B, self.D = y0c.shape
+        self.dev = y0c.device
+        self.img = self.plan.image()
+        self.rtol, self.atol = rtol, atol
+        self.steps = []                 # accepted: (dt, ckpt)
+        self.rk = _rk_struct(7, 1, True, 0.0, rtol, atol, rows=_BETA, err=_C_ERR)   # one struct, dt set per attempt
+        self.outs = []                  # (output index, accepted-step index, w_ya, w_yb, w_k[7])
+        self.rhs0 = None                # (rk struct, ckpt) of f(t0, y0)
+        self._acc = None
+        self._slot = 0
+        self._ck_floats = {}
+        st, fresh = None, True
+        if model._is_ferro():
+            st = model.hysteresis_state(self.B, self.dev)
+            fresh = st is None
+            st = (torch.empty(self.B, self.plan.state_floats, dtype=torch.float32, device=self.dev) if fresh
+                  else st.clone())
+        self.st, self.fresh = st, fresh
+        self.out = self._run(y0c, times, options)
+        if st is not None:
+            model.adopt_state(st)
+
+    # -- one launch
+    def _attempt(self, rk, y, k0, want_y1, want_err, want_ckpt):
+        L = lib()
+        B, D = self.B, self.D
+        ks = torch.empty(rk.n_stages, B, D, dtype=torch.float32, device=self.dev)
+        y1 = torch.empty(B, D, dtype=torch.float32, device=self.dev) if want_y1 else None
+        ck = None
+        if want_ckpt:
+            key = (rk.n_stages, rk.first_eval)
+            n = self._ck_floats.get(key)
+            if n is None:
+                n = self._ck_floats[key] = int(L.fetode_smallnet_attempt_ckpt_floats(C.byref(self.plan.net), C.byref(rk),
+                                                                                      C.c_int64(B)))
+            ck = torch.empty(max(n, 1), dtype=torch.float32, device=self.dev)
+        err_ptr = C.c_void_p(0)
+        if want_err:
+            if self._acc is None or self._slot >= self._acc.numel():
+                self._acc = torch.zeros(512, dtype=torch.float64, device=self.dev)
+                self._slot = 0
+            err_ptr = C.c_void_p(self._acc.data_ptr() + 8 * self._slot)
+        check(L.fetode_smallnet_attempt_fwd(C.byref(self.plan.net), ptr(self.img), C.byref(rk), ptr(y), ptr(k0), ptr(y1),
+                                            ptr(ks), ptr(self.st), C.c_int(1 if self.fresh else 0), C.c_int64(B),
+                                            ptr(ck), err_ptr, stream()), "smallnet_attempt_fwd")
+        self.fresh = False
+        err = None
+        if want_err:
+            err = self._acc[self._slot]
+            self._slot += 1
+        return y1, ks, ck, err
+
+    def _run(self, y, times, options):
+        from .odeint import combine
+        rtol, atol = self.rtol, self.atol
+        sync = options.get("norm_sync")
+        max_steps = int(options.get("max_num_steps", 2 ** 31 - 1))
+        stats = options.get("stats")
+        n_el = float(self.B * self.D)
+
+        def ratio_of(err):
+            if sync is not None:
+                pair = torch.stack([err, torch.tensor(n_el, dtype=torch.float64, device=self.dev)])
+                sync(pair)
+                s, n = pair.tolist()
+                return (s / max(n, 1.0)) ** 0.5
+            return (float(err.item()) / max(n_el, 1.0)) ** 0.5
+
+        rk0 = _rk_struct(1, 0, False, 0.0)
+        _, ks0, ck0, _ = self._attempt(rk0, y, None, False, False, self.keep)
+        f0 = ks0[0]
+        self.rhs0 = (rk0, ck0)
+        first = options.get("first_step")
+        if first is not None:
+            dt = float(first)
+        else:
+            d0 = _sumsq(y, y, y, atol, rtol, sync) ** 0.5
+            d1 = _sumsq(f0, y, y, atol, rtol, sync) ** 0.5
+            h0 = 1e-6 if (d0 < 1e-5 or d1 < 1e-5) else 0.01 * d0 / d1
+            _, ksp, _, _ = self._attempt(_rk_struct(2, 1, False, h0, rows=((1.0,),)), y, f0, False, False, False)
+            d2 = _sumsq(combine(None, [ksp[1], f0], [1.0, -1.0]), y, y, atol, rtol, sync) ** 0.5 / h0
+            h1 = max(1e-6, h0 * 1e-3) if (d1 <= 1e-15 and d2 <= 1e-15) else (0.01 / max(d1, d2)) ** 0.2
+            dt = min(100.0 * h0, h1)
+
+        sol = [y]
+        fy, ta, tb = f0, times[0], times[0]
+        dense = None
+        n_acc = n_rej = 0
+        for oi, tq in enumerate(times[1:], start=1):
+            while tq > tb:
+                t_new = tb + dt
+                if not (math.isfinite(dt) and t_new > tb):
+                    raise AssertionError(f"fetode.odeint(dopri5): underflow in dt {dt}")
+                self.rk.dt = dt
+                y1, ks, ck, err = self._attempt(self.rk, y, fy, True, True, self.keep)
+                ratio = ratio_of(err)
+                if not math.isfinite(ratio):
+                    raise AssertionError("fetode.odeint(dopri5): non-finite values in the state / error estimate")
+                if ratio <= 1.0:
+                    dense = (y, y1, ks, dt)
+                    ta, tb, y, fy = tb, t_new, y1, ks[6]
+                    n_acc += 1
+                    if self.keep:
+                        self.steps.append((dt, ck))
+                else:
+                    n_rej += 1
+                if ratio == 0.0:
+                    dt = dt * 10.0
+                else:
+                    dfac = 1.0 if ratio < 1.0 else 0.2
+                    dt = dt * min(10.0, max(0.9 / ratio ** 0.2, dfac))
+                if n_acc + n_rej > max_steps:
+                    raise RuntimeError("fetode.odeint(dopri5): max_num_steps exceeded")
+            if dense is None:
+                sol.append(y)
+                continue
+            sol.append(_dense_eval((dense[0], dense[1], list(dense[2]), dense[3]), ta, tb, tq, combine))
+            if self.keep:
+                self.outs.append((oi, n_acc - 1) + _dense_weights(ta, tb, tq, dense[3]))
+        if stats is not None:
+            stats.update(accepted=n_acc, rejected=n_rej, fused=True)
+        return torch.stack(sol, 0)
+
+
+class FusedDopri5Fn(torch.autograd.Function):
+    """[T, B, D] dopri5 solution with autograd edges to y0 and the model's parameters.  The reverse sweep differentiates
+    the accepted steps and the dense-output combinations; step sizes are constants (discretise-then-optimise, what
+    torchdiffeq's plain ``odeint`` backward does through its recorded operations)."""
+
+    @staticmethod
+    def forward(ctx, model, times, rtol, atol, options, y0, *params):
+        solve = _FusedSolve(model, ops.f32c(y0.detach()), times, rtol, atol, options, keep=True)
+        ctx.solve = solve
+        return solve.out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        from .training import unfold_param_grads
+        sv = ctx.solve
+        plan, L = sv.plan, lib()
+        B, D, dev = sv.B, sv.D, sv.dev
+        g_out = ops.f32c(g_out)
+        gfold = torch.zeros(int(L.fetode_smallnet_gfold_floats(C.byref(plan.net))), dtype=torch.float32, device=dev)
+        # adjoints of (ya, yb, k_0..k_6) of every step that produced outputs, from the dense-output weights
+        G = {}
+        if sv.outs:
+            W = torch.tensor([[w_ya, w_yb] + list(w_k) for (_, _, w_ya, w_yb, w_k) in sv.outs],
+                             dtype=torch.float32).to(dev)
+            for j, (oi, n, *_w) in enumerate(sv.outs):
+                term = W[j].view(9, 1, 1) * g_out[oi].unsqueeze(0)
+                if n in G:
+                    G[n] += term
+                else:
+                    G[n] = term.contiguous()
+        net, img = C.byref(plan.net), ptr(sv.img)
+
+        def sweep(rk, ck, g_y1, g_ks, x_y1, x_klast, x_y, want_k0):
+            g_y = torch.empty(B, D, dtype=torch.float32, device=dev)
+            g_k0 = torch.empty(B, D, dtype=torch.float32, device=dev) if want_k0 else None
+            check(L.fetode_smallnet_attempt_bwd(net, img, C.byref(rk), ptr(ck), ptr(g_y1), ptr(g_ks), ptr(x_y1),
+                                                ptr(x_klast), ptr(x_y), ptr(g_y), ptr(g_k0), ptr(gfold), C.c_int64(B),
+                                                stream()), "smallnet_attempt_bwd")
+            return g_y, g_k0
+
+        carry_y = carry_k = None
+        for n in range(len(sv.steps) - 1, -1, -1):
+            dt, ck = sv.steps[n]
+            rk = sv.rk
+            rk.dt = dt
+            Gn = G.get(n)
+            carry_y, carry_k = sweep(rk, ck, None if Gn is None else Gn[1], None if Gn is None else Gn[2:9], carry_y,
+                                     carry_k, None if Gn is None else Gn[0], True)
+        rk0, ck0 = sv.rhs0
+        gy0, _ = sweep(rk0, ck0, None, None, None, carry_k, carry_y, False)
+        gy0 = gy0 + g_out[0]
+        outs = unfold_param_grads(plan, gfold, ctx.needs_input_grad, 6)
+        return (None, None, None, None, None, gy0 if ctx.needs_input_grad[5] else None, *outs)
+
+
+def fused_dopri5(model, y0, times, rtol, atol, options) -> torch.Tensor:
+    plan = model.small_plan()
+    params = [t for v in plan.views for n, t in v.tensors() if t is not None and n != "grid"]
+    if torch.is_grad_enabled() and (y0.requires_grad or any(p.requires_grad for p in params)):
+        return FusedDopri5Fn.apply(model, times, float(rtol), float(atol), options, y0, *params)
+    return _FusedSolve(model, ops.f32c(y0.detach()), times, float(rtol), float(atol), options, keep=False).out

@@ -54,6 +54,34 @@ def _wide_ok(plan, B: int) -> bool:
 _WIDE_ENV = None
 
 
+def unfold_param_grads(plan, gfold: torch.Tensor, needs_input_grad, first: int) -> list:
+    """Chain rule from the folded gradient buffer of the small-net reverse sweeps to the reference's parameters
+    (fetode_smallnet_unfold); returns one tensor (or None) per ``fused_params`` entry, ``needs_input_grad[first:]``
+    saying which are wanted."""
+    L = lib()
+    dev = gfold.device
+    views = plan.views
+    structs = (KanLayer * 2)(*[v.struct() for v in views])
+    grads = (KanLayerGrads * 2)()
+    outs = []
+    k = first
+    for li, v in enumerate(views):
+        for name, t in v.tensors():
+            if t is None or name == "grid":
+                continue
+            gt = torch.zeros(t.shape, dtype=torch.float32, device=dev) if needs_input_grad[k] else None
+            k += 1
+            outs.append(gt)
+            if name.startswith("bp"):
+                grads[li].bp[int(name[2:])] = ptr(gt).value
+            else:
+                setattr(grads[li], name, ptr(gt).value)
+    check(L.fetode_smallnet_unfold(C.byref(plan.net), structs, ptr(gfold), grads, stream()), "smallnet_unfold")
+    # no host synchronisation: any f32c() temporary behind `structs` was allocated on this stream, and the caching
+    # allocator only hands its block to work queued later on the same stream (this also keeps the step capturable)
+    return outs
+
+
 class FusedRKFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, model, times, kind, uniform_dt, y0, *params):
@@ -118,26 +146,7 @@ class FusedRKFn(torch.autograd.Function):
                   "smallnet_wide_bwd" if ctx.wide else "smallnet_rk_bwd")
             carry = g_y0
         gy0 = g_out[0] if carry is None else carry + g_out[0]
-        # chain rule folded -> reference parameters
-        views = plan.views
-        structs = (KanLayer * 2)(*[v.struct() for v in views])
-        grads = (KanLayerGrads * 2)()
-        outs = []
-        k = 5
-        for li, v in enumerate(views):
-            for name, t in v.tensors():
-                if t is None or name == "grid":
-                    continue
-                gt = torch.zeros(t.shape, dtype=torch.float32, device=dev) if ctx.needs_input_grad[k] else None
-                k += 1
-                outs.append(gt)
-                if name.startswith("bp"):
-                    grads[li].bp[int(name[2:])] = ptr(gt).value
-                else:
-                    setattr(grads[li], name, ptr(gt).value)
-        check(L.fetode_smallnet_unfold(C.byref(plan.net), structs, ptr(gfold), grads, stream()), "smallnet_unfold")
-        # no host synchronisation: any f32c() temporary behind `structs` was allocated on this stream, and the caching
-        # allocator only hands its block to work queued later on the same stream (this also keeps the step capturable)
+        outs = unfold_param_grads(plan, gfold, ctx.needs_input_grad, 5)
         return (None, None, None, None, gy0 if ctx.needs_input_grad[4] else None, *outs)
 
 

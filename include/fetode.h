@@ -218,6 +218,38 @@ FETODE_API int fetode_smallnet_wide_fwd(const fetode_smallnet_t* net, const floa
 FETODE_API int fetode_smallnet_wide_bwd(const fetode_smallnet_t* net, const float* packed, int tableau, const float* ckpt,
                          const float* g_yout, const float* g_traj, int32_t dump_every, float* g_y0, float* gfold,
                          int64_t B, double dt, int32_t n_steps, void* stream);
+/* ONE attempted step of an explicit Runge-Kutta method with a caller-supplied tableau, as one launch: the building block
+ * of the adaptive solver.  Replaces, for the recognised small KAN / KANFET right-hand side, what torchdiffeq's
+ * _runge_kutta_step + _compute_error_ratio do per attempt at train_kanfet_node_predprey.py:252 (dopri5 is that script's
+ * default method): six right-hand sides, the stage sums, the 5th-order solution and the error norm.
+ *   k_0 is given (first_eval = 1: FSAL) or evaluated (first_eval = 0);
+ *   stage s input  ys_s = y + dt sum_{r<s} a[s][r] k_r,  k_s = f(ys_s)  for first_eval <= s < n_stages (<= 7);
+ *   y1 = ys_{n_stages-1} when y1_is_last_input (dopri5: the last row of the tableau is the solution), else y;
+ *   ks [n_stages, B, D] receives every k_s (k_0 copied when given);  y1 [B, D] or NULL;
+ *   *errsq += sum_{rows, d} ( dt sum_s e[s] k_s / (atol + rtol max(|y|, |y1|)) )^2   (caller zeroes; NULL: skipped);
+ *   state advances with EVERY evaluated stage, also on attempts the controller then rejects (the reference's stateful
+ *   modules do the same);  ckpt: fetode_smallnet_attempt_ckpt_floats floats or NULL.
+ * _attempt_bwd is the adjoint of one ACCEPTED attempt: g_y1 [B,D] / g_ks [n_stages,B,D] (either may be NULL) are the
+ * adjoints of the outputs; x_y1, x_klast, x_y are optional [B,D] addends to g_y1, g_ks[n_stages-1] and the returned
+ * g_y (the carries of the next step, so that the host adds nothing between launches); g_y [B,D], g_k0 [B,D] (when
+ * first_eval) are written, parameter adjoints are ADDED to gfold (fetode_smallnet_gfold_floats, fetode_smallnet_unfold).
+ * Step sizes are constants of the differentiation, as in torchdiffeq's discretise-then-optimise backward.
+ * Same shape support as fetode_smallnet_wide_*. */
+typedef struct fetode_rk_attempt {
+    int32_t n_stages, first_eval, y1_is_last_input, _pad;
+    float a[7][7];
+    float e[7];
+    float dt, rtol, atol;
+} fetode_rk_attempt_t;
+FETODE_API int64_t fetode_smallnet_attempt_ckpt_floats(const fetode_smallnet_t* net, const fetode_rk_attempt_t* rk,
+                                                       int64_t B);
+FETODE_API int fetode_smallnet_attempt_fwd(const fetode_smallnet_t* net, const float* packed,
+                         const fetode_rk_attempt_t* rk, const float* y, const float* k0, float* y1, float* ks,
+                         float* state, int state_is_zero, int64_t B, float* ckpt, double* errsq, void* stream);
+FETODE_API int fetode_smallnet_attempt_bwd(const fetode_smallnet_t* net, const float* packed,
+                         const fetode_rk_attempt_t* rk, const float* ckpt, const float* g_y1, const float* g_ks,
+                         const float* x_y1, const float* x_klast, const float* x_y, float* g_y, float* g_k0,
+                         float* gfold, int64_t B, void* stream);
 FETODE_API int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
                         float* dy, float* state, int state_is_zero, int64_t B, void* stream);
 
