@@ -343,6 +343,44 @@ def lv_train_section(ctx, B, fp32_peak, with_cpu):
     return out
 
 
+def lv_dopri5_section(ctx, B, rtol=1e-5, atol=1e-7):
+    """Config 1 with the script's own solver call -- ``odeint(calDeriv, X0, t)`` = torchdiffeq's default dopri5
+    (train_kanfet_node_predprey.py:252): one launch per attempted step, one per accepted step on the way back, one
+    8-byte read-back per attempt (so: eager, not graph-replayed).  Tolerances 1e-5 / 1e-7, not torchdiffeq's default
+    1e-7 / 1e-9: the spline right-hand side is C2 only and the hysteretic gate sees the previous STAGE input, so the
+    embedded error estimate is low-order and the default tolerances mean ~850 000 steps per solve in fp32 on any
+    implementation (profiles/experiments/dopri5_time.py)."""
+    import fetode
+    model = make_model().to(ctx.dev)
+    n, T = 34, 3.5
+    t = torch.linspace(0, T, n + 1, dtype=torch.float64)
+    gen = torch.Generator().manual_seed(100 + ctx.rank)
+    x0 = (torch.rand(B, 2, generator=gen) * 6.75 + 0.25) if B > 1 else torch.ones(1, 2)
+    x0d = x0.to(ctx.dev)
+    tgt = torch.randn(n + 1, B, 2, generator=gen).to(ctx.dev)
+    func = fetode.as_rhs(model)
+    opt = fetode.optim.Adam(model.parameters(), lr=2e-3)
+    st = {}
+
+    def it():
+        opt.zero_grad()
+        model.reset_state()
+        pred = fetode.odeint(func, x0d, t, rtol=rtol, atol=atol, options={"stats": st})
+        ((pred - tgt) ** 2).mean().backward()
+        opt.step()
+    k = 3
+    ms = ctx.timed(it, k, 1, flush=False, grad=True) / k
+    att = st.get("accepted", 0) + st.get("rejected", 0)
+    return {"workload": "config 1 with the script's solver call: LV KANFET([2,10,2]) NODE training iteration, adaptive dopri5 "
+                        f"(rtol {rtol:g}, atol {atol:g}), t in [0, {T}] x {n + 1} samples, MSE, fused Adam "
+                        "(train_kanfet_node_predprey.py:246-257)",
+            "rows_per_gpu": B, "ms_per_step": ms, "graph_replayed": False, "fused_attempt_kernels": bool(st.get("fused")),
+            "accepted_steps": st.get("accepted"), "rejected_steps": st.get("rejected"),
+            "us_per_attempt_fwd_bwd": ms * 1e3 / att if att else None,
+            "staged_path_ms_per_step": {"value": 19913.5, "source": "profiles/r2_dopri5_fused_vs_staged.jsonl (same model, B = 1)"}
+            if B == 1 else None}
+
+
 def ecg_train_section(ctx, B, tf32_peak, with_cpu):
     """Config 3: KanFet_MLP_NODE(T=96, latent 64, nb 12, hidden 128) training step (train_ecg_kan_fet_nn_ode.py:1100-1112),
     classic RK4 x 8, cross-entropy, clip_grad_norm_(1.0), AdamW; B rows per GPU.  At N > 1 every rank but the last
@@ -550,6 +588,7 @@ def run_ours(args):
         fwd_bwd = {}
         for name, fn, a in (("lv_train_B1", lv_train_section, (1, fp32_peak, with_cpu)),
                             ("lv_train_B65536", lv_train_section, (65536, fp32_peak, with_cpu)),
+                            ("lv_train_dopri5_B1", lv_dopri5_section, (1,)),
                             ("ecg_train_B4096", ecg_train_section, (4096, tf32_peak, with_cpu)),
                             ("ett_encoder_B4096", ett_encoder_section, (4096, tf32_peak)),
                             ("mnist_train_B1024", mnist_train_section, (1024, fp32_peak))):
