@@ -345,8 +345,9 @@ def lv_train_section(ctx, B, fp32_peak, with_cpu):
 
 def lv_dopri5_section(ctx, B, rtol=1e-5, atol=1e-7):
     """Config 1 with the script's own solver call -- ``odeint(calDeriv, X0, t)`` = torchdiffeq's default dopri5
-    (train_kanfet_node_predprey.py:252): one launch per attempted step, one per accepted step on the way back, one
-    8-byte read-back per attempt (so: eager, not graph-replayed).  Tolerances 1e-5 / 1e-7, not torchdiffeq's default
+    (train_kanfet_node_predprey.py:252).  B <= 12: the accept / reject controller runs inside the kernel
+    (fetode_smallnet_dp5_solve_fwd / _bwd), one launch per 4096 accepted steps; larger batches: one launch per attempted
+    step and one 8-byte read-back (eager either way, not graph-replayed).  Tolerances 1e-5 / 1e-7, not torchdiffeq's default
     1e-7 / 1e-9: the spline right-hand side is C2 only and the hysteretic gate sees the previous STAGE input, so the
     embedded error estimate is low-order and the default tolerances mean ~850 000 steps per solve in fp32 on any
     implementation (profiles/experiments/dopri5_time.py)."""
@@ -375,9 +376,11 @@ def lv_dopri5_section(ctx, B, rtol=1e-5, atol=1e-7):
                         f"(rtol {rtol:g}, atol {atol:g}), t in [0, {T}] x {n + 1} samples, MSE, fused Adam "
                         "(train_kanfet_node_predprey.py:246-257)",
             "rows_per_gpu": B, "ms_per_step": ms, "graph_replayed": False, "fused_attempt_kernels": bool(st.get("fused")),
+            "controller_on_device": bool(st.get("device_controller")),
             "accepted_steps": st.get("accepted"), "rejected_steps": st.get("rejected"),
             "us_per_attempt_fwd_bwd": ms * 1e3 / att if att else None,
-            "staged_path_ms_per_step": {"value": 19913.5, "source": "profiles/r2_dopri5_fused_vs_staged.jsonl (same model, B = 1)"}
+            "other_paths_ms_per_step": {"host_controlled_attempt_launches": 657.4, "staged_per_stage_launches": 19913.5,
+                                        "source": "profiles/r2_dopri5_fused_vs_staged.jsonl (same model, B = 1)"}
             if B == 1 else None}
 
 

@@ -61,16 +61,18 @@ struct SWArgs {
     int nst, n_steps, dump_every, state_is_zero;
 };
 
-// sum over the ten lanes of a group (rotations by 1, 2, 4 and the two leftovers); every lane of the group gets the total
+// sum over the ten lanes of a group in four shuffles; every lane of the group gets the total, BIT-IDENTICALLY: the tree
+// ((0+1)+(2+3)) + ((4+5)+(6+7)) and (8+9) is built from exchanges between partners (a + b == b + a), so the ten replicas
+// of a trajectory never drift apart and a solve resumed from saved state reproduces an uninterrupted one exactly
 __device__ __forceinline__ float grp_sum(float v, int gbase, int h, bool lane_ok) {
-    auto rot = [&](float x, int k) {
-        const int src = lane_ok ? gbase + (h + k >= SW_H ? h + k - SW_H : h + k) : (gbase + h);
-        return __shfl_sync(0xffffffffu, x, src);
-    };
-    const float s1 = v + rot(v, 1);          // 2 consecutive
-    const float s2 = s1 + rot(s1, 2);        // 4
-    const float s4 = s2 + rot(s2, 4);        // 8
-    return s4 + rot(s1, 8);                  // + elements 8, 9
+    const bool low = h < 8;
+    auto from = [&](float x, int hh) { return __shfl_sync(0xffffffffu, x, lane_ok ? gbase + hh : gbase + h); };
+    const float s1 = v + from(v, h ^ 1);
+    const float t2 = from(s1, low ? (h ^ 2) : h);
+    const float s2 = low ? s1 + t2 : s1;
+    const float t4 = from(s2, low ? (h ^ 4) : h);
+    const float s4 = low ? s2 + t4 : s2;
+    return s4 + from(s4, low ? 8 : 0);
 }
 
 // per-lane layer-1 work of one input d: silu, 1 - moving_up, and the branch factor r of basis j = h
@@ -661,6 +663,281 @@ __global__ void __launch_bounds__(SW_THREADS) smallnet_wide_step_bwd_kernel(cons
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// the whole adaptive solve on the device (small batches: one CTA holds every trajectory)
+// ------------------------------------------------------------------------------------------
+// For B <= SW_GRP * SW_WARPS trajectories -- the reference's Lotka-Volterra run is ONE -- the dopri5 controller itself
+// runs in the kernel: attempt, error norm (block reduction), accept / reject, step-size update (double precision, the
+// host controller's formulas), dense output at every requested time the accepted step covers.  The host launches it
+// once per `cap` accepted steps (checkpoint chunk) and reads eight doubles back per launch instead of one per attempt.
+//   ctrl[0] tb  [1] ta  [2] dt  [3] next output index  [4] accepted  [5] rejected  [6] status  [7] accepted in this chunk
+//   status: 0 done, 1 launch again (chunk full / attempt budget spent), 2 dt underflow, 3 non-finite error ratio.
+constexpr int SW_SOLVE_MAXB = SW_GRP * SW_WARPS;
+
+struct SWSolveArgs {
+    const float* packed;
+    float *y, *fy;             // [B, D] in/out: solution and FSAL slope at tb
+    float* state;              // [B, D + H] in/out or null
+    float* out;                // [T, B, D]; rows 1.. written here
+    const double* times;       // [T]
+    double* ctrl;              // [8]
+    float* ckpt;               // [cap][7][B][SW_REC] or null (no reverse sweep wanted)
+    float* dts;                // [cap]
+    int* rec_step;             // [T]  absolute index of the accepted step that produced output oi
+    float* rec_w;              // [T][9] weights of (ya, yb, k_0..k_6)
+    double cmid[SW_MAXS];
+    float A[SW_MAXS][SW_MAXS], E[SW_MAXS];
+    float rtol, atol;
+    int B, T, cap, max_attempts, state_is_zero;
+    // reverse sweep
+    const float* g_out;        // [T, B, D]
+    float *carry_y, *carry_k;  // [B, D] in/out
+    float* gfold;
+    int n_steps, step_base;    // chunk length, absolute index of its first step
+    int* cursor;               // in/out: highest output index whose adjoint has not been consumed yet
+};
+
+__device__ __forceinline__ void sw_dense_weights(const double (&cmid)[SW_MAXS], double ta, double tb, double tq, double h,
+                                                 float (&w)[9]) {
+    if (tq == tb) {
+#pragma unroll
+        for (int i = 0; i < 9; ++i) w[i] = i == 1 ? 1.f : 0.f;
+        return;
+    }
+    const double x = (tq - ta) / (tb - ta), x2 = x * x, x3 = x2 * x, x4 = x2 * x2;
+    const double w_mid = 16 * x2 - 32 * x3 + 16 * x4;
+    w[0] = (float)(1.0 - 11 * x2 + 18 * x3 - 8 * x4 + w_mid);
+    w[1] = (float)(-5 * x2 + 14 * x3 - 8 * x4);
+#pragma unroll
+    for (int s = 0; s < SW_MAXS; ++s) {
+        double v = w_mid * h * cmid[s];
+        if (s == 0) v += h * (x - 4 * x2 + 5 * x3 - 2 * x4);
+        if (s == 6) v += h * (x2 - 3 * x3 + 2 * x4);
+        w[2 + s] = (float)v;
+    }
+}
+
+template <int BR>
+__global__ void __launch_bounds__(SW_THREADS) smallnet_wide_solve_fwd_kernel(const SWSolveArgs a) {
+    extern __shared__ float4 sw_smem4[];
+    float* sm = reinterpret_cast<float*>(sw_smem4);
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    constexpr int SF = FERRO ? SW_D + SW_H : 0;
+    __shared__ double red[SW_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < L.total / 4; i += SW_THREADS) sw_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    __syncthreads();
+    const bool lane_ok = lane < SW_GRP * SW_H;
+    const int g = lane_ok ? lane / SW_H : 0, h = lane_ok ? lane % SW_H : 0, gbase = lane_ok ? g * SW_H : lane;
+    const int t = warp * SW_GRP + g;
+    const bool live = lane_ok && t < a.B;
+    const int tt = live ? t : 0;
+    const size_t slot_stride = (size_t)a.B * SW_REC;
+    float y[SW_D], prev1[SW_D] = {0.f, 0.f}, prev2 = 0.f, k[SW_MAXS][SW_D], ys[SW_D];
+#pragma unroll
+    for (int d = 0; d < SW_D; ++d) { y[d] = a.y[tt * SW_D + d]; k[0][d] = a.fy[tt * SW_D + d]; }
+    if (FERRO && !a.state_is_zero) {
+#pragma unroll
+        for (int d = 0; d < SW_D; ++d) prev1[d] = a.state[tt * SF + d];
+        prev2 = a.state[tt * SF + SW_D + h];
+    }
+    double tb = a.ctrl[0], ta = a.ctrl[1], dt = a.ctrl[2];
+    int oi = (int)a.ctrl[3];
+    long long n_acc = (long long)a.ctrl[4], n_rej = (long long)a.ctrl[5];
+    int chunk = 0, attempts = 0, status = 0;
+    const double n_el = (double)a.B * SW_D;
+    while (true) {
+        if (oi >= a.T) { status = 0; break; }
+        if (attempts >= a.max_attempts || (a.ckpt && chunk >= a.cap)) { status = 1; break; }
+        const double t_new = tb + dt;
+        if (!(isfinite(dt) && t_new > tb)) { status = 2; break; }
+        const float dtf = (float)dt;
+        float* ck = a.ckpt ? a.ckpt + ((size_t)chunk * SW_MAXS) * slot_stride + (size_t)tt * SW_REC : nullptr;
+        if (ck && live) {
+            if (h < SW_D) ck[h] = prev1[h];
+            ck[SW_D + h] = prev2;
+        }
+#pragma unroll
+        for (int s = 1; s < SW_MAXS; ++s) {
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) {
+                float acc = 0.f;
+#pragma unroll
+                for (int r = 0; r < s; ++r) acc = fmaf(a.A[s][r], k[r][d], acc);
+                ys[d] = fmaf(dtf, acc, y[d]);
+            }
+            float x2;
+            sw_rhs<BR>(sm, L, gbase, h, lane_ok, ys, prev1, prev2, k[s], x2);
+            if (ck && live) {
+                float* c = ck + (size_t)s * slot_stride;
+                if (h < SW_D) c[h] = ys[h];
+                c[SW_D + h] = x2;
+            }
+        }
+        ++attempts;
+        // ---- error norm over the whole batch (the controller's one global RMS)
+        double esum = 0.0;
+        if (live && h < SW_D) {
+            float e = 0.f;
+#pragma unroll
+            for (int s = 0; s < SW_MAXS; ++s) e = fmaf(a.E[s], k[s][h], e);
+            e *= dtf;
+            const float q = e / fmaf(a.rtol, fmaxf(fabsf(y[h]), fabsf(ys[h])), a.atol);
+            esum = (double)q * (double)q;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) esum += __shfl_xor_sync(0xffffffffu, esum, o);
+        if (lane == 0) red[warp] = esum;
+        __syncthreads();
+        double tot = 0.0;
+#pragma unroll
+        for (int w = 0; w < SW_WARPS; ++w) tot += red[w];
+        __syncthreads();
+        const double ratio = sqrt(tot / n_el);
+        if (!isfinite(ratio)) { status = 3; break; }
+        if (ratio <= 1.0) {
+            while (oi < a.T && a.times[oi] <= t_new) {
+                float w[9];
+                sw_dense_weights(a.cmid, tb, t_new, a.times[oi], dt, w);
+                if (live && h < SW_D) {
+                    float v;
+                    if (w[1] == 1.f && w[0] == 0.f) v = ys[h];              // tq == tb: the step's end point itself
+                    else {
+                        v = w[0] * y[h];
+                        v = fmaf(w[1], ys[h], v);
+#pragma unroll
+                        for (int s = 0; s < SW_MAXS; ++s) v = fmaf(w[2 + s], k[s][h], v);
+                    }
+                    a.out[((size_t)oi * a.B + tt) * SW_D + h] = v;
+                }
+                if (tid == 0 && a.rec_step) {
+                    a.rec_step[oi] = (int)n_acc;
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) a.rec_w[oi * 9 + i] = w[i];
+                }
+                ++oi;
+            }
+            if (tid == 0 && a.dts) a.dts[chunk] = dtf;
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) { y[d] = ys[d]; k[0][d] = k[SW_MAXS - 1][d]; }
+            ta = tb; tb = t_new;
+            ++n_acc; ++chunk;
+        } else {
+            ++n_rej;
+        }
+        if (ratio == 0.0) dt *= 10.0;
+        else dt *= fmin(10.0, fmax(0.9 / pow(ratio, 0.2), ratio < 1.0 ? 1.0 : 0.2));
+    }
+    if (live) {
+        if (h < SW_D) { a.y[tt * SW_D + h] = y[h]; a.fy[tt * SW_D + h] = k[0][h]; }
+        if (FERRO && a.state) {
+            if (h < SW_D) a.state[tt * SF + h] = prev1[h];
+            a.state[tt * SF + SW_D + h] = prev2;
+        }
+    }
+    if (tid == 0) {
+        a.ctrl[0] = tb; a.ctrl[1] = ta; a.ctrl[2] = dt; a.ctrl[3] = (double)oi; a.ctrl[4] = (double)n_acc;
+        a.ctrl[5] = (double)n_rej; a.ctrl[6] = (double)status; a.ctrl[7] = (double)chunk;
+    }
+}
+
+template <int BR>
+__global__ void __launch_bounds__(SW_THREADS) smallnet_wide_solve_bwd_kernel(const SWSolveArgs a) {
+    extern __shared__ float4 sw_smem4[];
+    float* sm = reinterpret_cast<float*>(sw_smem4);
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    constexpr bool FERRO = BR == FETODE_BRANCH_FERRO2D;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < L.total_ext / 4; i += SW_THREADS) sw_smem4[i] = reinterpret_cast<const float4*>(a.packed)[i];
+    float* acc_all = sm + L.total_ext;
+    float* tile_all = acc_all + SW_WARPS * SW_NACC * 32;
+    for (int i = tid; i < SW_WARPS * SW_NACC * 32; i += SW_THREADS) acc_all[i] = 0.f;
+    int oi = *a.cursor;                                  // read by everyone before the barrier, written after the sweep
+    __syncthreads();
+    float* acc = acc_all + warp * SW_NACC * 32 + lane;
+    float* tile = tile_all + warp * SW_D * 32 * SW_TSTRIDE;
+    const bool lane_ok = lane < SW_GRP * SW_H;
+    const int g = lane_ok ? lane / SW_H : 0, h = lane_ok ? lane % SW_H : 0, gbase = lane_ok ? g * SW_H : lane;
+    const int t = warp * SW_GRP + g;
+    const bool live = lane_ok && t < a.B;
+    const int tt = live ? t : 0;
+    const size_t slot_stride = (size_t)a.B * SW_REC;
+    float cy[SW_D], ckk[SW_D];
+#pragma unroll
+    for (int d = 0; d < SW_D; ++d) { cy[d] = live ? a.carry_y[tt * SW_D + d] : 0.f; ckk[d] = live ? a.carry_k[tt * SW_D + d] : 0.f; }
+    for (int n = a.n_steps - 1; n >= 0; --n) {
+        const float dtf = a.dts[n];
+        float G[9][SW_D];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { G[i][0] = 0.f; G[i][1] = 0.f; }
+        while (oi >= 1 && a.rec_step[oi] == a.step_base + n) {
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) {
+                const float go = live ? a.g_out[((size_t)oi * a.B + tt) * SW_D + d] : 0.f;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) G[i][d] = fmaf(a.rec_w[oi * 9 + i], go, G[i][d]);
+            }
+            --oi;
+        }
+        const float* ck = a.ckpt + ((size_t)n * SW_MAXS) * slot_stride + (size_t)tt * SW_REC;
+        float gY[SW_MAXS][SW_D], gy[SW_D] = {0.f, 0.f};
+#pragma unroll
+        for (int s = 0; s < SW_MAXS; ++s) { gY[s][0] = 0.f; gY[s][1] = 0.f; }
+#pragma unroll
+        for (int s = SW_MAXS - 1; s >= 1; --s) {
+            float gk[SW_D], gin[SW_D], yin[SW_D], pin[SW_D];
+            const float* c = ck + (size_t)s * slot_stride;
+            const float* cp = ck + (size_t)(s - 1) * slot_stride;
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) {
+                float v = G[2 + s][d] + (s == SW_MAXS - 1 ? ckk[d] : 0.f);
+#pragma unroll
+                for (int q = s + 1; q < SW_MAXS; ++q) v = fmaf(dtf * a.A[q][s], gY[q][d], v);
+                gk[d] = live ? v : 0.f;
+                yin[d] = c[d];
+                pin[d] = cp[d];
+            }
+            sw_rhs_bwd<BR>(sm, L, gbase, h, lane, lane_ok, yin, pin, FERRO ? cp[SW_D + h] : 0.f, c[SW_D + h], gk, gin, acc,
+                           tile);
+#pragma unroll
+            for (int d = 0; d < SW_D; ++d) {
+                gY[s][d] = gin[d] + (s == SW_MAXS - 1 ? G[1][d] + cy[d] : 0.f);
+                gy[d] += gY[s][d];
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < SW_D; ++d) {
+            float w = G[2][d];
+#pragma unroll
+            for (int q = 1; q < SW_MAXS; ++q) w = fmaf(dtf * a.A[q][0], gY[q][d], w);
+            ckk[d] = w;
+            cy[d] = gy[d] + G[0][d];
+        }
+    }
+    if (live && h < SW_D) { a.carry_y[tt * SW_D + h] = cy[h]; a.carry_k[tt * SW_D + h] = ckk[h]; }
+    __syncthreads();
+    if (tid == 0) *a.cursor = oi;
+    const SNGfoldW gf = snw_gfold(SW_D, SW_H, SW_F, SW_NB);
+    for (int i = tid; i < SW_NACC * SW_H; i += SW_THREADS) {
+        const int c = i / SW_H, hh = i % SW_H;
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < SW_WARPS; ++w)
+#pragma unroll
+            for (int gg = 0; gg < SW_GRP; ++gg) v += acc_all[(w * SW_NACC + c) * 32 + gg * SW_H + hh];
+        if (v == 0.f) continue;
+        int dst = -1;
+        if (c < SW_C_BP2) { const int f = c / SW_D, o = c % SW_D; dst = gf.ws2 + (hh * SW_F + f) * SW_D + o; }
+        else if (c < SW_C_W1) { const int q = c - SW_C_BP2; dst = gf.bp2 + (q / SW_NB) * SW_H * SW_NB + hh * SW_NB + q % SW_NB; }
+        else if (c < SW_C_GS1) { const int q = c - SW_C_W1; dst = gf.ws1 + q * SW_H + hh; }
+        else if (c == SW_C_GS1) dst = gf.gsum1 + hh;
+        else if (c < SW_C_GS2) { const int q = c - SW_C_BP1; dst = gf.bp1 + (q / SW_D) * SW_D * SW_NB + (q % SW_D) * SW_NB + hh; }
+        else if (hh < SW_D) dst = gf.gsum2 + hh;
+        if (dst >= 0) atomicAdd(a.gfold + dst, v);
+    }
+}
+
 }  // namespace fetode
 
 using namespace fetode;
@@ -864,6 +1141,98 @@ extern "C" int fetode_smallnet_attempt_bwd(const fetode_smallnet_t* net, const f
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e) return (int)e;
         k<<<grid, SW_THREADS, smem, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}
+
+// ---- the whole dopri5 solve on the device (B <= 12) -------------------------------------------------------------------
+static void snw_dp5_tableau(SWSolveArgs& a) {
+    static const double A[7][6] = {
+        {0, 0, 0, 0, 0, 0},
+        {1.0 / 5, 0, 0, 0, 0, 0},
+        {3.0 / 40, 9.0 / 40, 0, 0, 0, 0},
+        {44.0 / 45, -56.0 / 15, 32.0 / 9, 0, 0, 0},
+        {19372.0 / 6561, -25360.0 / 2187, 64448.0 / 6561, -212.0 / 729, 0, 0},
+        {9017.0 / 3168, -355.0 / 33, 46732.0 / 5247, 49.0 / 176, -5103.0 / 18656, 0},
+        {35.0 / 384, 0, 500.0 / 1113, 125.0 / 192, -2187.0 / 6784, 11.0 / 84}};
+    static const double E[7] = {35.0 / 384 - 1951.0 / 21600, 0, 500.0 / 1113 - 22642.0 / 50715, 125.0 / 192 - 451.0 / 720,
+                                -2187.0 / 6784 + 12231.0 / 42400, 11.0 / 84 - 649.0 / 6300, -1.0 / 60};
+    static const double M[7] = {6025192743.0 / 30085553152.0 / 2, 0, 51252292925.0 / 65400821598.0 / 2,
+                                -2691868925.0 / 45128329728.0 / 2, 187940372067.0 / 1594534317056.0 / 2,
+                                -1776094331.0 / 19743644256.0 / 2, 11237099.0 / 235043384.0 / 2};
+    for (int i = 0; i < 7; ++i) {
+        a.E[i] = (float)E[i];
+        a.cmid[i] = M[i];
+        for (int j = 0; j < 7; ++j) a.A[i][j] = j < 6 ? (float)A[i][j] : 0.f;
+    }
+}
+
+extern "C" int32_t fetode_smallnet_dp5_max_rows(void) { return SW_SOLVE_MAXB; }
+
+extern "C" int64_t fetode_smallnet_dp5_ckpt_floats(const fetode_smallnet_t* net, int64_t B, int32_t cap) {
+    if (!snw_has(net) || B < 0 || B > SW_SOLVE_MAXB || cap < 0) return -1;
+    return (int64_t)cap * SW_MAXS * B * SW_REC;
+}
+
+extern "C" int fetode_smallnet_dp5_solve_fwd(const fetode_smallnet_t* net, const float* packed, float* y, float* fy,
+                                             float* state, int state_is_zero, int64_t B, const double* times, int32_t T,
+                                             float* out, double* ctrl, double rtol, double atol, float* ckpt, float* dts,
+                                             int32_t cap, int32_t* rec_step, float* rec_w, int32_t max_attempts,
+                                             void* stream) {
+    if (!snw_has(net)) return FETODE_EUNSUPPORTED;
+    FETODE_CHECK_ARG(packed && y && fy && times && out && ctrl && T >= 1 && B >= 1 && max_attempts >= 1);
+    if (B > SW_SOLVE_MAXB) return FETODE_EUNSUPPORTED;
+    if (ckpt) FETODE_CHECK_ARG(dts && rec_step && rec_w && cap >= 1);
+    if (net->branch == FETODE_BRANCH_FERRO2D && !state_is_zero) FETODE_CHECK_ARG(state != nullptr);
+    SWSolveArgs a{};
+    snw_dp5_tableau(a);
+    a.packed = packed; a.y = y; a.fy = fy; a.state = state; a.out = out; a.times = times; a.ctrl = ctrl; a.ckpt = ckpt;
+    a.dts = dts; a.rec_step = rec_step; a.rec_w = rec_w; a.rtol = (float)rtol; a.atol = (float)atol; a.B = (int)B; a.T = T;
+    a.cap = cap; a.max_attempts = max_attempts; a.state_is_zero = state_is_zero;
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    const size_t smem = (size_t)L.total * 4;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (net->branch == FETODE_BRANCH_FERRO2D) {
+        auto k = smallnet_wide_solve_fwd_kernel<FETODE_BRANCH_FERRO2D>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<1, SW_THREADS, smem, st>>>(a);
+    } else {
+        auto k = smallnet_wide_solve_fwd_kernel<FETODE_BRANCH_LOGISTIC>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<1, SW_THREADS, smem, st>>>(a);
+    }
+    return FETODE_LAUNCH_RC();
+}
+
+extern "C" int fetode_smallnet_dp5_solve_bwd(const fetode_smallnet_t* net, const float* packed, const float* ckpt,
+                                             const float* dts, int32_t n_steps, int32_t step_base, const int32_t* rec_step,
+                                             const float* rec_w, const float* g_out, int32_t* cursor, float* carry_y,
+                                             float* carry_k, float* gfold, int64_t B, void* stream) {
+    if (!snw_has(net)) return FETODE_EUNSUPPORTED;
+    FETODE_CHECK_ARG(packed && ckpt && dts && rec_step && rec_w && g_out && cursor && carry_y && carry_k && gfold &&
+                     n_steps >= 0 && B >= 1);
+    if (B > SW_SOLVE_MAXB) return FETODE_EUNSUPPORTED;
+    if (n_steps == 0) return FETODE_OK;
+    SWSolveArgs a{};
+    snw_dp5_tableau(a);
+    a.packed = packed; a.ckpt = const_cast<float*>(ckpt); a.dts = const_cast<float*>(dts); a.n_steps = n_steps;
+    a.step_base = step_base; a.rec_step = const_cast<int*>(rec_step); a.rec_w = const_cast<float*>(rec_w); a.g_out = g_out;
+    a.cursor = cursor; a.carry_y = carry_y; a.carry_k = carry_k; a.gfold = gfold; a.B = (int)B;
+    constexpr SNLayout L = sn_layout(SW_D, SW_H, SW_NB, SW_G);
+    const size_t smem = (size_t)(L.total_ext + SW_WARPS * SW_NACC * 32 + SW_WARPS * SW_D * 32 * SW_TSTRIDE) * 4;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (net->branch == FETODE_BRANCH_FERRO2D) {
+        auto k = smallnet_wide_solve_bwd_kernel<FETODE_BRANCH_FERRO2D>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<1, SW_THREADS, smem, st>>>(a);
+    } else {
+        auto k = smallnet_wide_solve_bwd_kernel<FETODE_BRANCH_LOGISTIC>;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e) return (int)e;
+        k<<<1, SW_THREADS, smem, st>>>(a);
     }
     return FETODE_LAUNCH_RC();
 }

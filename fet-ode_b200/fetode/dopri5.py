@@ -233,16 +233,19 @@ class _FusedSolve:
     def _attempt(self, rk, y, k0, want_y1, want_err, want_ckpt):
         L = lib()
         B, D = self.B, self.D
-        ks = torch.empty(rk.n_stages, B, D, dtype=torch.float32, device=self.dev)
-        y1 = torch.empty(B, D, dtype=torch.float32, device=self.dev) if want_y1 else None
-        ck = None
+        # ks | y1 | ckpt share one allocation (the caching allocator is the second largest host cost of an attempt)
+        n_ks, n_y1, n_ck = rk.n_stages * B * D, (B * D if want_y1 else 0), 0
         if want_ckpt:
             key = (rk.n_stages, rk.first_eval)
-            n = self._ck_floats.get(key)
-            if n is None:
-                n = self._ck_floats[key] = int(L.fetode_smallnet_attempt_ckpt_floats(C.byref(self.plan.net), C.byref(rk),
-                                                                                      C.c_int64(B)))
-            ck = torch.empty(max(n, 1), dtype=torch.float32, device=self.dev)
+            n_ck = self._ck_floats.get(key)
+            if n_ck is None:
+                n_ck = self._ck_floats[key] = int(L.fetode_smallnet_attempt_ckpt_floats(C.byref(self.plan.net),
+                                                                                      C.byref(rk), C.c_int64(B)))
+        pad = (-(n_ks + n_y1)) % 4                           # checkpoint records stay 16-byte aligned
+        buf = torch.empty(n_ks + n_y1 + pad + n_ck, dtype=torch.float32, device=self.dev)
+        ks = buf[:n_ks].view(rk.n_stages, B, D)
+        y1 = buf[n_ks:n_ks + n_y1].view(B, D) if want_y1 else None
+        ck = buf[n_ks + n_y1 + pad:] if want_ckpt else None
         err_ptr = C.c_void_p(0)
         if want_err:
             if self._acc is None or self._slot >= self._acc.numel():
@@ -258,6 +261,64 @@ class _FusedSolve:
             err = self._acc[self._slot]
             self._slot += 1
         return y1, ks, ck, err
+
+    # -- controller on the device (B <= 12: one CTA holds the batch; the reference's LV run is one trajectory)
+    CHUNK = 4096            # accepted steps per launch when the reverse sweep is wanted (checkpoint chunk)
+    ATTEMPTS = 1 << 16      # attempts per launch: bounds the run time of one launch (~0.6 s)
+
+    def _device_controller_ok(self, sync) -> bool:
+        import os
+        return (sync is None and os.environ.get("FETODE_DOPRI5_DEVICE", "1") != "0"
+                and self.B <= int(lib().fetode_smallnet_dp5_max_rows()))
+
+    def _run_on_device(self, y, f0, times, dt, max_steps, stats):
+        L = lib()
+        B, D, dev, T = self.B, self.D, self.dev, len(times)
+        out = torch.empty(T, B, D, dtype=torch.float32, device=dev)
+        out[0].copy_(y)
+        if T == 1:
+            if stats is not None:
+                stats.update(accepted=0, rejected=0, fused=True, device_controller=True)
+            return out
+        times_d = torch.tensor(times, dtype=torch.float64).to(dev)
+        ctrl = torch.tensor([times[0], times[0], dt, 1.0, 0.0, 0.0, 0.0, 0.0], dtype=torch.float64).to(dev)
+        ycur, fy = y.clone(), f0.clone()
+        self.chunks = []
+        self.rec_step = self.rec_w = None
+        if self.keep:
+            self.rec_step = torch.full((T,), -1, dtype=torch.int32, device=dev)
+            self.rec_w = torch.zeros(T, 9, dtype=torch.float32, device=dev)
+            n_ck = int(L.fetode_smallnet_dp5_ckpt_floats(C.byref(self.plan.net), C.c_int64(B), C.c_int32(self.CHUNK)))
+        base = 0
+        while True:
+            ck = dts = None
+            if self.keep:
+                ck = torch.empty(n_ck, dtype=torch.float32, device=dev)
+                dts = torch.empty(self.CHUNK, dtype=torch.float32, device=dev)
+            budget = int(min(self.ATTEMPTS, max(1, max_steps + 1)))
+            check(L.fetode_smallnet_dp5_solve_fwd(
+                C.byref(self.plan.net), ptr(self.img), ptr(ycur), ptr(fy), ptr(self.st), C.c_int(1 if self.fresh else 0),
+                C.c_int64(B), C.c_void_p(times_d.data_ptr()), C.c_int32(T), ptr(out), C.c_void_p(ctrl.data_ptr()),
+                C.c_double(self.rtol), C.c_double(self.atol), ptr(ck), ptr(dts), C.c_int32(self.CHUNK),
+                C.c_void_p(self.rec_step.data_ptr() if self.keep else 0), ptr(self.rec_w), C.c_int32(budget), stream()),
+                "smallnet_dp5_solve_fwd")
+            self.fresh = False
+            c = ctrl.tolist()                                  # the one synchronisation of this launch
+            n_chunk, status = int(c[7]), int(c[6])
+            if self.keep and n_chunk > 0:
+                self.chunks.append((ck, dts, n_chunk, base))
+                base += n_chunk
+            if status == 2:
+                raise AssertionError(f"fetode.odeint(dopri5): underflow in dt {c[2]}")
+            if status == 3:
+                raise AssertionError("fetode.odeint(dopri5): non-finite values in the state / error estimate")
+            if c[4] + c[5] > max_steps:
+                raise RuntimeError("fetode.odeint(dopri5): max_num_steps exceeded")
+            if status == 0:
+                break
+        if stats is not None:
+            stats.update(accepted=int(c[4]), rejected=int(c[5]), fused=True, device_controller=True)
+        return out
 
     def _run(self, y, times, options):
         from .odeint import combine
@@ -291,6 +352,8 @@ class _FusedSolve:
             h1 = max(1e-6, h0 * 1e-3) if (d1 <= 1e-15 and d2 <= 1e-15) else (0.01 / max(d1, d2)) ** 0.2
             dt = min(100.0 * h0, h1)
 
+        if self._device_controller_ok(sync):
+            return self._run_on_device(y, f0, times, dt, max_steps, stats)
         sol = [y]
         fy, ta, tb = f0, times[0], times[0]
         dense = None
@@ -372,6 +435,16 @@ class FusedDopri5Fn(torch.autograd.Function):
             return g_y, g_k0
 
         carry_y = carry_k = None
+        if getattr(sv, "chunks", None):
+            T = g_out.shape[0]
+            cursor = torch.full((1,), T - 1, dtype=torch.int32, device=dev)
+            carry_y = torch.zeros(B, D, dtype=torch.float32, device=dev)
+            carry_k = torch.zeros(B, D, dtype=torch.float32, device=dev)
+            for ck, dts, n, base in reversed(sv.chunks):
+                check(L.fetode_smallnet_dp5_solve_bwd(net, img, ptr(ck), ptr(dts), C.c_int32(n), C.c_int32(base),
+                                                      C.c_void_p(sv.rec_step.data_ptr()), ptr(sv.rec_w), ptr(g_out),
+                                                      C.c_void_p(cursor.data_ptr()), ptr(carry_y), ptr(carry_k),
+                                                      ptr(gfold), C.c_int64(B), stream()), "smallnet_dp5_solve_bwd")
         for n in range(len(sv.steps) - 1, -1, -1):
             dt, ck = sv.steps[n]
             rk = sv.rk

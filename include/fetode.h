@@ -250,6 +250,28 @@ FETODE_API int fetode_smallnet_attempt_bwd(const fetode_smallnet_t* net, const f
                          const fetode_rk_attempt_t* rk, const float* ckpt, const float* g_y1, const float* g_ks,
                          const float* x_y1, const float* x_klast, const float* x_y, float* g_y, float* g_k0,
                          float* gfold, int64_t B, void* stream);
+/* The WHOLE dopri5 solve on the device for B <= fetode_smallnet_dp5_max_rows() (12) trajectories -- the reference's
+ * Lotka-Volterra run is one (train_kanfet_node_predprey.py:146-147, :252): torchdiffeq's _adaptive_step loop (attempt,
+ * error ratio, accept / reject, _optimal_step_size with safety 0.9 / ifactor 10 / dfactor 0.2, _interp_evaluate at the
+ * requested times) runs inside one CTA; the host launches once per `cap` accepted steps.
+ *   y, fy [B,D]: solution and FSAL slope f(y) at ctrl[0], in/out;  times [T] (device doubles), out [T,B,D] (row 0 is the
+ *   caller's);  ctrl [8] device doubles, in/out: tb, ta, dt, next output index (start at 1), accepted, rejected,
+ *   status (0 done | 1 launch again | 2 dt underflow | 3 non-finite error ratio), accepted steps in this launch.
+ *   Reverse sweep (optional, ckpt != NULL): ckpt [cap][7][B][12] (fetode_smallnet_dp5_ckpt_floats), dts [cap],
+ *   rec_step [T] / rec_w [T][9]: which accepted step produced output i and with which weights of (ya, yb, k_0..k_6).
+ * _solve_bwd walks one chunk backwards: g_out [T,B,D] adjoints of the outputs, *cursor (device int, start T-1) the highest
+ * output not yet consumed, carry_y / carry_k [B,D] in/out (zero before the last chunk; after the first chunk they are
+ * the adjoints of y(t0) -- without g_out[0] -- and of f(y0)), gfold as fetode_smallnet_rk_bwd. */
+FETODE_API int32_t fetode_smallnet_dp5_max_rows(void);
+FETODE_API int64_t fetode_smallnet_dp5_ckpt_floats(const fetode_smallnet_t* net, int64_t B, int32_t cap);
+FETODE_API int fetode_smallnet_dp5_solve_fwd(const fetode_smallnet_t* net, const float* packed, float* y, float* fy,
+                         float* state, int state_is_zero, int64_t B, const double* times, int32_t T, float* out,
+                         double* ctrl, double rtol, double atol, float* ckpt, float* dts, int32_t cap,
+                         int32_t* rec_step, float* rec_w, int32_t max_attempts, void* stream);
+FETODE_API int fetode_smallnet_dp5_solve_bwd(const fetode_smallnet_t* net, const float* packed, const float* ckpt,
+                         const float* dts, int32_t n_steps, int32_t step_base, const int32_t* rec_step,
+                         const float* rec_w, const float* g_out, int32_t* cursor, float* carry_y, float* carry_k,
+                         float* gfold, int64_t B, void* stream);
 FETODE_API int fetode_smallnet_rhs(const fetode_smallnet_t* net, const float* packed, const float* y,
                         float* dy, float* state, int state_is_zero, int64_t B, void* stream);
 

@@ -115,3 +115,61 @@ def test_fused_dopri5_single_time_and_first_step_option(cuda):
         two = fetode.odeint(lambda tt, X: m(X), x0, torch.tensor([0.0, 0.3]), rtol=1e-4, atol=1e-6,
                             options={"first_step": 0.05, "stats": st})
     assert two.shape == (2, 3, 2) and st["accepted"] >= 1 and torch.isfinite(two).all()
+
+
+@pytest.mark.parametrize("branch", ["logistic", "ferro2d"])
+def test_device_controller_equals_host_controller(cuda, branch, monkeypatch):
+    """B <= 12: the accept / reject loop itself runs in the kernel (fetode_smallnet_dp5_solve_fwd / _bwd).  Same
+    arithmetic per attempt as the host-controlled launches, so values, step counts and gradients agree closely."""
+    layers, m = fetode_kan_random([2, 10, 2], branch, seed=41, device=cuda)
+    x0 = lv_inputs(5, 6)
+    t = torch.linspace(0, 0.9, 10, dtype=torch.float64)
+    res = []
+    for dev_ctl in ("1", "0"):
+        monkeypatch.setenv("FETODE_DOPRI5_DEVICE", dev_ctl)
+        m.zero_grad()
+        if branch == "ferro2d":
+            m.reset_state()
+        st = {}
+        xg = x0.to(cuda).requires_grad_(True)
+        out = fetode.odeint(lambda tt, X: m(X), xg, t, rtol=1e-5, atol=1e-7, options={"stats": st})
+        assert st.get("fused") is True and bool(st.get("device_controller")) == (dev_ctl == "1")
+        out[1:].square().mean().backward()
+        state = m.hysteresis_state(5, cuda).clone() if branch == "ferro2d" else None
+        res.append((out.detach(), xg.grad.clone(), {n: p.grad.clone() for n, p in m.named_parameters()}, st, state))
+    a, b = res
+    assert abs(a[3]["accepted"] - b[3]["accepted"]) <= 2 and abs(a[3]["rejected"] - b[3]["rejected"]) <= 2
+    assert max_rel(a[0], b[0]) < 2e-5
+    if a[3]["accepted"] == b[3]["accepted"] and a[3]["rejected"] == b[3]["rejected"]:
+        assert max_rel(a[1], b[1]) < 1e-4
+        for n in a[2]:
+            assert max_rel(a[2][n], b[2][n]) < 1e-4, n
+        if state is not None:
+            assert max_rel(a[4], b[4]) < 1e-4
+
+
+def test_device_controller_resumes_across_launches(cuda, monkeypatch):
+    """Checkpoint chunks of 7 accepted steps and 5 attempts per launch: the solve is re-launched many times and must
+    give what one launch gives (the controller state travels in ctrl[8], the adjoint carries in carry_y / carry_k)."""
+    from fetode import dopri5
+    layers, m = fetode_kan_random([2, 10, 2], "ferro2d", seed=43, device=cuda)
+    x0 = lv_inputs(12, 2)
+    t = torch.linspace(0, 0.5, 6, dtype=torch.float64)
+    res = []
+    for chunk, attempts in ((4096, 1 << 16), (7, 5)):
+        monkeypatch.setattr(dopri5._FusedSolve, "CHUNK", chunk)
+        monkeypatch.setattr(dopri5._FusedSolve, "ATTEMPTS", attempts)
+        m.zero_grad()
+        m.reset_state()
+        st = {}
+        xg = x0.to(cuda).requires_grad_(True)
+        out = fetode.odeint(lambda tt, X: m(X), xg, t, rtol=1e-5, atol=1e-7, options={"stats": st})
+        assert st.get("device_controller") is True
+        (out * torch.arange(1, 7, device=cuda).view(6, 1, 1)).sum().backward()
+        res.append((out.detach(), xg.grad.clone(), {n: p.grad.clone() for n, p in m.named_parameters()}, st))
+    a, b = res
+    assert a[3] == b[3] and a[3]["accepted"] > 14
+    assert torch.equal(a[0], b[0])
+    assert max_rel(a[1], b[1]) < 1e-5
+    for n in a[2]:
+        assert max_rel(a[2][n], b[2][n]) < 1e-5, n
