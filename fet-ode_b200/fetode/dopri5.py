@@ -6,8 +6,9 @@ algorithm (SURVEY appendix B -- PARITY UNPINNED): FSAL tableau, Hairer initial s
 state tensor, controller safety 0.9 / ifactor 10 / dfactor 0.2, 4th-order dense output, time kept in float64 on the host.
 
 Two execution paths (both on the GPU): FUSED when ``func(t, y)`` is a bare call of a small KAN / KANFET the
-hidden-units-on-lanes kernels support (the Lotka-Volterra script's model: one launch per attempted step, one per accepted
-step in the reverse sweep -- see ``_FusedSolve`` below), STAGED for any other callable:
+hidden-units-on-lanes kernels support (the Lotka-Volterra script's model: for B <= 12 the whole accept / reject loop
+runs inside one kernel, for larger batches one launch per attempted step and one per accepted step in the reverse sweep
+-- see ``_FusedSolve`` below), STAGED for any other callable:
 
 The right-hand side is called once per stage, in the order torchdiffeq calls it (stateful neurons mutate their
 hysteresis snapshot on every call, including the initial-step probe and rejected attempts).  Stage sums, the error
