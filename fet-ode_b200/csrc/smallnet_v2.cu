@@ -265,10 +265,10 @@ __device__ __forceinline__ float sn2_horner(const float4 c, float s) {
 // ------------------------------------------------------------------------------------------
 // one right-hand-side evaluation for the TP pairs of this lane
 // ------------------------------------------------------------------------------------------
-// SPLIT = 2: two adjacent lanes share a pair of trajectories -- both evaluate the layer-1 features (2 of the 12 inputs of
-// a right-hand side), each owns H/2 hidden units (their layer-1 sums, layer-2 features and partial outputs), and the
-// partial outputs meet in one shuffle.  1.19x the instructions for twice the warps and a chain of 7 instead of 12
-// inputs per lane: the shape for batches too small to fill the SMs with one lane per pair (latency-bound regime).
+// SPLIT = 2: two adjacent lanes share a pair of trajectories -- each evaluates the layer-1 features of ONE of the two
+// inputs and that input's contribution to every hidden unit, each owns H/2 hidden units (their layer-2 features and
+// partial outputs); the layer-1 halves and the partial outputs cross in shuffles.  Twice the warps and a chain of 6
+// instead of 12 inputs per lane: the shape for batches too small to fill the SMs with one lane per pair.
 template <int D, int H, int NB, int G, int BR, int TP, int THREADS, bool UNI, int SPLIT>
 __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x2 (&ys)[D][TP], f32x2 (&prev1)[D][TP],
                                         f32x2* colcur, const f32x2* colprev, f32x2 (&out)[D][TP], const int sub) {
@@ -278,26 +278,33 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
     static_assert(H % SPLIT == 0, "hidden units must divide over the split lanes");
     const int h0 = SPLIT > 1 ? sub * HS : 0;
     const float4 hdr = *reinterpret_cast<const float4*>(sm + L.hdr);
-    // ---------------- layer 1: per input d, its features once, then a rolled loop over the H outputs; the partial
-    // sums of output h travel through this thread's column (colcur[h]) between the two inputs
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
+    if constexpr (SPLIT > 1) {
+        // ---------------- layer 1, split lanes: lane `sub` evaluates the features of input d = sub ONLY and forms that
+        // input's contribution to all H pre-activations; per pair of units (one mine, one the partner's) the partner's
+        // half crosses in one shuffle.  No feature is evaluated twice (the first SPLIT build evaluated both inputs in
+        // both lanes: 1.19x the instructions).
+        static_assert(SPLIT == 2 && D == 2, "input-split layer 1: two lanes, two inputs");
+        const int d = sub;
         const float* blk = sm + L.l1 + d * L.L1S;
         f32x2 silu[TP], r[TP][NB];
         {
             f32x2 xin[TP], pv[TP];
 #pragma unroll
-            for (int p = 0; p < TP; ++p) { xin[p] = ys[d][p]; pv[p] = prev1[d][p]; prev1[d][p] = ys[d][p]; }
+            for (int p = 0; p < TP; ++p) {
+                xin[p] = sub ? ys[1][p] : ys[0][p];
+                pv[p] = sub ? prev1[1][p] : prev1[0][p];
+                prev1[0][p] = ys[0][p];
+                prev1[1][p] = ys[1][p];
+            }
             sn2_features<NB, BR, TP>(xin, pv, pk2(hdr.x, hdr.y), blk + L.o_bc, silu, r);
         }
-        // spline term: scalar per trajectory (the interval differs between the two halves of a pair)
         const float4 gi = *reinterpret_cast<const float4*>(blk + L.o_gi);
         float sp_s[2 * TP], sp_k[2 * TP];
         int sp_m[2 * TP];
 #pragma unroll
         for (int p = 0; p < TP; ++p) {
             float xs[2];
-            upk2(ys[d][p], xs[0], xs[1]);
+            upk2(sub ? ys[1][p] : ys[0][p], xs[0], xs[1]);
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 int m;
@@ -306,22 +313,14 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
             }
         }
         const float4* tab = reinterpret_cast<const float4*>(sm + L.l1tab);
-#pragma unroll 2
-        for (int hh = 0; hh < HS; ++hh) {
-            const int h = h0 + hh;
-            f32x2 acc[TP];
-            if (d == 0) {
-                const f32x2 b = lds_pair(sm + L.b1 + 2 * h);
+        auto unit = [&](int h, bool with_bias, f32x2 (&acc)[TP]) {
+            const f32x2 b = with_bias ? lds_pair(sm + L.b1 + 2 * h) : pk2(0.f, 0.f);
 #pragma unroll
-                for (int p = 0; p < TP; ++p) acc[p] = b;
-            } else {
-#pragma unroll
-                for (int p = 0; p < TP; ++p) acc[p] = colcur[(hh * TP + p) * THREADS];
-            }
+            for (int p = 0; p < TP; ++p) acc[p] = b;
             const float4* w4 = reinterpret_cast<const float4*>(blk + L.o_w1 + h * L.W1Q);
 #pragma unroll
             for (int q = 0; q < (1 + NB + 1) / 2; ++q) {
-                const float4 w = w4[q];                              // features 2q, 2q+1 (0 = silu, 1+j = r_j)
+                const float4 w = w4[q];
 #pragma unroll
                 for (int p = 0; p < TP; ++p) {
                     acc[p] = fma2(pk2(w.x, w.y), q == 0 ? silu[p] : r[p][2 * q - 1], acc[p]);
@@ -334,9 +333,87 @@ __device__ __forceinline__ void sn2_rhs(const float* __restrict__ sm, const f32x
                 upk2(acc[p], lo, hi);
                 lo = fmaf(sn2_horner(tab[sp_m[2 * p] + h], sp_s[2 * p]), sp_k[2 * p], lo);
                 hi = fmaf(sn2_horner(tab[sp_m[2 * p + 1] + h], sp_s[2 * p + 1]), sp_k[2 * p + 1], hi);
-                colcur[(hh * TP + p) * THREADS] = pk2(lo, hi);
+                acc[p] = pk2(lo, hi);
+            }
+        };
+        const int h_other = (1 - sub) * HS;
+#pragma unroll 1
+        for (int hh = 0; hh < HS; ++hh) {
+            f32x2 mine[TP], other[TP];
+            unit(h0 + hh, true, mine);             // my unit, my input (+ the bias, once)
+            unit(h_other + hh, false, other);      // the partner's unit, my input
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                float lo, hi, mlo, mhi;
+                upk2(other[p], lo, hi);
+                upk2(mine[p], mlo, mhi);
+                mlo += __shfl_xor_sync(0xffffffffu, lo, 1);
+                mhi += __shfl_xor_sync(0xffffffffu, hi, 1);
+                colcur[(hh * TP + p) * THREADS] = pk2(mlo, mhi);
             }
         }
+    } else {
+        // ---------------- layer 1: per input d, its features once, then a rolled loop over the H outputs; the partial
+        // sums of output h travel through this thread's column (colcur[h]) between the two inputs
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const float* blk = sm + L.l1 + d * L.L1S;
+            f32x2 silu[TP], r[TP][NB];
+            {
+                f32x2 xin[TP], pv[TP];
+#pragma unroll
+                for (int p = 0; p < TP; ++p) { xin[p] = ys[d][p]; pv[p] = prev1[d][p]; prev1[d][p] = ys[d][p]; }
+                sn2_features<NB, BR, TP>(xin, pv, pk2(hdr.x, hdr.y), blk + L.o_bc, silu, r);
+            }
+            // spline term: scalar per trajectory (the interval differs between the two halves of a pair)
+            const float4 gi = *reinterpret_cast<const float4*>(blk + L.o_gi);
+            float sp_s[2 * TP], sp_k[2 * TP];
+            int sp_m[2 * TP];
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                float xs[2];
+                upk2(ys[d][p], xs[0], xs[1]);
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    int m;
+                    sn2_locate<UNI>(xs[q], blk + L.o_kn, gi, NK, m, sp_s[2 * p + q], sp_k[2 * p + q]);
+                    sp_m[2 * p + q] = (d * L.NI + m) * H;
+                }
+            }
+            const float4* tab = reinterpret_cast<const float4*>(sm + L.l1tab);
+#pragma unroll 2
+            for (int hh = 0; hh < HS; ++hh) {
+                const int h = h0 + hh;
+                f32x2 acc[TP];
+                if (d == 0) {
+                    const f32x2 b = lds_pair(sm + L.b1 + 2 * h);
+#pragma unroll
+                    for (int p = 0; p < TP; ++p) acc[p] = b;
+                } else {
+#pragma unroll
+                    for (int p = 0; p < TP; ++p) acc[p] = colcur[(hh * TP + p) * THREADS];
+                }
+                const float4* w4 = reinterpret_cast<const float4*>(blk + L.o_w1 + h * L.W1Q);
+#pragma unroll
+                for (int q = 0; q < (1 + NB + 1) / 2; ++q) {
+                    const float4 w = w4[q];                              // features 2q, 2q+1 (0 = silu, 1+j = r_j)
+#pragma unroll
+                    for (int p = 0; p < TP; ++p) {
+                        acc[p] = fma2(pk2(w.x, w.y), q == 0 ? silu[p] : r[p][2 * q - 1], acc[p]);
+                        if (2 * q + 1 <= NB) acc[p] = fma2(pk2(w.z, w.w), r[p][2 * q], acc[p]);
+                    }
+                }
+#pragma unroll
+                for (int p = 0; p < TP; ++p) {
+                    float lo, hi;
+                    upk2(acc[p], lo, hi);
+                    lo = fmaf(sn2_horner(tab[sp_m[2 * p] + h], sp_s[2 * p]), sp_k[2 * p], lo);
+                    hi = fmaf(sn2_horner(tab[sp_m[2 * p + 1] + h], sp_s[2 * p + 1]), sp_k[2 * p + 1], hi);
+                    colcur[(hh * TP + p) * THREADS] = pk2(lo, hi);
+                }
+            }
+        }
+
     }
 
     // ---------------- layer 2: loop over its H inputs
@@ -660,14 +737,14 @@ static int sn2_launch_k(const SNArgs& a, const float* img2, cudaStream_t st) {
 }
 
 // Launch shape (measured on B200, profiles/r2_sn_sweep.jsonl).  The kernel is latency-bound (shared-memory operand loads
-// and MUFU chains), so resident warps matter more than spill-freedom:
-//   * from ~2*10^5 rows: two trajectories per lane, 64 registers, four 256-thread CTAs per SM (32 warps; shared memory =
-//     4 x (15 KB image + 40 KB columns)): 2.6e9 traj-steps/s at 2^20 rows (128 registers / 16 warps: 2.2e9; four
-//     trajectories per lane at 168 registers / 12 warps: 2.4e9);
-//   * below that the rows no longer fill the SMs with warps: SPLIT = 2 (two lanes per trajectory pair, half the
-//     hidden units each) doubles the warps and shortens every lane's dependency chain: 65 536 rows 1.26e9 -> 1.60e9,
-//     131 072 rows (the 8-GPU shard of the 2^20 ensemble) 1.90e9 -> 1.95e9.
-// FETODE_SN2_SHAPE=12564|164|2064|2128|2256 overrides (experiments only; read once).
+// and MUFU chains): what pays is a short dependency chain per lane and no spills, then resident warps.
+//   * SPLIT = 2 everywhere: two lanes per trajectory pair, each evaluates ONE input's layer-1 features and owns half the
+//     hidden units (chain of 6 instead of 12 feature evaluations per right-hand side, no feature evaluated twice),
+//     64-thread CTAs at <= 102 registers (zero spills), ten CTAs = 20 warps per SM:
+//       2^20 rows 2.67e9 traj-steps/s, 524 288: 2.65e9, 262 144: 2.62e9, 131 072 (the 8-GPU shard): 2.55e9, 65 536: 2.2e9;
+//   * one lane per pair (64 registers with spills, four 256-thread CTAs = 32 warps per SM) reaches 2.63e9 at 2^20 rows
+//     but starves below: 262 144: 2.20e9, 131 072: 1.90e9, 65 536: 1.26e9 -- kept for A/B runs only.
+// FETODE_SN2_SHAPE=20610|2064|12564|164 overrides (experiments only; read once).
 static int sn2_shape(long long B) {
     static int forced = -1;
     if (forced < 0) {
@@ -675,20 +752,22 @@ static int sn2_shape(long long B) {
         forced = e ? atoi(e) : 0;
     }
     if (forced > 0) return forced;
-    if (B >= 196608) return 12564;
-    return B >= 98304 ? 2128 : 2064;
+    (void)B;
+    return 20610;
 }
 
 template <int BR>
 static int sn2_launch_b(const SNArgs& a, const float* img2, cudaStream_t st) {
     const int shape = sn2_shape(a.B);
-    if (a.tab == FETODE_TABLEAU_RK4_38)
-        return shape == 164 ? sn2_launch_k<BR, 1, 64, 8, true>(a, img2, st) : sn2_launch_k<BR, 1, 256, 4, true>(a, img2, st);
+    if (a.tab == FETODE_TABLEAU_RK4_38) {                                         // torchdiffeq "rk4" (3/8 rule)
+        if (shape == 164) return sn2_launch_k<BR, 1, 64, 8, true>(a, img2, st);
+        if (shape == 12564) return sn2_launch_k<BR, 1, 256, 4, true>(a, img2, st);
+        return sn2_launch_k<BR, 1, 64, 10, true, 2>(a, img2, st);
+    }
     switch (shape) {
         case 164: return sn2_launch_k<BR, 1, 64, 8, false>(a, img2, st);
         case 2064: return sn2_launch_k<BR, 1, 64, 8, false, 2>(a, img2, st);      // split pairs, 128 registers
-        case 2128: return sn2_launch_k<BR, 1, 128, 8, false, 2>(a, img2, st);     // split pairs, 64 registers
-        case 2256: return sn2_launch_k<BR, 1, 256, 4, false, 2>(a, img2, st);
+        case 20610: return sn2_launch_k<BR, 1, 64, 10, false, 2>(a, img2, st);    // split pairs, <= 102 registers
         default: return sn2_launch_k<BR, 1, 256, 4, false>(a, img2, st);
     }
 }

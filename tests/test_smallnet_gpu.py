@@ -77,6 +77,30 @@ def test_fixed_step_trajectories_match_oracle(cuda, branch, tableau):
     assert max_rel(got, want) < TRAJ_TOL
 
 
+@pytest.mark.parametrize("branch", ["logistic", "ferro2d"])
+@pytest.mark.parametrize("tableau", ["euler", "midpoint", "rk4_classic", "rk4"])
+def test_lane_per_trajectory_kernel_all_tableaus_above_wide_threshold(cuda, branch, tableau):
+    """13 001 rows (odd: a half-filled pair and a ragged last CTA) is above the hidden-units-on-lanes threshold, so the
+    split-lane kernel of csrc/smallnet_v2.cu runs (two lanes per trajectory pair, the classic and the 3/8 register
+    layouts); every row against the oracle, plus the hysteresis state left behind."""
+    layers, m = fetode_kan_random([2, 10, 2], branch, seed=12, device=cuda)
+    f, states = _oracle_rhs(layers, branch)
+    B = 13001
+    x0 = lv_inputs(B, 3)
+    x0[:4000] = torch.rand(4000, 2) * 3 - 1.5                     # rows inside the knot span
+    n, dt = 12, 0.014
+    t = torch.arange(n + 1, dtype=torch.float64) * dt
+    with torch.no_grad():
+        if tableau == "rk4_classic":
+            want = OS.rk4_classic(f, x0, 0.0, n * dt, n, trajectory=True)
+        else:
+            want = OS.odeint(f, x0, t, method=tableau)
+        got = fetode.odeint(lambda tt, X: m(X), x0.to(cuda), t, method=tableau)
+    assert got.shape == want.shape
+    assert max_rel(got, want) < TRAJ_TOL
+    assert torch.isfinite(got).all()
+
+
 def test_fused_path_equals_staged_path(cuda):
     """The one-launch fused integration and the stage-by-stage driver agree."""
     layers, m = fetode_kan_random([2, 10, 2], "ferro2d", seed=4, device=cuda)
