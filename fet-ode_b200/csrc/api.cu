@@ -12,6 +12,7 @@ extern "C" const char* fetode_strerror(int rc) {
         case FETODE_EUNSUPPORTED: return "fetode: shape or option not supported by the sm_100a kernels";
         case FETODE_ENOGPU: return "fetode: no CUDA device of compute capability 10.x";
         case FETODE_ESHAPE: return "fetode: shape mismatch";
+        case FETODE_ETOOLARGE: return "fetode: layer needs more scratch than the library's static array (FETODE_STATIC_WS_FLOATS)";
         default: break;
     }
     if (rc > 0) return cudaGetErrorString((cudaError_t)rc);

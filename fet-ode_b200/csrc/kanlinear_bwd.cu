@@ -12,6 +12,8 @@
 //                         parameter gradients (a,b | k,Ec) are reduced over the rows of the tile here
 //   3. kl_unfold_kernel   chain rule from the folded weights back to base_weight / spline_weight /
 //                         spline_scaler / logistic_weight / logistic_scaler / logistic_bias / Ps,bias,coef
+#include <mutex>
+
 #include "kanlinear.cuh"
 
 namespace fetode {
@@ -519,4 +521,49 @@ extern "C" int fetode_kanlinear_unfold(const fetode_kanlayer_t* P, float* ws_acc
                                        void* stream) {
     FETODE_CHECK_ARG(ws_acc && grads);
     return kl_unfold_launch(P, grads, ws_acc, (cudaStream_t)stream);
+}
+
+// ---- fetode_kanlinear_bwd with library-owned scratch (no allocation anywhere on the call path) ----------------------
+// No counterpart in the reference: added for callers that cannot allocate (CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The folded-gradient workspace of
+// fetode_kanlinear_bwd lives in ONE file-scope device array per GPU that loads the library (FETODE_STATIC_WS_FLOATS
+// floats = 1 MiB, held until exit).  Every call shares it and it keeps the last call's contents: the launch clears the
+// part it uses first (cudaMemsetAsync on the caller's stream, as fetode_kanlinear_bwd does for a caller's buffer), and
+// calls that overlap on the GPU (different streams, or replays of two captured graphs at once) RACE on it.
+static __device__ __align__(256) float g_kl_static_ws[FETODE_STATIC_WS_FLOATS];
+
+static int kl_static_ws_address(float** out) {
+    // In host code `g_kl_static_ws` is a host-side stand-in, not a device address: ask the runtime, once per device,
+    // with that device current.
+    constexpr int MAXDEV = 64;
+    static float* addr[MAXDEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= MAXDEV) return FETODE_EUNSUPPORTED;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_kl_static_ws);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return FETODE_EINVAL;
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return FETODE_OK;
+}
+
+extern "C" int64_t fetode_kanlinear_bwd_static_max_floats(void) { return FETODE_STATIC_WS_FLOATS; }
+
+extern "C" int fetode_kanlinear_bwd_static(const fetode_kanlayer_t* P, const float* wcat, const float* x,
+                                           const float* prev, int prev_is_zero, const float* gy, float* gx,
+                                           const fetode_kanlayer_grads_t* grads, int64_t B, void* stream) {
+    const int64_t need = fetode_kanlinear_bwd_ws_floats(P);
+    if (need < 0) return kl_check(P) != FETODE_OK ? kl_check(P) : FETODE_EUNSUPPORTED;
+    if (need > FETODE_STATIC_WS_FLOATS) return FETODE_ETOOLARGE;     // layer needs more scratch than the library holds
+    float* ws = nullptr;
+    int rc = kl_static_ws_address(&ws);
+    if (rc) return rc;
+    return fetode_kanlinear_bwd(P, wcat, x, prev, prev_is_zero, gy, gx, grads, ws, B, stream);
 }

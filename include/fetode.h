@@ -35,6 +35,7 @@ extern "C" {
 #define FETODE_EUNSUPPORTED (-2)   /* shape / option outside what the kernels implement    */
 #define FETODE_ENOGPU       (-3)   /* no sm_100 device                                     */
 #define FETODE_ESHAPE       (-4)   /* shape mismatch (reference raises AssertionError)     */
+#define FETODE_ETOOLARGE    (-5)   /* needs more scratch than the library's static array holds (fetode_kanlinear_bwd_static) */
 
 FETODE_API const char* fetode_strerror(int rc);
 FETODE_API int fetode_version(void);
@@ -109,6 +110,20 @@ FETODE_API int fetode_kanlinear_bwd(const fetode_kanlayer_t* L, const float* wca
                          float* gx /* [B,I] or NULL, overwritten */,
                          const fetode_kanlayer_grads_t* grads, float* ws,
                          int64_t B, void* stream);
+/* fetode_kanlinear_bwd for callers that cannot allocate: NO COUNTERPART IN THE REFERENCE -- added
+ * (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments and
+ * results as fetode_kanlinear_bwd minus `ws`: the scratch is a static device array inside the library,
+ * FETODE_STATIC_WS_FLOATS floats (1 MiB) per GPU that loads the library, held until exit.  Nothing on the call path
+ * allocates (no cudaMalloc / cudaFree / allocating library routine).  Layers with
+ * fetode_kanlinear_bwd_ws_floats(L) > FETODE_STATIC_WS_FLOATS are rejected with FETODE_ETOOLARGE.  Every call shares
+ * the array, which keeps the last call's contents; the call clears what it uses on `stream` first.  Calls that OVERLAP
+ * on the GPU (two streams, two graphs replayed at once) race on it: serialise them. */
+#define FETODE_STATIC_WS_FLOATS 262144
+FETODE_API int64_t fetode_kanlinear_bwd_static_max_floats(void);
+FETODE_API int fetode_kanlinear_bwd_static(const fetode_kanlayer_t* L, const float* wcat, const float* x,
+                         const float* prev, int prev_is_zero, const float* gy,
+                         float* gx /* [B,I] or NULL, overwritten */,
+                         const fetode_kanlayer_grads_t* grads, int64_t B, void* stream);
 /* The same backward split in two for a layer that is applied many times per optimiser step (once per Runge-Kutta
  * stage: 32 times per step in train_ecg_kan_fet_nn_ode.py's RK4 x 8 loop).  _bwd_acc ADDS this call's folded-weight
  * gradient ([I*F, O] then the output-gradient column sums [O]) to ws_acc (fetode_kanlinear_bwd_ws_floats(L) floats,
