@@ -614,11 +614,11 @@ def run_ours(args):
         traffic, traffic_src = None, None
         try:
             import csv
-            prof = os.path.join(ROOT, "profiles", "r2_smallnet_rk2_ncu_full.csv")
+            prof = os.path.join(ROOT, "profiles", "r2_smallnet_rk2_split_ncu_full.csv")
             vals = {r[0]: (r[1], float(r[2])) for r in csv.reader(open(prof)) if len(r) == 3 and r[0].startswith("dram__bytes")}
             scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
             traffic = sum(v * scale[u] for u, v in vals.values())
-            traffic_src = "profiles/r2_smallnet_rk2_ncu_full.csv (dram read+write of one launch at 2^20 rows)"
+            traffic_src = "profiles/r2_smallnet_rk2_split_ncu_full.csv (dram read+write of one launch at 2^20 rows)"
         except Exception:
             pass
         roofline = {
@@ -626,7 +626,7 @@ def run_ours(args):
             "traffic": traffic, "traffic_source": traffic_src,
             "peak_source": "live FFMA probe (fetode_probe_fp32_peak); MEASURED_PEAKS.json holds HBM/bf16 only" if fp32_peak
                            else "fallback 2*128*148*1.965 GHz",
-            "kernel": "smallnet_rk2_kernel<2,10,10,5,FERRO2D,...>", "rows_per_launch": B,
+            "kernel": "smallnet_rk2_kernel<2,10,10,5,FERRO2D,TP=1,64 threads,MINB=10,SPLIT=2>", "rows_per_launch": B,
             "flop_per_traj_step": FLOP_PER_TRAJ_STEP,
             "convention": "MODEL FLOP of SURVEY 8(d) (30 per branch basis, dense 8-coefficient spline); the kernel "
                           "executes fewer (factored exponentials, 4-term cubic): see profiles/ for executed-instruction rates",
