@@ -19,7 +19,7 @@ torch.manual_seed(0)
 if which == "lv":
     model = fetode.KANFET([2, 10, 2], grid_size=5).to(dev)
     opt = fetode.optim.Adam(model.parameters(), lr=2e-3)
-    B, n = 65536, 34
+    B, n = int(os.environ.get("LV_ROWS", "65536")), 34
     t = torch.linspace(0, 3.5, n + 1, dtype=torch.float64)
     x0 = (torch.rand(B, 2) * 6.75 + 0.25).to(dev)
     tgt = torch.randn(n + 1, B, 2).to(dev)
