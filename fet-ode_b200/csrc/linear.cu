@@ -23,45 +23,75 @@ struct GemmArgs {
 };
 
 // C[m,n] (+)= sum_k A[m*sAm + k*sAk] * B[k*sBk + n*sBn] (+ bias[n]);  C row-major [M, N].
-// 32 x 64 tile, 128 threads, 4 x 4 outputs per thread: per k one 128-bit load of four A rows (two addresses per warp:
-// broadcast), one of four B columns, 16 FMA -- 8 FMA per shared-memory instruction (the first version's 2 x 4 tile did
-// 8 per 3 and ran at 3.5 TFLOP/s: 19 us per product under ncu, 7 % of the ECG step).
+// BM x 64 tile (BM = 32 or 16), 128 threads, (BM / 8) x 4 outputs per thread: per k one 128-bit (64-bit) load of the A
+// rows (two addresses per warp: broadcast), one of four B columns, 16 (8) FMA.  The next k-tile's global loads are
+// issued into registers before the current tile's FMAs (the products are one wave of 4-warp CTAs: nothing else hides
+// the load latency); BM = 16 is used while 32-row tiles would leave SMs with a single CTA (the ECG head: 4096 rows).
+template <int BM>
 __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a) {
-    __shared__ __align__(16) float As[LG_BK][LG_BM + 4];
+    constexpr int RPT = BM / 8;                             // rows per thread
+    constexpr int NA = BM * LG_BK / LG_THREADS, NBL = LG_BK * LG_BN / LG_THREADS;
+    __shared__ __align__(16) float As[LG_BK][BM + 4];
     __shared__ __align__(16) float Bs[LG_BK][LG_BN];
     const int tid = threadIdx.x;
-    const long long m0 = (long long)blockIdx.x * LG_BM;
+    const long long m0 = (long long)blockIdx.x * BM;
     const int n0 = blockIdx.y * LG_BN;
     const int k_begin = blockIdx.z * a.k_per_split, k_end = min(a.K, k_begin + a.k_per_split);
-    const int ty = tid / 16, tx = tid % 16;                 // thread -> rows 4 ty .. 4 ty + 3 ; columns 4 tx .. 4 tx + 3
-    float acc[4][4];
+    const int ty = tid / 16, tx = tid % 16;                 // thread -> rows RPT ty .. ; columns 4 tx .. 4 tx + 3
+    float acc[RPT][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < RPT; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
     const bool a_k_fast = a.sAk == 1, b_n_fast = a.sBn == 1;
-    for (int k0 = k_begin; k0 < k_end; k0 += LG_BK) {
-#pragma unroll 4
-        for (int q = tid; q < LG_BM * LG_BK; q += LG_THREADS) {
-            const int kk = a_k_fast ? q % LG_BK : q / LG_BM, mm = a_k_fast ? q / LG_BK : q % LG_BM;
+    float ra[NA], rb[NBL];
+    auto fetch = [&](int k0) {
+#pragma unroll
+        for (int u = 0; u < NA; ++u) {
+            const int q = tid + u * LG_THREADS;
+            const int kk = a_k_fast ? q % LG_BK : q / BM, mm = a_k_fast ? q / LG_BK : q % BM;
             const long long m = m0 + mm;
             const int k = k0 + kk;
-            As[kk][mm] = (m < a.M && k < k_end) ? a.A[m * a.sAm + k * a.sAk] : 0.f;
+            ra[u] = (m < a.M && k < k_end) ? a.A[m * a.sAm + k * a.sAk] : 0.f;
         }
-#pragma unroll 4
-        for (int q = tid; q < LG_BK * LG_BN; q += LG_THREADS) {
+#pragma unroll
+        for (int u = 0; u < NBL; ++u) {
+            const int q = tid + u * LG_THREADS;
             const int nn = b_n_fast ? q % LG_BN : q / LG_BK, kk = b_n_fast ? q / LG_BN : q % LG_BK;
             const int n = n0 + nn, k = k0 + kk;
-            Bs[kk][nn] = (n < a.N && k < k_end) ? a.B[k * a.sBk + n * a.sBn] : 0.f;
+            rb[u] = (n < a.N && k < k_end) ? a.B[k * a.sBk + n * a.sBn] : 0.f;
+        }
+    };
+    if (k_begin < k_end) fetch(k_begin);
+    for (int k0 = k_begin; k0 < k_end; k0 += LG_BK) {
+#pragma unroll
+        for (int u = 0; u < NA; ++u) {
+            const int q = tid + u * LG_THREADS;
+            const int kk = a_k_fast ? q % LG_BK : q / BM, mm = a_k_fast ? q / LG_BK : q % BM;
+            As[kk][mm] = ra[u];
+        }
+#pragma unroll
+        for (int u = 0; u < NBL; ++u) {
+            const int q = tid + u * LG_THREADS;
+            const int nn = b_n_fast ? q % LG_BN : q / LG_BK, kk = b_n_fast ? q / LG_BN : q % LG_BK;
+            Bs[kk][nn ^ ((kk & 15) << 2)] = rb[u];        // 4-column groups swizzled by k: a k-fast B (the forward's W[o, k])
+                                                          // would otherwise store 32 lanes into one bank
         }
         __syncthreads();
+        if (k0 + LG_BK < k_end) fetch(k0 + LG_BK);          // in flight during the FMAs below
 #pragma unroll
         for (int kk = 0; kk < LG_BK; ++kk) {
-            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][4 * tx]);
-            const float4 av = *reinterpret_cast<const float4*>(&As[kk][4 * ty]);
-            const float ar[4] = {av.x, av.y, av.z, av.w};
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][4 * (tx ^ (kk & 15))]);
+            float ar[RPT];
+            if constexpr (RPT == 4) {
+                const float4 av = *reinterpret_cast<const float4*>(&As[kk][4 * ty]);
+                ar[0] = av.x; ar[1] = av.y; ar[2] = av.z; ar[3] = av.w;
+            } else {
+                const float2 av = *reinterpret_cast<const float2*>(&As[kk][2 * ty]);
+                ar[0] = av.x; ar[1] = av.y;
+            }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < RPT; ++i) {
                 acc[i][0] = fmaf(ar[i], b.x, acc[i][0]); acc[i][1] = fmaf(ar[i], b.y, acc[i][1]);
                 acc[i][2] = fmaf(ar[i], b.z, acc[i][2]); acc[i][3] = fmaf(ar[i], b.w, acc[i][3]);
             }
@@ -69,8 +99,8 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
         __syncthreads();
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const long long m = m0 + 4 * ty + i;
+    for (int i = 0; i < RPT; ++i) {
+        const long long m = m0 + RPT * ty + i;
         if (m >= a.M) continue;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -106,10 +136,14 @@ static int small_gemm(const GemmArgs& a0, int splits, cudaStream_t st) {
     splits = std::max(1, std::min(splits, (a.K + LG_BK - 1) / LG_BK));
     a.k_per_split = ((a.K + splits - 1) / splits + LG_BK - 1) / LG_BK * LG_BK;
     splits = (a.K + a.k_per_split - 1) / a.k_per_split;
-    const long long mt = (a.M + LG_BM - 1) / LG_BM;
+    const long long nt = (a.N + LG_BN - 1) / LG_BN;
+    const long long mt32 = (a.M + LG_BM - 1) / LG_BM;
+    const bool half = mt32 * nt * splits < 2 * 148 && a.M > 16;          // 32-row tiles would not give every SM two CTAs
+    const long long mt = half ? (a.M + 15) / 16 : mt32;
     if (mt > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
-    const dim3 grid((unsigned)mt, (unsigned)((a.N + LG_BN - 1) / LG_BN), (unsigned)splits);
-    small_gemm_kernel<<<grid, LG_THREADS, 0, st>>>(a);
+    const dim3 grid((unsigned)mt, (unsigned)nt, (unsigned)splits);
+    if (half) small_gemm_kernel<16><<<grid, LG_THREADS, 0, st>>>(a);
+    else small_gemm_kernel<LG_BM><<<grid, LG_THREADS, 0, st>>>(a);
     return FETODE_LAUNCH_RC();
 }
 
