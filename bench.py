@@ -121,6 +121,25 @@ def cpu_lv_train_ms(model, B, iters=2):
     return 1e3 * (time.perf_counter() - t0) / iters
 
 
+def cpu_lv_dopri5_ms(model, rtol, atol):
+    """fwd+bwd of one LV training iteration with the adaptive solver (oracle port of dopri5, torch autograd) on the host
+    cores, one trajectory (the script's batch); returns (ms, accepted, rejected)."""
+    from oracle import layers as OL
+    from oracle import solvers as OS
+    lay = oracle_layers(model, grad=True)
+    gen = torch.Generator().manual_seed(1)
+    x0 = torch.ones(1, 2)
+    target = torch.randn(35, 1, 2, generator=gen)
+    t = torch.linspace(0, 3.5, 35, dtype=torch.float64)
+    st = {}
+    states = OL.kanfet_states(lay)
+    f = lambda tt, h: OL.kan_forward(h, lay, branch="ferro2d", states=states)
+    t0 = time.perf_counter()
+    pred = OS.odeint(f, x0, t, rtol=rtol, atol=atol, stats=st)
+    ((pred - target) ** 2).mean().backward()
+    return 1e3 * (time.perf_counter() - t0), st.get("accepted"), st.get("rejected")
+
+
 def cpu_ecg_train_ms(model, B):
     """fwd+bwd of one ECG training step (RK4 x 8, cross-entropy) on the host cores, B rows (bounded sample)."""
     import torch.nn.functional as F
@@ -343,14 +362,11 @@ def lv_train_section(ctx, B, fp32_peak, with_cpu):
     return out
 
 
-def lv_dopri5_section(ctx, B, rtol=1e-5, atol=1e-7):
-    """Config 1 with the script's own solver call -- ``odeint(calDeriv, X0, t)`` = torchdiffeq's default dopri5
-    (train_kanfet_node_predprey.py:252).  B <= 12: the accept / reject controller runs inside the kernel
-    (fetode_smallnet_dp5_solve_fwd / _bwd), one launch per 4096 accepted steps; larger batches: one launch per attempted
-    step and one 8-byte read-back (eager either way, not graph-replayed).  Tolerances 1e-5 / 1e-7, not torchdiffeq's default
-    1e-7 / 1e-9: the spline right-hand side is C2 only and the hysteretic gate sees the previous STAGE input, so the
-    embedded error estimate is low-order and the default tolerances mean ~850 000 steps per solve in fp32 on any
-    implementation (profiles/experiments/dopri5_time.py)."""
+def lv_dopri5_section(ctx, B, with_cpu=False, rtol=1e-7, atol=1e-9):
+    """Config 1 with the script's own solver call -- ``odeint(calDeriv, X0, t)`` = torchdiffeq's default dopri5 at its
+    default tolerances rtol 1e-7 / atol 1e-9 (train_kanfet_node_predprey.py:252).  B <= 12: the accept / reject controller
+    runs inside the kernel (fetode_smallnet_dp5_solve_fwd / _bwd), one launch per 4096 accepted steps; larger batches: one
+    launch per attempted step and one 8-byte read-back (eager either way, not graph-replayed)."""
     import fetode
     model = make_model().to(ctx.dev)
     n, T = 34, 3.5
@@ -372,16 +388,19 @@ def lv_dopri5_section(ctx, B, rtol=1e-5, atol=1e-7):
     k = 3
     ms = ctx.timed(it, k, 1, flush=False, grad=True) / k
     att = st.get("accepted", 0) + st.get("rejected", 0)
-    return {"workload": "config 1 with the script's solver call: LV KANFET([2,10,2]) NODE training iteration, adaptive dopri5 "
+    out = {"workload": "config 1 with the script's solver call: LV KANFET([2,10,2]) NODE training iteration, adaptive dopri5 "
                         f"(rtol {rtol:g}, atol {atol:g}), t in [0, {T}] x {n + 1} samples, MSE, fused Adam "
                         "(train_kanfet_node_predprey.py:246-257)",
             "rows_per_gpu": B, "ms_per_step": ms, "graph_replayed": False, "fused_attempt_kernels": bool(st.get("fused")),
             "controller_on_device": bool(st.get("device_controller")),
             "accepted_steps": st.get("accepted"), "rejected_steps": st.get("rejected"),
             "us_per_attempt_fwd_bwd": ms * 1e3 / att if att else None,
-            "other_paths_ms_per_step": {"host_controlled_attempt_launches": 657.4, "staged_per_stage_launches": 19913.5,
-                                        "source": "profiles/r2_dopri5_fused_vs_staged.jsonl (same model, B = 1)"}
-            if B == 1 else None}
+            "other_paths": "profiles/r2_dopri5_fused_vs_staged.jsonl (host-controlled attempt launches, per-stage launches)"}
+    if with_cpu and B == 1:
+        cms, acc, rej = cpu_lv_dopri5_ms(make_model(), rtol, atol)
+        out["cpu"] = {"ms_per_step": cms, "accepted_steps": acc, "rejected_steps": rej, "cores": os.cpu_count(), "kind": "port",
+                      "sample": "one iteration, one trajectory: oracle dopri5 + torch autograd (same weights, same tolerances)"}
+    return out
 
 
 def ecg_train_section(ctx, B, tf32_peak, with_cpu):
@@ -591,7 +610,7 @@ def run_ours(args):
         fwd_bwd = {}
         for name, fn, a in (("lv_train_B1", lv_train_section, (1, fp32_peak, with_cpu)),
                             ("lv_train_B65536", lv_train_section, (65536, fp32_peak, with_cpu)),
-                            ("lv_train_dopri5_B1", lv_dopri5_section, (1,)),
+                            ("lv_train_dopri5_B1", lv_dopri5_section, (1, with_cpu)),
                             ("ecg_train_B4096", ecg_train_section, (4096, tf32_peak, with_cpu)),
                             ("ett_encoder_B4096", ett_encoder_section, (4096, tf32_peak)),
                             ("mnist_train_B1024", mnist_train_section, (1024, fp32_peak))):

@@ -15,7 +15,9 @@ Two groups:
    ``# pip install torchdiffeq``) and NOT installed here, so this part is written from the
    published algorithm (torchdiffeq 0.2.x: fixed-grid euler/midpoint/rk4(3/8-rule) and the
    Dormand-Prince 5(4) adaptive solver with Hairer initial step and 4th-order dense output).
-   PARITY UNPINNED for this group.
+   PARITY UNPINNED for this group, with one independent anchor: the Dormand-Prince tableau equals
+   scipy.integrate's RK45 tables and the embedded-error / mid-point weights satisfy their order
+   conditions (tests/test_oracle_dopri5_scipy.py); the controller details remain restated.
 """
 from __future__ import annotations
 
@@ -106,7 +108,7 @@ _DP_BETA = [
 ]
 _DP_CSOL = [35 / 384, 0, 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84, 0]
 _DP_CERR = [
-    35 / 384 - 1951 / 21600, 0, 500 / 1113 - 22642 / 50715, 125 / 192 - 451 / 720,
+    35 / 384 - 1951 / 21600, 0, 500 / 1113 - 22642 / 50085, 125 / 192 - 451 / 720,
     -2187 / 6784 - -12231 / 42400, 11 / 84 - 649 / 6300, -1.0 / 60.0,
 ]
 _DP_CMID = [

@@ -1,11 +1,8 @@
-"""LV training iteration with torchdiffeq's default METHOD (dopri5: the call of train_kanfet_node_predprey.py:252) --
-fused attempt kernels vs the staged path, fwd+bwd+Adam, wall-clock per iteration (the adaptive loop reads one double
-back per attempt, so the step is not graph-capturable).  Tolerances: rtol 1e-5 / atol 1e-7 by default.  With
-torchdiffeq's default 1e-7 / 1e-9 the hysteretic right-hand side (the gate sees the previous STAGE input, so the
-embedded error estimate is O(dt^2), not O(dt^5)) drives the controller to ~850 000 accepted steps for t in [0, 3.5] in
-fp32 -- measured here once: 72 s per iteration fused, 85 us per attempt fwd+bwd; the reference's controller sees the
-same right-hand side.
-usage: python profiles/experiments/dopri5_time.py [B ...]   (env RTOL / ATOL / BRANCH=KAN|KANFET)"""
+"""LV training iteration with torchdiffeq's default METHOD and tolerances (dopri5, rtol 1e-7 / atol 1e-9: the call of
+train_kanfet_node_predprey.py:252) -- fused attempt kernels vs the staged path, fwd+bwd+Adam, wall-clock per iteration
+(the adaptive loop reads the controller state back, so the step is not graph-capturable).
+usage: python profiles/experiments/dopri5_time.py [B ...]   (env RTOL / ATOL / BRANCH=KAN|KANFET / ONLY=fused /
+FETODE_DOPRI5_DEVICE=0 for host-controlled attempt launches)"""
 import json
 import os
 import sys
@@ -22,7 +19,7 @@ def run(B, fused, iters=5):
     torch.manual_seed(0)
     dev = torch.device("cuda:0")
     m = getattr(fetode, os.environ.get("BRANCH", "KANFET"))([2, 10, 2]).to(dev)
-    rtol, atol = float(os.environ.get("RTOL", "1e-5")), float(os.environ.get("ATOL", "1e-7"))
+    rtol, atol = float(os.environ.get("RTOL", "1e-7")), float(os.environ.get("ATOL", "1e-9"))
     t = torch.linspace(0, 3.5, 35, dtype=torch.float64)
     x0 = torch.ones(B, 2, device=dev) if B == 1 else (torch.rand(B, 2, device=dev) * 6.75 + 0.25)
     tgt = torch.randn(35, B, 2, device=dev)
@@ -44,7 +41,7 @@ def run(B, fused, iters=5):
         it()
     torch.cuda.synchronize()
     ms = (time.perf_counter() - t0) / iters * 1e3
-    return {"B": B, "model": type(m).__name__, "rtol": rtol, "atol": atol, "fused": fused, "ms_per_iteration": ms, "accepted": st.get("accepted"), "rejected": st.get("rejected")}
+    return {"B": B, "device_controller": bool(st.get("device_controller")), "model": type(m).__name__, "rtol": rtol, "atol": atol, "fused": fused, "ms_per_iteration": ms, "accepted": st.get("accepted"), "rejected": st.get("rejected")}
 
 
 if __name__ == "__main__":

@@ -149,26 +149,26 @@ def test_device_controller_equals_host_controller(cuda, branch, monkeypatch):
 
 
 def test_device_controller_resumes_across_launches(cuda, monkeypatch):
-    """Checkpoint chunks of 7 accepted steps and 5 attempts per launch: the solve is re-launched many times and must
+    """Checkpoint chunks of 3 accepted steps and 2 attempts per launch: the solve is re-launched many times and must
     give what one launch gives (the controller state travels in ctrl[8], the adjoint carries in carry_y / carry_k)."""
     from fetode import dopri5
     layers, m = fetode_kan_random([2, 10, 2], "ferro2d", seed=43, device=cuda)
     x0 = lv_inputs(12, 2)
-    t = torch.linspace(0, 0.5, 6, dtype=torch.float64)
+    t = torch.linspace(0, 1.0, 6, dtype=torch.float64)
     res = []
-    for chunk, attempts in ((4096, 1 << 16), (7, 5)):
+    for chunk, attempts in ((4096, 1 << 16), (3, 2)):
         monkeypatch.setattr(dopri5._FusedSolve, "CHUNK", chunk)
         monkeypatch.setattr(dopri5._FusedSolve, "ATTEMPTS", attempts)
         m.zero_grad()
         m.reset_state()
         st = {}
         xg = x0.to(cuda).requires_grad_(True)
-        out = fetode.odeint(lambda tt, X: m(X), xg, t, rtol=1e-5, atol=1e-7, options={"stats": st})
+        out = fetode.odeint(lambda tt, X: m(X), xg, t, rtol=1e-7, atol=1e-9, options={"stats": st})
         assert st.get("device_controller") is True
         (out * torch.arange(1, 7, device=cuda).view(6, 1, 1)).sum().backward()
         res.append((out.detach(), xg.grad.clone(), {n: p.grad.clone() for n, p in m.named_parameters()}, st))
     a, b = res
-    assert a[3] == b[3] and a[3]["accepted"] > 14
+    assert a[3] == b[3] and a[3]["accepted"] >= 10, a[3]
     assert torch.equal(a[0], b[0])
     assert max_rel(a[1], b[1]) < 1e-5
     for n in a[2]:

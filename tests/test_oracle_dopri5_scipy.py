@@ -1,0 +1,90 @@
+"""Partial pin of the adaptive-solver restatement (a12, torchdiffeq dopri5: absent third-party dependency, PARITY UNPINNED
+for the controller details).  What CAN be anchored on an independent implementation in this image:
+
+  * the Dormand-Prince tableau (nodes, stage matrix, 5th-order weights) of oracle/solvers.py AND of the product's host
+    controller fetode/dopri5.py equals scipy.integrate's RK45 tables (scipy 1.x, `scipy/integrate/_ivp/rk.py`);
+  * the embedded error weights and the dense-output mid-point weights -- torchdiffeq uses Shampine's variant, which is
+    NOT scipy's, so these are pinned by the order conditions they must satisfy (a 4th-order companion: E = b - b* kills
+    polynomials up to degree 3 and not degree 4; y_mid is the solution at t + h/2 to 4th order);
+  * the solver as a whole: same smooth problem, oracle dopri5 vs scipy RK45 at tight tolerances, both against the
+    closed-form solution.
+The CUDA tables (csrc/smallnet_wide.cu snw_dp5_tableau) are checked against the host controller on the GPU
+(tests/test_dopri5_fused_gpu.py)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+from scipy.integrate import solve_ivp
+from scipy.integrate._ivp.rk import RK45
+
+from oracle import solvers as OS
+
+
+def _tables(kind):
+    if kind == "oracle":
+        return OS._DP_ALPHA, OS._DP_BETA, OS._DP_CERR, OS._DP_CMID
+    from fetode import dopri5 as D                       # host-side tables only: nothing here touches the GPU library
+    return D._ALPHA, D._BETA, D._C_ERR, D._C_MID
+
+
+@pytest.mark.parametrize("kind", ["oracle", "product"])
+def test_tableau_equals_scipy_rk45(kind):
+    alpha, beta, _cerr, _cmid = _tables(kind)
+    assert np.allclose(np.array(alpha[:5], dtype=np.float64), RK45.C[1:], rtol=0, atol=1e-16)
+    assert alpha[5] == 1.0
+    for s in range(5):                                   # stage rows 1..5 of scipy's A
+        assert np.allclose(np.array(beta[s], dtype=np.float64), RK45.A[s + 1, :s + 1], rtol=0, atol=1e-15), s
+        assert math.isclose(sum(beta[s]), alpha[s], rel_tol=0, abs_tol=1e-15)      # row-sum condition
+    assert np.allclose(np.array(beta[5], dtype=np.float64), RK45.B, rtol=0, atol=1e-16)   # FSAL: last row == weights
+
+
+@pytest.mark.parametrize("kind", ["oracle", "product"])
+def test_error_and_midpoint_weights_satisfy_their_order_conditions(kind):
+    alpha, beta, cerr, cmid = _tables(kind)
+    c = np.array([0.0] + list(alpha), dtype=np.float64)                  # nodes of the 7 stages
+    A = np.zeros((7, 7))
+    for s in range(6):
+        A[s + 1, :s + 1] = beta[s]
+    E = np.array(cerr, dtype=np.float64)
+    b = np.array(list(beta[5]) + [0.0], dtype=np.float64)
+    bstar = b - E                                                        # the embedded 4th-order weights
+    # quadrature conditions up to order 4, tree conditions of order 3 and 4
+    for w, order in ((b, 5), (bstar, 4)):
+        for q in range(order):
+            assert abs(w @ c ** q - 1.0 / (q + 1)) < 1e-14, (order, q)
+        assert abs(w @ (A @ c) - 1.0 / 6) < 1e-14
+        assert abs(w @ (A @ c ** 2) - 1.0 / 12) < 1e-14
+        assert abs((w * c) @ (A @ c) - 1.0 / 8) < 1e-14
+        assert abs(w @ (A @ (A @ c)) - 1.0 / 24) < 1e-14
+    assert abs(bstar @ c ** 4 - 1.0 / 5) > 1e-4                          # ... and the companion is NOT 5th order
+    assert abs(E.sum()) < 1e-15
+    # Shampine's companion as torchdiffeq writes it
+    assert np.allclose(bstar, [1951 / 21600, 0, 22642 / 50085, 451 / 720, -12231 / 42400, 649 / 6300, 1 / 60], atol=1e-15)
+    # dense output: y_mid = y + h sum_i cmid_i k_i is the solution at t + h/2 to 4th order
+    m = np.array(cmid, dtype=np.float64)
+    for q in range(4):
+        assert abs(m @ c ** q - 0.5 ** (q + 1) / (q + 1)) < 1e-12, q
+    assert abs(m @ (A @ c) - 0.5 ** 3 / 6) < 1e-12
+
+
+def test_oracle_dopri5_and_scipy_rk45_agree_on_a_smooth_problem():
+    """y' = [[-0.5, 2], [-2, -0.5]] y: a damped rotation with a closed form.  Not a step-for-step comparison (the two
+    controllers differ in their embedded pair and rejection rule) -- both must sit within their tolerance of the truth,
+    and take a comparable number of steps."""
+    M = torch.tensor([[-0.5, 2.0], [-2.0, -0.5]], dtype=torch.float64)
+    f = lambda t, y: y @ M.T
+    y0 = torch.tensor([[1.0, 0.5]], dtype=torch.float64)
+    t = torch.linspace(0, 3.0, 13, dtype=torch.float64)
+    stats = {}
+    got = OS.odeint(f, y0, t, rtol=1e-8, atol=1e-10, stats=stats)[:, 0, :].numpy()
+    ref = solve_ivp(lambda tt, y: M.numpy() @ y, (0.0, 3.0), y0[0].numpy(), method="RK45", t_eval=t.numpy(), rtol=1e-8,
+                    atol=1e-10)
+    tt = t.numpy()
+    rot = np.stack([np.cos(2 * tt) * 1.0 + np.sin(2 * tt) * 0.5, -np.sin(2 * tt) * 1.0 + np.cos(2 * tt) * 0.5], 1)
+    truth = np.exp(-0.5 * tt)[:, None] * rot
+    assert np.abs(got - truth).max() < 5e-8
+    assert np.abs(ref.y.T - truth).max() < 5e-7
+    assert np.abs(got - ref.y.T).max() < 5e-7
+    n_scipy = ref.nfev // 6
+    assert 0.5 * n_scipy <= stats["accepted"] + stats["rejected"] <= 2.0 * n_scipy
