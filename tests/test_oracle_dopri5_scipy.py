@@ -88,3 +88,23 @@ def test_oracle_dopri5_and_scipy_rk45_agree_on_a_smooth_problem():
     assert np.abs(got - ref.y.T).max() < 5e-7
     n_scipy = ref.nfev // 6
     assert 0.5 * n_scipy <= stats["accepted"] + stats["rejected"] <= 2.0 * n_scipy
+
+
+@pytest.mark.parametrize("method,order", [("euler", 1), ("midpoint", 2), ("rk4", 4), ("rk4_classic", 4)])
+def test_fixed_grid_restatements_converge_at_their_order(method, order):
+    """torchdiffeq's fixed-grid solvers are restated too ("rk4" = the 3/8 rule); an independent property each must have:
+    halving the step divides the global error by 2^order on a smooth problem with a closed form."""
+    M = torch.tensor([[-0.5, 2.0], [-2.0, -0.5]], dtype=torch.float64)
+    f = lambda t, y: y @ M.T
+    y0 = torch.tensor([[1.0, 0.5]], dtype=torch.float64)
+    T = 1.0
+    truth = math.exp(-0.5 * T) * np.array([math.cos(2 * T) + 0.5 * math.sin(2 * T), -math.sin(2 * T) + 0.5 * math.cos(2 * T)])
+    errs = []
+    for n in (16, 32):
+        if method == "rk4_classic":
+            y = OS.rk4_classic(f, y0, 0.0, T, n)
+        else:
+            y = OS.odeint(f, y0, torch.linspace(0, T, n + 1, dtype=torch.float64), method=method)[-1]
+        errs.append(np.abs(y[0].numpy() - truth).max())
+    rate = math.log2(errs[0] / errs[1])
+    assert abs(rate - order) < 0.25, (errs, rate)
