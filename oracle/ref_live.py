@@ -116,6 +116,7 @@ def script_module(name: str):
     train_ecg, mnist_kuramoto_kan, ...) with the extra stubs it needs."""
     if name in _cache:
         return _cache[name]
+    _install_stubs()                                    # another test may have removed a stub since the first call
     ek = efficientkan()
     ferro_class()
     if "kan_diffusion" not in sys.modules:
