@@ -20,14 +20,27 @@ struct GemmArgs {
     long long M, sAm, sAk, sBk, sBn;
     int N, K, k_per_split;
     int accumulate;          // C += (the weight-gradient buffer is shared by every call of a step), never overwritten
+    // fused head (fetode_head_fwd / _bwd): dh = gain * (silu(z) W^T + b)
+    int a_silu, b_silu;      // the A / B operand is silu(stored value)
+    const float* scale;      // device scalar multiplying the result (the gain), or null
+    const float* emul;       // [M, N]: the result is also multiplied by silu'(emul[m, n]), or null
+    float* C2;               // [M, N]: receives the UNSCALED result (before scale / emul), or null
 };
+
+__device__ __forceinline__ float lg_silu(float x) { return x / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float lg_dsilu(float x) {
+    const float s = 1.0f / (1.0f + __expf(-x));
+    return s * fmaf(x, 1.0f - s, 1.0f);
+}
 
 // C[m,n] (+)= sum_k A[m*sAm + k*sAk] * B[k*sBk + n*sBn] (+ bias[n]);  C row-major [M, N].
 // BM x 64 tile (BM = 32 or 16), 128 threads, (BM / 8) x 4 outputs per thread: per k one 128-bit (64-bit) load of the A
 // rows (two addresses per warp: broadcast), one of four B columns, 16 (8) FMA.  The next k-tile's global loads are
 // issued into registers before the current tile's FMAs (the products are one wave of 4-warp CTAs: nothing else hides
 // the load latency); BM = 16 is used while 32-row tiles would leave SMs with a single CTA (the ECG head: 4096 rows).
-template <int BM>
+// HEAD = true compiles the fused-head prologues / epilogues in (a_silu, b_silu, scale, emul, C2); the plain products keep
+// their own lean instantiation.
+template <int BM, bool HEAD>
 __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a) {
     constexpr int RPT = BM / 8;                             // rows per thread
     constexpr int NA = BM * LG_BK / LG_THREADS, NBL = LG_BK * LG_BN / LG_THREADS;
@@ -53,6 +66,7 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
             const long long m = m0 + mm;
             const int k = k0 + kk;
             ra[u] = (m < a.M && k < k_end) ? a.A[m * a.sAm + k * a.sAk] : 0.f;
+            if (HEAD && a.a_silu) ra[u] = lg_silu(ra[u]);
         }
 #pragma unroll
         for (int u = 0; u < NBL; ++u) {
@@ -60,6 +74,7 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
             const int nn = b_n_fast ? q % LG_BN : q / LG_BK, kk = b_n_fast ? q / LG_BN : q % LG_BK;
             const int n = n0 + nn, k = k0 + kk;
             rb[u] = (n < a.N && k < k_end) ? a.B[k * a.sBk + n * a.sBn] : 0.f;
+            if (HEAD && a.b_silu) rb[u] = lg_silu(rb[u]);
         }
     };
     if (k_begin < k_end) fetch(k_begin);
@@ -98,6 +113,7 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
         }
         __syncthreads();
     }
+    const float gain = (HEAD && a.scale) ? *a.scale : 1.0f;
 #pragma unroll
     for (int i = 0; i < RPT; ++i) {
         const long long m = m0 + RPT * ty + i;
@@ -108,26 +124,48 @@ __global__ void __launch_bounds__(LG_THREADS) small_gemm_kernel(const GemmArgs a
             if (n >= a.N) continue;
             float v = acc[i][j];
             if (a.bias && blockIdx.z == 0) v += a.bias[n];
+            if constexpr (HEAD) {
+                if (a.C2) a.C2[m * a.N + n] = v;
+                if (a.scale) v *= gain;
+                if (a.emul) v *= lg_dsilu(a.emul[m * a.N + n]);
+            }
             if (gridDim.z == 1 && !a.accumulate) a.C[m * a.N + n] = v;
             else atomicAdd(a.C + m * a.N + n, v);
         }
     }
 }
 
-// gb[o] += sum_b gy[b,o]
-__global__ void __launch_bounds__(256) colsum_acc_kernel(const float* gy, float* gb, long long B, int O) {
+// gb[o] += scale * sum_b gy[b,o];  optionally *gdot += sum_{b,o} gy[b,o] u[b,o]  (the gain's gradient in the fused head)
+__global__ void __launch_bounds__(256) colsum_acc_kernel(const float* gy, float* gb, long long B, int O, const float* scale,
+                                                         const float* u, float* gdot) {
     const int o = blockIdx.x * 32 + (threadIdx.x & 31);
     const int w = threadIdx.x >> 5;
-    float acc = 0.f;
+    float acc = 0.f, dot = 0.f;
     if (o < O)
-        for (long long b = (long long)blockIdx.y * 8 + w; b < B; b += (long long)gridDim.y * 8) acc += gy[b * O + o];
+        for (long long b = (long long)blockIdx.y * 8 + w; b < B; b += (long long)gridDim.y * 8) {
+            const float g = gy[b * O + o];
+            acc += g;
+            if (u) dot = fmaf(g, u[b * O + o], dot);
+        }
     __shared__ float part[8][33];
     part[w][threadIdx.x & 31] = acc;
     __syncthreads();
-    if (w == 0 && o < O) {
+    if (w == 0 && o < O && gb) {
         float s = 0.f;
         for (int k = 0; k < 8; ++k) s += part[k][threadIdx.x];
-        atomicAdd(gb + o, s);
+        atomicAdd(gb + o, scale ? s * *scale : s);
+    }
+    if (gdot) {                                           // uniform over the grid
+        __syncthreads();
+        part[w][threadIdx.x & 31] = dot;
+        __syncthreads();
+        if (w == 0) {
+            float s = 0.f;
+            for (int k = 0; k < 8; ++k) s += part[k][threadIdx.x];
+#pragma unroll
+            for (int q = 16; q > 0; q >>= 1) s += __shfl_xor_sync(0xffffffffu, s, q);
+            if (threadIdx.x == 0 && s != 0.f) atomicAdd(gdot, s);
+        }
     }
 }
 
@@ -142,8 +180,14 @@ static int small_gemm(const GemmArgs& a0, int splits, cudaStream_t st) {
     const long long mt = half ? (a.M + 15) / 16 : mt32;
     if (mt > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
     const dim3 grid((unsigned)mt, (unsigned)nt, (unsigned)splits);
-    if (half) small_gemm_kernel<16><<<grid, LG_THREADS, 0, st>>>(a);
-    else small_gemm_kernel<LG_BM><<<grid, LG_THREADS, 0, st>>>(a);
+    const bool head = a.a_silu || a.b_silu || a.scale || a.emul || a.C2;
+    if (head) {
+        if (half) small_gemm_kernel<16, true><<<grid, LG_THREADS, 0, st>>>(a);
+        else small_gemm_kernel<LG_BM, true><<<grid, LG_THREADS, 0, st>>>(a);
+    } else {
+        if (half) small_gemm_kernel<16, false><<<grid, LG_THREADS, 0, st>>>(a);
+        else small_gemm_kernel<LG_BM, false><<<grid, LG_THREADS, 0, st>>>(a);
+    }
     return FETODE_LAUNCH_RC();
 }
 
@@ -190,7 +234,59 @@ extern "C" int fetode_linear_bwd(const float* x, const float* weight, const floa
     }
     if (gbias) {
         const long long by = std::max(1LL, std::min<long long>((B + 63) / 64, 64));
-        colsum_acc_kernel<<<dim3((out_features + 31) / 32, (unsigned)by), 256, 0, st>>>(gy, gbias, B, out_features);
+        colsum_acc_kernel<<<dim3((out_features + 31) / 32, (unsigned)by), 256, 0, st>>>(gy, gbias, B, out_features, nullptr, nullptr,
+                                                                                  nullptr);
+    }
+    return FETODE_LAUNCH_RC();
+}
+
+// ---- fused tail of the ECG right-hand side: dh = gain * (silu(z) W^T + b) ------------------------------------------------
+// Replaces  z = self.act(z); dh = self.out(z); dh = self.scale * alpha * dh  (train_ecg_kan_fet_nn_ode.py:471-480, act =
+// nn.SiLU, alpha = softplus(log_alpha)) and its autograd: SiLU is the A-operand prologue of the product, the gain its
+// epilogue; in the reverse sweep silu' is the epilogue of the input-gradient product, SiLU the B-operand prologue of the
+// weight-gradient product, and the gain's gradient sum(gy * u) rides on the bias-gradient column sum.
+extern "C" int fetode_head_fwd(const float* z, const float* weight, const float* bias, const float* gain, float* u, float* y,
+                               int64_t B, int32_t in_features, int32_t out_features, void* stream) {
+    FETODE_CHECK_ARG(z && weight && gain && y && B >= 0 && in_features >= 1 && out_features >= 1);
+    if (B == 0) return FETODE_OK;
+    GemmArgs a{};
+    a.A = z; a.sAm = in_features; a.sAk = 1; a.a_silu = 1;
+    a.B = weight; a.sBk = 1; a.sBn = in_features;
+    a.bias = bias; a.C = y; a.C2 = u; a.scale = gain; a.M = B; a.N = out_features; a.K = in_features;
+    return small_gemm(a, 1, (cudaStream_t)stream);
+}
+
+extern "C" int fetode_head_bwd(const float* z, const float* weight, const float* gain, const float* u, const float* gy,
+                               float* gz, float* gweight, float* gbias, float* ggain, int64_t B, int32_t in_features,
+                               int32_t out_features, void* stream) {
+    FETODE_CHECK_ARG(z && weight && gain && gy && B >= 0 && in_features >= 1 && out_features >= 1 && (!ggain || u));
+    if (B == 0) return FETODE_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (gz) {                                               // gz[b, k] = gain * (sum_o gy[b, o] W[o, k]) * silu'(z[b, k])
+        GemmArgs a{};
+        a.A = gy; a.sAm = out_features; a.sAk = 1;
+        a.B = weight; a.sBk = in_features; a.sBn = 1;
+        a.C = gz; a.scale = gain; a.emul = z; a.M = B; a.N = in_features; a.K = out_features;
+        const int rc = small_gemm(a, 1, st);
+        if (rc) return rc;
+    }
+    if (gweight) {                                          // gW[o, k] += gain * sum_b gy[b, o] silu(z[b, k])
+        if (B > 0x7fffffffLL) return FETODE_EUNSUPPORTED;
+        GemmArgs a{};
+        a.A = gy; a.sAm = 1; a.sAk = out_features;
+        a.B = z; a.sBk = in_features; a.sBn = 1; a.b_silu = 1;
+        a.C = gweight; a.scale = gain; a.M = out_features; a.N = in_features; a.K = (int)B;
+        a.accumulate = 1;
+        const long long tiles = ((out_features + LG_BM - 1) / LG_BM) * (long long)((in_features + LG_BN - 1) / LG_BN);
+        int splits = (int)std::max(1LL, std::min<long long>(148LL * 2 / tiles, (B + 127) / 128));
+        if (splits < 2) splits = 2;
+        const int rc = small_gemm(a, splits, st);
+        if (rc) return rc;
+    }
+    if (gbias || ggain) {
+        const long long by = std::max(1LL, std::min<long long>((B + 63) / 64, 64));
+        colsum_acc_kernel<<<dim3((out_features + 31) / 32, (unsigned)by), 256, 0, st>>>(gy, gbias, B, out_features, gain,
+                                                                                  ggain ? u : nullptr, ggain);
     }
     return FETODE_LAUNCH_RC();
 }

@@ -167,9 +167,10 @@ class MLPKANODEFunc(nn.Module):
         h = ops.ln_tanh(h, self.ln, self.h_bound)           # LayerNorm + h_bound * tanh(h / h_bound) :459-461, one kernel
         phi = self.h_feat(h, nan_to_num=True)                # sigmoid + nan_to_num fused into the neuron kernel :464-465
         z = self.act(self.kan1(phi))
-        z = self.act(self.kan2(z))
-        dh = ops.linear(z, self.out)                         # nn.Linear(hidden, latent) :475, fp32 FMA kernel
-        return self._gain() * dh
+        z = self.kan2(z)
+        # act -> nn.Linear(hidden, latent) -> scale * softplus(log_alpha) (:471-480) as one product: SiLU is its
+        # operand prologue, the gain its epilogue
+        return ops.head(z, self.act, self.out, self._gain())
 
 
 class No_MLP_KANODEFunc(nn.Module):

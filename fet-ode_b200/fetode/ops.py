@@ -519,6 +519,58 @@ def linear(x: torch.Tensor, lin: torch.nn.Linear) -> torch.Tensor:
     return lin(x)
 
 
+class HeadFn(torch.autograd.Function):
+    """dh = gain * (silu(z) W^T + b): the tail of MLPKANODEFunc.forward (train_ecg_kan_fet_nn_ode.py:471-480) as one
+    launch (csrc/linear.cu fetode_head_fwd); backward = three launches, the gradients of (W, b, gain) accumulate in the
+    ParamGroup buffer behind ``handle``."""
+
+    @staticmethod
+    def forward(ctx, z, weight, bias, gain, handle=None):
+        B, K = z.shape
+        O = weight.shape[0]
+        y = torch.empty(B, O, dtype=torch.float32, device=z.device)
+        u = torch.empty(B, O, dtype=torch.float32, device=z.device) if handle is not None else None
+        w, b, g = f32c(weight.detach()), f32c(bias.detach()), f32c(gain.detach()).reshape(1)
+        check(lib().fetode_head_fwd(ptr(z), ptr(w), ptr(b), ptr(g), ptr(u), ptr(y), C.c_int64(B), C.c_int32(K),
+                                    C.c_int32(O), stream()), "head_fwd")
+        if handle is not None:
+            ctx.save_for_backward(z, w, g, u)
+        ctx.handle = handle
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        z, w, g, u = ctx.saved_tensors
+        B, K = z.shape
+        O = w.shape[0]
+        gy = f32c(gy)
+        gz = torch.empty_like(z) if ctx.needs_input_grad[0] else None
+        (gw, gb, gg), acc, first = group_grad_views(ctx.handle, z.device)
+        check(lib().fetode_head_bwd(ptr(z), ptr(w), ptr(g), ptr(u), ptr(gy), ptr(gz), ptr(gw), ptr(gb), ptr(gg.reshape(1)),
+                                    C.c_int64(B), C.c_int32(K), C.c_int32(O), stream()), "head_bwd")
+        return gz, None, None, None, (acc if first else None)
+
+
+def head(z: torch.Tensor, act, lin: torch.nn.Linear, gain: torch.Tensor) -> torch.Tensor:
+    """gain * lin(act(z)) -- fused when act is SiLU, the input a CUDA fp32 [B, in] tensor, the layer has a bias and either
+    nothing or every one of (weight, bias, gain) requires a gradient; otherwise the three steps separately."""
+    _require_cuda(z, "input")
+    if (isinstance(act, torch.nn.SiLU) and z.is_cuda and z.dim() == 2 and z.dtype == torch.float32
+            and lin.weight.dtype == torch.float32 and lin.bias is not None and gain.numel() == 1
+            and gain.dtype == torch.float32):
+        params = [lin.weight, lin.bias, gain]
+        if not torch.is_grad_enabled() or not (z.requires_grad or any(p.requires_grad for p in params)):
+            return HeadFn.apply(f32c(z), lin.weight, lin.bias, gain, None)
+        if all(p.requires_grad for p in params):
+            grp = lin.__dict__.get("_fetode_hgroup")
+            if grp is None:
+                grp = lin.__dict__["_fetode_hgroup"] = ParamGroup()
+            h = grp.handle(params)
+            if h is not None:
+                return HeadFn.apply(f32c(z), lin.weight.detach(), lin.bias.detach(), gain.detach(), h)
+    return gain * linear(act(z), lin)
+
+
 # --------------------------------------------------------------------------------------
 # fused small-width network + Runge-Kutta loop
 # --------------------------------------------------------------------------------------

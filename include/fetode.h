@@ -156,6 +156,18 @@ FETODE_API int fetode_linear_fwd(const float* x, const float* weight, const floa
                       int32_t in_features, int32_t out_features, void* stream);
 FETODE_API int fetode_linear_bwd(const float* x, const float* weight, const float* gy, float* gx, float* gweight,
                       float* gbias, int64_t B, int32_t in_features, int32_t out_features, void* stream);
+/* The tail of the ECG right-hand side as one product:  dh = gain * (silu(z) W^T + b)
+ * Replaces  z = self.act(z); dh = self.out(z); dh = self.scale * alpha * dh  (train_ecg_kan_fet_nn_ode.py:471-480; act =
+ * nn.SiLU, alpha = softplus(log_alpha)) and its autograd.  gain: DEVICE scalar (scale * alpha, formed by the caller:
+ * its own autograd stays with the caller).  z [B, in], weight [out, in], bias [out] or NULL, y [B, out];
+ * u [B, out] (or NULL) receives the unscaled product, which _bwd needs for the gain's gradient.
+ * _bwd: gz [B, in] overwritten (or NULL); gweight [out, in], gbias [out], ggain [1] are ADDED to (caller zeroes; any may
+ * be NULL; ggain needs u). */
+FETODE_API int fetode_head_fwd(const float* z, const float* weight, const float* bias, const float* gain, float* u,
+                       float* y, int64_t B, int32_t in_features, int32_t out_features, void* stream);
+FETODE_API int fetode_head_bwd(const float* z, const float* weight, const float* gain, const float* u, const float* gy,
+                       float* gz, float* gweight, float* gbias, float* ggain, int64_t B, int32_t in_features,
+                       int32_t out_features, void* stream);
 
 /* B-spline basis values alone: KANLinear.b_splines efficientkan.py:117-131 (used by update_grid :184-221 and
  * curve2coeff :133-143 on CUDA inputs).  grid [I, G+2k+1], x [B,I] -> out [B, I, G+k]; spline_order must be 3. */

@@ -101,3 +101,41 @@ def test_shared_gradient_accumulators_over_repeated_calls(cuda, B):
     want2.backward()
     for (n, p), q in zip(lin.named_parameters(), ref_lin.parameters()):
         assert max_rel(p.grad, q.grad) < 2e-4, n
+
+
+@pytest.mark.parametrize("B,K,O", [(1, 128, 64), (26, 128, 64), (300, 40, 7), (4096, 128, 64)])
+def test_fused_head_matches_the_three_torch_steps(cuda, B, K, O):
+    """ops.head = gain * lin(silu(z)) (train_ecg_kan_fet_nn_ode.py:471-480) against torch in fp64, called THREE times in
+    one graph with a shared gain node (as once per Runge-Kutta stage): value, input gradient and the accumulated
+    gradients of weight, bias and of the two scalars behind the gain."""
+    import torch.nn.functional as F
+    gen = torch.Generator().manual_seed(B + K)
+    lin = torch.nn.Linear(K, O).to(cuda)
+    scale = torch.nn.Parameter(torch.tensor(1.3, device=cuda))
+    log_alpha = torch.nn.Parameter(torch.tensor(-1.0, device=cuda))
+    zs = [(torch.randn(B, K, generator=gen) * 2).to(cuda) for _ in range(3)]
+    ws = [torch.randn(B, O, generator=gen).to(cuda) for _ in range(3)]
+    act = torch.nn.SiLU()
+
+    zi = [z.clone().requires_grad_(True) for z in zs]
+    gain = scale * F.softplus(log_alpha)
+    outs = [ops.head(z, act, lin, gain) for z in zi]
+    sum((o * w).sum() for o, w in zip(outs, ws)).backward()
+    got = ([o.detach() for o in outs], [z.grad for z in zi], lin.weight.grad.clone(), lin.bias.grad.clone(),
+           scale.grad.clone(), log_alpha.grad.clone())
+
+    W, b = lin.weight.detach().double().requires_grad_(True), lin.bias.detach().double().requires_grad_(True)
+    s64, a64 = scale.detach().double().requires_grad_(True), log_alpha.detach().double().requires_grad_(True)
+    z64 = [z.double().requires_grad_(True) for z in zs]
+    g64 = s64 * F.softplus(a64)
+    o64 = [g64 * F.linear(F.silu(z), W, b) for z in z64]
+    sum((o * w.double()).sum() for o, w in zip(o64, ws)).backward()
+    for i in range(3):
+        assert max_rel(got[0][i], o64[i]) < 2e-6, i
+        assert max_rel(got[1][i], z64[i].grad) < 5e-6, i
+    assert max_rel(got[2], W.grad) < 2e-5
+    assert max_rel(got[3], b.grad) < 2e-5
+    assert max_rel(got[4], s64.grad) < 2e-5
+    assert max_rel(got[5], a64.grad) < 2e-5
+    with torch.no_grad():                                    # inference path: no saved buffers, same values
+        assert max_rel(ops.head(zs[0], act, lin, scale * F.softplus(log_alpha)), o64[0]) < 2e-6
