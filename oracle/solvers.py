@@ -214,6 +214,8 @@ def _dopri5(f: Rhs, y0: Tensor, t: Tensor, rtol: float, atol: float, max_steps=2
 
     f0 = f(t[0], y0)
     dt = initial_step(t[0], f0)
+    if stats is not None:
+        stats["first_step"] = float(dt)
     y, fy, ta, tb, coef = y0, f0, t[0], t[0], [y0] * 5
     sol, n_acc, n_rej = [y0], 0, 0
     for i in range(1, t.shape[0]):

@@ -108,3 +108,19 @@ def test_fixed_grid_restatements_converge_at_their_order(method, order):
         errs.append(np.abs(y[0].numpy() - truth).max())
     rate = math.log2(errs[0] / errs[1])
     assert abs(rate - order) < 0.25, (errs, rate)
+
+
+@pytest.mark.parametrize("rtol,atol", [(1e-7, 1e-9), (1e-3, 1e-6)])
+def test_initial_step_equals_scipy_select_initial_step(rtol, atol):
+    """Hairer-Norsett-Wanner II.4 starting step, as torchdiffeq (_select_initial_step, order 4 -> exponent 1/5) and scipy
+    (select_initial_step with the error-estimator order 4) both implement it: same number on the same problem."""
+    from scipy.integrate._ivp.common import select_initial_step
+    M = torch.tensor([[-0.5, 2.0], [-2.0, -0.5]], dtype=torch.float64)
+    y0 = torch.tensor([[1.0, 0.5]], dtype=torch.float64)
+    st = {}
+    OS.odeint(lambda t, y: torch.tanh(y) @ M.T, y0, torch.tensor([0.0, 0.05], dtype=torch.float64), rtol=rtol, atol=atol,
+              stats=st)
+    fun = lambda t, y: M.numpy() @ np.tanh(y)
+    y0n = y0[0].numpy()
+    want = select_initial_step(fun, 0.0, y0n, np.inf, np.inf, fun(0.0, y0n), 1.0, 4, rtol, atol)
+    assert math.isclose(st["first_step"], want, rel_tol=1e-9), (st["first_step"], want)
