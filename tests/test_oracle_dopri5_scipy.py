@@ -124,3 +124,30 @@ def test_initial_step_equals_scipy_select_initial_step(rtol, atol):
     y0n = y0[0].numpy()
     want = select_initial_step(fun, 0.0, y0n, np.inf, np.inf, fun(0.0, y0n), 1.0, 4, rtol, atol)
     assert math.isclose(st["first_step"], want, rel_tol=1e-9), (st["first_step"], want)
+
+
+def test_product_dense_output_weights_equal_the_quartic_fit():
+    """fetode/dopri5.py evaluates the dense output as ONE linear combination of (ya, yb, k_0..k_6) (host-side weights
+    `_dense_weights`, also computed on the device by the solve kernel).  Against the definition it was derived from
+    (torchdiffeq _interp_fit / _interp_evaluate: quartic through ya, y_mid, yb with end slopes), on random data."""
+    from fetode import dopri5 as D
+    rng = np.random.default_rng(0)
+    for _ in range(20):
+        ya, yb = rng.normal(size=3), rng.normal(size=3)
+        ks = rng.normal(size=(7, 3))
+        ta = rng.uniform(-1, 1)
+        h = rng.uniform(0.01, 0.5)
+        tb = ta + h
+        tq = ta + rng.uniform(0, 1) * h
+        y_mid = ya + h * (np.array(D._C_MID) @ ks)
+        f0, f1 = ks[0], ks[6]
+        a = 2 * h * (f1 - f0) - 8 * (yb + ya) + 16 * y_mid
+        b = h * (5 * f0 - 3 * f1) + 18 * ya + 14 * yb - 32 * y_mid
+        c = h * (f1 - 4 * f0) - 11 * ya - 5 * yb + 16 * y_mid
+        x = (tq - ta) / (tb - ta)
+        want = ya + x * h * f0 + x ** 2 * c + x ** 3 * b + x ** 4 * a
+        w_ya, w_yb, w_k = D._dense_weights(ta, tb, tq, h)
+        got = w_ya * ya + w_yb * yb + np.array(w_k) @ ks
+        assert np.allclose(got, want, rtol=1e-12, atol=1e-12)
+    assert D._dense_weights(0.0, 1.0, 1.0, 1.0) == (0.0, 1.0, [0.0] * 7)
+    assert D._dense_weights(0.0, 1.0, 0.0, 1.0) == (1.0, 0.0, [0.0] * 7)
