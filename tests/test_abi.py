@@ -27,6 +27,13 @@ def test_library_exports_every_declared_symbol():
     assert lib.fetode_version() >= 100
     lib.fetode_strerror.restype = ctypes.c_char_p
     assert b"shape" in lib.fetode_strerror(-4)
+    # host-only queries of the allocation-free variant: its limit is the header's, and the error it answers with has a text
+    src = open(os.path.join(ROOT, "include", "fetode.h")).read()
+    cap = int(re.search(r"#define\s+FETODE_STATIC_WS_FLOATS\s+(\d+)", src).group(1))
+    lib.fetode_kanlinear_bwd_static_max_floats.restype = ctypes.c_int64
+    assert lib.fetode_kanlinear_bwd_static_max_floats() == cap == 262144
+    toolarge = int(re.search(r"#define\s+FETODE_ETOOLARGE\s+\((-?\d+)\)", src).group(1))
+    assert b"static" in lib.fetode_strerror(toolarge)
 
 
 def test_every_reference_citation_in_header_names_a_file_and_line():
